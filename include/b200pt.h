@@ -1,0 +1,283 @@
+/* b200pt.h — C ABI of libb200pt.so, the B200-native (sm_100a CUDA) replacement for the
+ * trace-loop hot path of antlilja/vulkan-pathtracer.
+ *
+ * The reference has no FFI; the seam is the public surface of `RaytracingPass`
+ * (src/RaytracingPass.zig) as used by src/main.zig, with `Scene` (src/Scene.zig) and `Camera`
+ * (src/Camera.zig) values crossing it.  Each entry point below cites the reference interface it
+ * replaces.  Plain pointers and sizes only; no C++/torch types.  All functions return 0 on
+ * success or a negative PtStatus; pt_last_error() gives a thread-local message.
+ *
+ * Ownership (mirrors `defer scene.deinit()` right after Scene.load, src/RaytracingPass.zig:102-103):
+ * host scene arrays are borrowed for the duration of pt_create only; the renderer copies what it
+ * needs to the device before returning and owns all device memory until pt_destroy.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ status codes
+ * Negative values mirror the named Zig errors of the loader (src/Scene.zig:135,176-182,251,266,
+ * 277,292,307,322,495-496) and generic failures. */
+typedef enum PtStatus {
+    PT_OK = 0,
+    PT_ERR_INVALID_ARGUMENT = -1,
+    PT_ERR_CUDA = -2,
+    PT_ERR_OUT_OF_MEMORY = -3,
+    PT_ERR_IO = -4,                       /* std.fs open/read errors, error.EndOfFile */
+    PT_ERR_INVALID_FILE_EXTENSION = -10,  /* error.InvalidFileExtension   Scene.zig:135 */
+    PT_ERR_GLTF_PARSE = -11,              /* zgltf parse errors            Scene.zig:92,109 */
+    PT_ERR_GLTF_NOT_TRIANGLES = -12,      /* error.GltfNotATriangleTopology Scene.zig:176 */
+    PT_ERR_GLTF_NO_INDICES = -13,         /* error.GltfNoIndices           Scene.zig:178 */
+    PT_ERR_GLTF_NO_POSITIONS = -14,       /* error.GltfNoPositions         Scene.zig:179 */
+    PT_ERR_GLTF_NO_NORMALS = -15,         /* error.GltfNoNormals           Scene.zig:180 */
+    PT_ERR_GLTF_NO_TANGENTS = -16,        /* error.GltfNoTangents          Scene.zig:181 */
+    PT_ERR_GLTF_NO_TEXCOORDS = -17,       /* error.GltfNoTextureCoordinates Scene.zig:182 */
+    PT_ERR_NO_MATERIAL = -18,             /* error.NoMaterial              Scene.zig:251 */
+    PT_ERR_NO_BUFFER_VIEW = -19,          /* error.NoBufferView            Scene.zig:266 */
+    PT_ERR_INVALID_ATTRIBUTE_TYPE = -20,  /* error.Invalid{Position,Normal,Tangent,Texcoord}Type :277-322 */
+    PT_ERR_NO_SCENE = -21,                /* error.NoScene                 Scene.zig:495 */
+    PT_ERR_TOO_MANY_SCENES = -22,         /* error.TooManyScenes           Scene.zig:496 */
+    PT_ERR_IMAGE_DECODE = -23,            /* stb_image failure             stb_image.zig:11-18 */
+    PT_ERR_INVALID_INDEX_TYPE = -24,      /* `unreachable` at Scene.zig:252-256 (u8 indices) */
+    PT_ERR_NCCL = -30
+} PtStatus;
+
+/* ------------------------------------------------------------------ scene data contract
+ * 1:1 with the host arrays of `Scene` (src/Scene.zig:14-54, 68-77). */
+
+/* Scene.Primitive (src/Scene.zig:24-37).  Offsets are byte offsets into triangle_data.
+ * info = material_index[0:24] | uint32_indices << 31  (device flags, src/RaytracingPass.zig:18-31,
+ * src/shaders/triangle.glsl:4-5). */
+typedef struct PtPrimitive {
+    uint64_t indices_offset;
+    uint64_t positions_offset;
+    uint64_t normals_offset;
+    uint64_t tangents_offset;
+    uint64_t uvs_offset;
+    uint32_t max_vertex;
+    uint32_t triangle_count;
+    uint32_t info;
+    uint32_t _pad;
+} PtPrimitive;
+
+#define PT_MATERIAL_INDEX_MASK 0x00FFFFFFu
+#define PT_UINT32_INDICES_MASK 0x80000000u
+#define PT_INVALID_TEXTURE 0xFFFFFFFFu
+
+/* Scene.Mesh (src/Scene.zig:19-22): primitive range [start, end) — one BLAS per mesh, one geometry
+ * per primitive (src/RaytracingPass.zig:277-352). */
+typedef struct PtMesh {
+    uint32_t start;
+    uint32_t end;
+} PtMesh;
+
+/* Scene.Material (src/Scene.zig:39-48) == shader Material (src/shaders/material.glsl:7-16). */
+typedef struct PtMaterial {
+    uint32_t albedo_factor;           /* r | g<<8 | b<<16, unorm8 */
+    uint32_t metal_roughness_factor;  /* roughness<<8 | metallic<<16 */
+    uint32_t emissive_factor;
+    uint32_t albedo_texture_index;    /* PT_INVALID_TEXTURE = none */
+    uint32_t metal_roughness_texture_index;
+    uint32_t emissive_texture_index;
+    uint32_t normal_texture_index;
+} PtMaterial;
+
+/* Scene.Texture (src/Scene.zig:50-54): tightly packed RGBA8, row 0 first, uploaded as
+ * r8g8b8a8_unorm with a single mip (src/RaytracingPass.zig:500-512, src/Image.zig:32). */
+typedef struct PtTexture {
+    const uint8_t* rgba;
+    uint32_t width;
+    uint32_t height;
+} PtTexture;
+
+/* Scene.Instance (src/Scene.zig:14-17).  transform = 16 floats, rows of M (the Mat4 is stored
+ * transposed, Scene.zig:529); the first 12 (3x4 row-major) are what the TLAS consumes
+ * (src/Tlas.zig:33-41). */
+typedef struct PtInstance {
+    uint64_t mesh_index;
+    float transform[16];
+} PtInstance;
+
+typedef struct PtSceneDesc {
+    const uint8_t* triangle_data;
+    size_t triangle_data_len;
+    const PtPrimitive* primitives;
+    size_t num_primitives;
+    const PtMesh* meshes;
+    size_t num_meshes;
+    const PtMaterial* materials;
+    size_t num_materials;
+    const PtTexture* textures;
+    size_t num_textures;
+    const PtInstance* instances;
+    size_t num_instances;
+} PtSceneDesc;
+
+/* ------------------------------------------------------------------ render configuration
+ * Arguments of RaytracingPass.init (src/RaytracingPass.zig:87-97) and the CLI defaults
+ * (src/main.zig:29-67). */
+enum {
+    PT_PARTITION_NONE = 0,   /* this renderer renders every pixel */
+    PT_PARTITION_TILES = 1   /* interleaved 32x8 tiles: owner = tile_index % world */
+};
+
+enum {
+    PT_FLAG_SORT_BY_MATERIAL = 1u << 0,   /* material-sorted shading queue */
+    PT_FLAG_TRACE_BVH2 = 1u << 1,         /* use the simple BVH2 reference walker, not the BVH8 kernel */
+    PT_FLAG_NO_PRIMARY_REUSE = 1u << 2    /* re-trace the (identical) primary ray for every sample */
+};
+
+typedef struct PtRenderConfig {
+    uint32_t width;        /* --resolution-x (1920) */
+    uint32_t height;       /* --resolution-y (1080) */
+    uint32_t num_samples;  /* --num-samples  (1)  NUM_SAMPLES spec constant, ray_gen.rgen:17 */
+    uint32_t num_bounces;  /* --num-bounces  (2)  NUM_BOUNCES = ray segments,  ray_gen.rgen:18 */
+    uint32_t divider;      /* --render-resolution-divider (1), RaytracingPass.zig:149-152 */
+    int32_t device;        /* CUDA device ordinal */
+    int32_t rank;          /* tile owner id   (PT_PARTITION_TILES) */
+    int32_t world;         /* number of ranks (PT_PARTITION_TILES) */
+    uint32_t partition;    /* PT_PARTITION_* */
+    uint32_t flags;        /* PT_FLAG_* */
+} PtRenderConfig;
+
+/* Per-frame input == PushConstants (src/RayTracingPipeline.zig:15-22, filled at
+ * src/RaytracingPass.zig:563-569). */
+typedef struct PtCamera {
+    float position[4];
+    float horizontal[4];
+    float vertical[4];
+    float forward[4];
+    uint32_t frame_count;
+} PtCamera;
+
+/* Closest-hit record == Payload (src/shaders/common.glsl:4-11) without the matrices (they follow
+ * from `instance`).  Miss: t == 1e32f and all ids 0xFFFFFFFF. */
+typedef struct PtHit {
+    float t;
+    float b1;
+    float b2;
+    uint32_t instance;
+    uint32_t primitive_index;  /* meshes[mesh].start + geometry, closest_hit.rchit:11 */
+    uint32_t triangle_index;   /* gl_PrimitiveID,                closest_hit.rchit:12 */
+} PtHit;
+
+typedef struct PtRay {
+    float origin[3];
+    float tmin;
+    float dir[3];
+    float tmax;
+} PtRay;
+
+typedef struct PtStats {
+    uint64_t rays_traced;        /* closest-hit queries executed by the last pt_render */
+    uint64_t rays_hit;
+    uint32_t wavefront_iterations;
+    uint32_t kernel_launches;    /* kernels launched by the last pt_render */
+    float ms_trace;              /* CUDA-event time of the traversal launches of the last frame
+                                    (only when profiling is enabled with pt_set_profiling) */
+    float ms_shade;
+    float ms_other;
+    float ms_total;
+    uint64_t bvh_nodes;          /* BVH8 nodes (all BLAS + TLAS) */
+    uint64_t bvh_bytes;
+    uint64_t num_triangles;
+    float ms_build;              /* device BVH build time in pt_create */
+} PtStats;
+
+typedef struct PtRenderer PtRenderer;
+typedef struct PtScene PtScene;
+
+/* ------------------------------------------------------------------ errors */
+const char* pt_last_error(void);
+const char* pt_status_name(int status);
+
+/* ------------------------------------------------------------------ Scene.load  (src/Scene.zig:79-154)
+ * glTF 2.0 (.gltf with external .bin/.png, or .glb) -> host arrays with the exact layout of the
+ * reference loader.  `*out` owns the arrays; pt_scene_desc() borrows them. */
+int pt_scene_load(const char* path, PtScene** out);
+int pt_scene_desc(const PtScene* scene, PtSceneDesc* out);
+void pt_scene_free(PtScene* scene);
+
+/* ------------------------------------------------------------------ Camera  (src/Camera.zig:25-46,86-102)
+ * Camera.new(fov, aspect, position) followed by updateOrientation/updateVectors with the given
+ * yaw/pitch in degrees (0,0 = reference start-up state, src/main.zig:220-224). */
+int pt_camera_new(float fov, float aspect_ratio, const float position[3], float yaw_deg,
+                  float pitch_deg, uint32_t frame_count, PtCamera* out);
+
+/* ------------------------------------------------------------------ RaytracingPass
+ * init    src/RaytracingPass.zig:87-200  (scene upload, BLAS/TLAS build -> GPU BVH8 builder) */
+int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer** out);
+/* deinit  src/RaytracingPass.zig:202-222 */
+void pt_destroy(PtRenderer* r);
+/* record  src/RaytracingPass.zig:520-675: enqueue one frame on `cuda_stream` (a cudaStream_t, or
+ * NULL for the renderer's own stream) and return immediately; like the reference the image is
+ * overwritten every frame (ray_gen.rgen:21,104). */
+int pt_render(PtRenderer* r, const PtCamera* camera, void* cuda_stream);
+/* the frame fence  src/Swapchain.zig:60-62 */
+int pt_sync(PtRenderer* r);
+/* resize  src/RaytracingPass.zig:677-704.  Like the reference it re-creates the storage image at
+ * the full new extent (the divider is dropped, quirk Q13). */
+int pt_resize(PtRenderer* r, uint32_t width, uint32_t height);
+
+/* Output image (storage image, ray_gen.rgen:104).  Render extent = resolution / divider. */
+int pt_render_extent(const PtRenderer* r, uint32_t* width, uint32_t* height);
+/* linear RGBA fp32, row 0 = top, alpha 1 */
+int pt_read_rgba32f(PtRenderer* r, float* host_dst);
+int pt_device_image(PtRenderer* r, float** device_ptr);
+/* The reference's own pixel format: b8g8r8a8_unorm (src/Swapchain.zig:115-118): NaN->0, clamp,
+ * round-to-nearest 8 bit.  Converted on the device, then copied. */
+int pt_read_bgra8(PtRenderer* r, uint8_t* host_dst);
+/* Asynchronous variants for pipelined hosts: convert/copy on the render stream into pinned host
+ * memory supplied by the caller; complete after pt_sync or a sync of the stream. */
+int pt_read_rgba32f_async(PtRenderer* r, float* pinned_host_dst, void* cuda_stream);
+int pt_read_bgra8_async(PtRenderer* r, uint8_t* pinned_host_dst, void* cuda_stream);
+/* Primary-hit id buffers of the last frame (parity: instance / primitive_index / triangle_index,
+ * 0xFFFFFFFF on miss).  Any pointer may be NULL. */
+int pt_read_ids(PtRenderer* r, uint32_t* instance, uint32_t* primitive, uint32_t* triangle);
+/* Full-resolution output: nearest up-scale of the render extent when divider > 1 (the blit at
+ * src/RaytracingPass.zig:599-635), plain copy otherwise. */
+int pt_read_rgba32f_upscaled(PtRenderer* r, float* host_dst);
+
+/* Progressive accumulation over frame_count (optional, off by default: the reference overwrites).
+ * When enabled pt_render adds the frame into a running sum; pt_read_accum_mean divides. */
+int pt_set_accumulate(PtRenderer* r, int enabled);
+int pt_reset_accum(PtRenderer* r);
+int pt_device_accum(PtRenderer* r, float** device_ptr, uint32_t* frames);
+int pt_read_accum_mean(PtRenderer* r, float* host_dst, uint32_t total_frames);
+
+/* Measurement. */
+int pt_set_profiling(PtRenderer* r, int enabled);
+int pt_get_stats(PtRenderer* r, PtStats* out);
+
+/* Kernel-level access for parity tests: trace `n` arbitrary world-space rays through the same
+ * BVH and traversal kernel pt_render uses (host pointers). */
+int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits);
+/* Independent, unoptimised one-thread-per-ray walker over the shipped BVH8: counts the nodes and
+ * triangles an ordered closest-hit traversal must decode (SURVEY.md §8d algorithmic bytes =
+ * 80*nodes + 48*tris).  Counts the ray set of the last pt_render. */
+int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t* rays);
+
+/* Multi-GPU (one process per GPU).  Peer stores: rank 0 exports its image buffer as a CUDA IPC
+ * handle, the other ranks open it and their accumulate kernel writes owned tiles straight into it
+ * over NVLink.  `handle` is 64 bytes. */
+int pt_ipc_export_image(PtRenderer* r, uint8_t handle[64]);
+int pt_ipc_open_root_image(PtRenderer* r, const uint8_t handle[64]);
+
+/* Headless image output (replaces the swapchain present). */
+int pt_write_pfm(const char* path, const float* rgba, uint32_t width, uint32_t height);
+int pt_write_exr(const char* path, const float* rgba, uint32_t width, uint32_t height);
+
+/* Library/device introspection. */
+int pt_device_count(void);
+const char* pt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_H */
