@@ -1,0 +1,245 @@
+"""Host-side mirror of the reference's RaytracingPass interface over libb200pt.so (ctypes).
+
+    RaytracingPass.init(...)    -> Renderer(scene, width, height, num_samples, num_bounces, divider)
+    RaytracingPass.record(...)  -> Renderer.record(camera)   (asynchronous, like a command buffer)
+    frame fence                 -> Renderer.sync()
+    RaytracingPass.resize(...)  -> Renderer.resize(w, h)
+    RaytracingPass.deinit()     -> Renderer.deinit()
+
+(/root/reference/src/RaytracingPass.zig:87-97, 520-528, 677-683, 202).  There is NO CPU fallback:
+importing works anywhere (so the symbol table can be checked), but creating a Renderer without the
+CUDA library or without a GPU raises.
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+if _ROOT not in sys.path:
+    sys.path.insert(0, _ROOT)
+
+from tools.scene import (PtCamera, PtInstance, PtMaterial, PtMesh, PtPrimitive, PtRenderConfig,  # noqa: E402,F401
+                         PtSceneDesc, PtTexture)
+
+LIB_PATH = os.path.join(_HERE, "libb200pt.so")
+
+PT_PARTITION_NONE, PT_PARTITION_TILES = 0, 1
+PT_FLAG_SORT_BY_MATERIAL, PT_FLAG_TRACE_BVH2, PT_FLAG_NO_PRIMARY_REUSE = 1, 2, 4
+
+PtHit_dtype = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("instance", "<u4"), ("primitive_index", "<u4"),
+                        ("triangle_index", "<u4")])
+PtRay_dtype = np.dtype([("origin", "<f4", 3), ("tmin", "<f4"), ("dir", "<f4", 3), ("tmax", "<f4")])
+
+
+class PtStats(C.Structure):
+    _fields_ = [("rays_traced", C.c_uint64), ("rays_hit", C.c_uint64), ("wavefront_iterations", C.c_uint32),
+                ("kernel_launches", C.c_uint32), ("ms_trace", C.c_float), ("ms_shade", C.c_float), ("ms_other", C.c_float),
+                ("ms_total", C.c_float), ("bvh_nodes", C.c_uint64), ("bvh_bytes", C.c_uint64), ("num_triangles", C.c_uint64),
+                ("ms_build", C.c_float)]
+
+
+class PtError(RuntimeError):
+    def __init__(self, status, name, message):
+        super().__init__(f"{name} ({status}): {message}")
+        self.status, self.name, self.message = status, name, message
+
+
+_lib = None
+
+
+def lib():
+    """Load libb200pt.so (fails loudly when it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PtError(-2, "CudaError", f"{LIB_PATH} is missing: build it with __graft_entry__.build() "
+                          "(make -C vulkan-pathtracer_b200/csrc); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.pt_last_error.restype = C.c_char_p
+        L.pt_status_name.restype = C.c_char_p
+        L.pt_status_name.argtypes = [C.c_int]
+        L.pt_version.restype = C.c_char_p
+        L.pt_create.argtypes = [C.POINTER(PtSceneDesc), C.POINTER(PtRenderConfig), C.POINTER(C.c_void_p)]
+        L.pt_destroy.argtypes = [C.c_void_p]
+        L.pt_destroy.restype = None
+        L.pt_render.argtypes = [C.c_void_p, C.POINTER(PtCamera), C.c_void_p]
+        L.pt_sync.argtypes = [C.c_void_p]
+        L.pt_resize.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+        L.pt_render_extent.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        for n in ("pt_read_rgba32f", "pt_read_bgra8", "pt_read_rgba32f_upscaled"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_void_p]
+        for n in ("pt_read_rgba32f_async", "pt_read_bgra8_async"):
+            getattr(L, n).argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pt_device_image.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.pt_read_ids.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pt_set_accumulate.argtypes = [C.c_void_p, C.c_int]
+        L.pt_reset_accum.argtypes = [C.c_void_p]
+        L.pt_device_accum.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32)]
+        L.pt_read_accum_mean.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        L.pt_set_profiling.argtypes = [C.c_void_p, C.c_int]
+        L.pt_get_stats.argtypes = [C.c_void_p, C.POINTER(PtStats)]
+        L.pt_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.pt_count_traversal.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.pt_ipc_export_image.argtypes = [C.c_void_p, C.c_void_p]
+        L.pt_ipc_open_root_image.argtypes = [C.c_void_p, C.c_void_p]
+        L.pt_camera_new.argtypes = [C.c_float, C.c_float, C.POINTER(C.c_float * 3), C.c_float, C.c_float, C.c_uint32,
+                                    C.POINTER(PtCamera)]
+        L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.pt_write_exr.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.pt_scene_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        L.pt_scene_desc.argtypes = [C.c_void_p, C.POINTER(PtSceneDesc)]
+        L.pt_scene_free.argtypes = [C.c_void_p]
+        L.pt_scene_free.restype = None
+        _lib = L
+    return _lib
+
+
+def check(status):
+    if status != 0:
+        L = lib()
+        raise PtError(status, L.pt_status_name(status).decode(), (L.pt_last_error() or b"").decode())
+
+
+def camera_new(fov, aspect_ratio, position=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0, frame_count=0):
+    """Camera.new(fov, aspect, position) (Camera.zig:25-46) through the C ABI."""
+    cam = PtCamera()
+    pos = (C.c_float * 3)(*position)
+    check(lib().pt_camera_new(fov, aspect_ratio, C.byref(pos), yaw, pitch, frame_count, C.byref(cam)))
+    return cam
+
+
+class LoadedScene:
+    """Scene.load(path) (Scene.zig:79) through the C ABI; owns the host arrays."""
+
+    def __init__(self, path):
+        self.handle = C.c_void_p()
+        check(lib().pt_scene_load(os.fsencode(path), C.byref(self.handle)))
+        self._desc = PtSceneDesc()
+        check(lib().pt_scene_desc(self.handle, C.byref(self._desc)))
+
+    def desc(self):
+        return self._desc
+
+    def close(self):
+        if self.handle:
+            lib().pt_scene_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Renderer:
+    """RaytracingPass over CUDA.  `scene` is anything with a .desc() -> PtSceneDesc
+    (tools.scene.PackedScene or LoadedScene)."""
+
+    def __init__(self, scene, width=1920, height=1080, num_samples=1, num_bounces=2, divider=1, device=0, rank=0, world=1,
+                 partition=PT_PARTITION_NONE, flags=0):
+        self.handle = C.c_void_p()
+        self.cfg = PtRenderConfig(width, height, num_samples, num_bounces, divider, device, rank, world, partition, flags)
+        desc = scene.desc()
+        check(lib().pt_create(C.byref(desc), C.byref(self.cfg), C.byref(self.handle)))
+        w, h = C.c_uint32(), C.c_uint32()
+        check(lib().pt_render_extent(self.handle, C.byref(w), C.byref(h)))
+        self.width, self.height = w.value, h.value
+
+    # -- RaytracingPass.record / fence / resize / deinit
+    def record(self, camera, stream=None):
+        check(lib().pt_render(self.handle, C.byref(camera), stream))
+
+    def sync(self):
+        check(lib().pt_sync(self.handle))
+
+    def resize(self, width, height):
+        check(lib().pt_resize(self.handle, width, height))
+        w, h = C.c_uint32(), C.c_uint32()
+        check(lib().pt_render_extent(self.handle, C.byref(w), C.byref(h)))
+        self.width, self.height = w.value, h.value
+
+    def deinit(self):
+        if self.handle:
+            lib().pt_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.deinit()
+        except Exception:
+            pass
+
+    # -- outputs
+    def image(self):
+        out = np.empty((self.height, self.width, 4), np.float32)
+        check(lib().pt_read_rgba32f(self.handle, out.ctypes.data))
+        return out
+
+    def image_bgra8(self):
+        out = np.empty((self.height, self.width, 4), np.uint8)
+        check(lib().pt_read_bgra8(self.handle, out.ctypes.data))
+        return out
+
+    def image_upscaled(self):
+        out = np.empty((self.cfg.height, self.cfg.width, 4), np.float32)
+        check(lib().pt_read_rgba32f_upscaled(self.handle, out.ctypes.data))
+        return out
+
+    def ids(self):
+        a = [np.empty((self.height, self.width), np.uint32) for _ in range(3)]
+        check(lib().pt_read_ids(self.handle, a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data))
+        return tuple(a)
+
+    def device_image_ptr(self):
+        p = C.c_void_p()
+        check(lib().pt_device_image(self.handle, C.byref(p)))
+        return p.value
+
+    def set_accumulate(self, on):
+        check(lib().pt_set_accumulate(self.handle, 1 if on else 0))
+
+    def reset_accum(self):
+        check(lib().pt_reset_accum(self.handle))
+
+    def device_accum_ptr(self):
+        p, n = C.c_void_p(), C.c_uint32()
+        check(lib().pt_device_accum(self.handle, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def accum_mean(self, total_frames=0):
+        out = np.empty((self.height, self.width, 4), np.float32)
+        check(lib().pt_read_accum_mean(self.handle, out.ctypes.data, total_frames))
+        return out
+
+    def set_profiling(self, on):
+        check(lib().pt_set_profiling(self.handle, 1 if on else 0))
+
+    def stats(self):
+        s = PtStats()
+        check(lib().pt_get_stats(self.handle, C.byref(s)))
+        return s
+
+    def trace(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=PtRay_dtype)
+        hits = np.empty(len(rays), PtHit_dtype)
+        check(lib().pt_trace_rays(self.handle, rays.ctypes.data, len(rays), hits.ctypes.data))
+        return hits
+
+    def count_traversal(self):
+        n, t, r = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(lib().pt_count_traversal(self.handle, C.byref(n), C.byref(t), C.byref(r)))
+        return n.value, t.value, r.value
+
+
+def write_pfm(path, rgba):
+    rgba = np.ascontiguousarray(rgba, np.float32)
+    check(lib().pt_write_pfm(os.fsencode(path), rgba.ctypes.data, rgba.shape[1], rgba.shape[0]))
+
+
+def write_exr(path, rgba):
+    rgba = np.ascontiguousarray(rgba, np.float32)
+    check(lib().pt_write_exr(os.fsencode(path), rgba.ctypes.data, rgba.shape[1], rgba.shape[0]))

@@ -1,0 +1,581 @@
+// api.cu — the C ABI of include/b200pt.h: renderer object (RaytracingPass.init / record / resize /
+// deinit, src/RaytracingPass.zig:87-222,520-704), image read-back, stats and test entry points.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "bvh_build.h"
+#include "render.h"
+
+namespace pt {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+
+}  // namespace pt
+
+using namespace pt;
+
+struct PtRenderer {
+    PtRenderConfig cfg{};
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    // scene on the device
+    uint8_t* d_blob = nullptr;
+    PrimRec* d_prims = nullptr;
+    PtMaterial* d_materials = nullptr;
+    TexRec* d_textures = nullptr;
+    std::vector<uint32_t*> d_texels;
+    PtInstance* d_instances_raw = nullptr;
+    InstanceRec* d_instances = nullptr;
+    SceneBvh bvh;
+    DeviceScene scene{};
+    uint64_t num_triangles = 0;
+    // frame state
+    PixelMap pm{};
+    PathBuffers pb{};
+    uint32_t max_iters = 0;
+    uint32_t full_w = 0, full_h = 0;     // window extent (resolution-x/-y)
+    float* d_image = nullptr;            // render extent, RGBA32F
+    uint32_t* d_ids = nullptr;           // 3 * W*H
+    uint8_t* d_bgra = nullptr;
+    float* d_upscaled = nullptr;
+    float* d_accum = nullptr;
+    float* d_remote_image = nullptr;     // rank 0's image mapped through CUDA IPC (optional)
+    bool accumulate = false;
+    uint32_t accum_frames = 0;
+    bool profiling = false;
+    TraceMode trace_mode = TRACE_BVH8;
+    std::vector<cudaEvent_t> events;     // profiling: 2 per kernel launch
+    std::vector<int> event_kind;         // 0 trace, 1 shade, 2 other
+    uint32_t last_iters = 0;
+    uint32_t last_launches = 0;
+    PtCamera last_cam{};
+    bool have_last_cam = false;
+    // standalone trace buffers
+    uint32_t* d_cursor = nullptr;
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(T** p, size_t count) {
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(p), std::max<size_t>(count, 1) * sizeof(T));
+    if (e != cudaSuccess) {
+        set_error(std::string("cudaMalloc failed: ") + cudaGetErrorString(e));
+        *p = nullptr;
+        return e == cudaErrorMemoryAllocation ? PT_ERR_OUT_OF_MEMORY : PT_ERR_CUDA;
+    }
+    return PT_OK;
+}
+
+void free_frame(PtRenderer* r) {
+    PathBuffers& b = r->pb;
+    cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b);
+    cudaFree(b.atten_sx); cudaFree(b.color_sy); cudaFree(b.final_sb); cudaFree(b.queue[0]); cudaFree(b.queue[1]);
+    cudaFree(b.qcount); cudaFree(b.trace_next); cudaFree(b.trav_counters);
+    b = PathBuffers{};
+    cudaFree(r->d_image); cudaFree(r->d_ids); cudaFree(r->d_bgra); cudaFree(r->d_upscaled); cudaFree(r->d_accum);
+    r->d_image = nullptr; r->d_ids = nullptr; r->d_bgra = nullptr; r->d_upscaled = nullptr; r->d_accum = nullptr;
+}
+
+// storage image = extent / divider (RaytracingPass.zig:149-152)
+int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divider) {
+    free_frame(r);
+    const uint32_t div = divider ? divider : 1u;
+    r->full_w = full_w; r->full_h = full_h;
+    PixelMap& pm = r->pm;
+    pm.width = full_w / div; pm.height = full_h / div;
+    pm.tiles_x = (pm.width + 31u) / 32u; pm.tiles_y = (pm.height + 7u) / 8u;
+    const bool tiles = r->cfg.partition == PT_PARTITION_TILES && r->cfg.world > 1;
+    pm.rank = tiles ? (uint32_t)r->cfg.rank : 0u;
+    pm.world = tiles ? (uint32_t)r->cfg.world : 1u;
+    const uint32_t n_tiles = pm.tiles_x * pm.tiles_y;
+    const uint32_t owned = n_tiles > pm.rank ? (n_tiles - pm.rank + pm.world - 1u) / pm.world : 0u;
+    pm.num_slots = owned * 256u;
+    const size_t n = pm.num_slots;
+    const uint32_t S = r->cfg.num_samples, B = r->cfg.num_bounces;
+    // trace iterations: B for the first sample, B-1 for every further one (primary hit reused);
+    // S*B when reuse is disabled.
+    uint64_t iters = (S == 0 || B == 0) ? 0 : ((r->cfg.flags & PT_FLAG_NO_PRIMARY_REUSE) ? (uint64_t)S * B : (uint64_t)B + (uint64_t)(S - 1) * (B - 1));
+    if (iters > (1u << 20)) { set_error("num_samples * num_bounces too large"); return PT_ERR_INVALID_ARGUMENT; }
+    r->max_iters = (uint32_t)iters;
+    PathBuffers& b = r->pb;
+    int rc;
+#define A(ptr, cnt) if ((rc = dev_alloc(&(ptr), (cnt))) != PT_OK) return rc
+    A(b.ray_o, n); A(b.ray_d, n); A(b.hit_a, n); A(b.hit_b, n); A(b.prim_a, n); A(b.prim_b, n);
+    A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n);
+    A(b.qcount, (size_t)r->max_iters + 2); A(b.trace_next, (size_t)r->max_iters + 2); A(b.trav_counters, 4);
+    const size_t px = (size_t)pm.width * pm.height;
+    A(r->d_image, px * 4); A(r->d_ids, px * 3);
+#undef A
+    PT_CUDA_CHECK(cudaMemset(r->d_image, 0, std::max<size_t>(px, 1) * 16));
+    PT_CUDA_CHECK(cudaMemset(r->d_ids, 0xff, std::max<size_t>(px, 1) * 12));
+    PT_CUDA_CHECK(cudaMemset(b.trav_counters, 0, 16));
+    r->accum_frames = 0;
+    return PT_OK;
+}
+
+int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
+    int rc;
+    if (s->triangle_data_len > 0xFFFFFFF0ull) { set_error("triangle_data larger than 4 GiB is not supported"); return PT_ERR_INVALID_ARGUMENT; }
+    if ((rc = dev_alloc(&r->d_blob, s->triangle_data_len + 16)) != PT_OK) return rc;
+    if (s->triangle_data_len) PT_CUDA_CHECK(cudaMemcpy(r->d_blob, s->triangle_data, s->triangle_data_len, cudaMemcpyHostToDevice));
+    // primitives: validate every offset against the blob (the reference trusts the file; we must not fault)
+    std::vector<PrimRec> prims(s->num_primitives);
+    for (size_t i = 0; i < s->num_primitives; ++i) {
+        const PtPrimitive& p = s->primitives[i];
+        const uint64_t nv = (uint64_t)p.max_vertex + 1, isz = (p.info & PT_UINT32_INDICES_MASK) ? 4 : 2;
+        const bool ok = p.indices_offset + 3ull * p.triangle_count * isz <= s->triangle_data_len && p.positions_offset + 12 * nv <= s->triangle_data_len &&
+                        p.normals_offset + 12 * nv <= s->triangle_data_len && p.tangents_offset + 16 * nv <= s->triangle_data_len &&
+                        p.uvs_offset + 8 * nv <= s->triangle_data_len && (p.indices_offset % isz) == 0 && (p.positions_offset % 4) == 0 &&
+                        (p.normals_offset % 4) == 0 && (p.tangents_offset % 4) == 0 && (p.uvs_offset % 4) == 0;
+        if (!ok) { set_error("primitive " + std::to_string(i) + ": offsets outside triangle_data or misaligned"); return PT_ERR_INVALID_ARGUMENT; }
+        if ((p.info & PT_MATERIAL_INDEX_MASK) >= s->num_materials) { set_error("primitive " + std::to_string(i) + ": material index out of range"); return PT_ERR_INVALID_ARGUMENT; }
+        // vertex indices must stay inside the attribute arrays
+        if (p.triangle_count) {
+            uint32_t mx = 0;
+            if (isz == 2) { const uint16_t* q = reinterpret_cast<const uint16_t*>(s->triangle_data + p.indices_offset); for (uint64_t k = 0; k < 3ull * p.triangle_count; ++k) mx = std::max<uint32_t>(mx, q[k]); }
+            else { const uint32_t* q = reinterpret_cast<const uint32_t*>(s->triangle_data + p.indices_offset); for (uint64_t k = 0; k < 3ull * p.triangle_count; ++k) mx = std::max(mx, q[k]); }
+            if (mx > p.max_vertex) { set_error("primitive " + std::to_string(i) + ": vertex index beyond max_vertex"); return PT_ERR_INVALID_ARGUMENT; }
+        }
+        prims[i] = PrimRec{(uint32_t)p.indices_offset, (uint32_t)p.positions_offset, (uint32_t)p.normals_offset, (uint32_t)p.tangents_offset,
+                           (uint32_t)p.uvs_offset, p.info, p.triangle_count, 0};
+        r->num_triangles += p.triangle_count;
+    }
+    if ((rc = dev_alloc(&r->d_prims, prims.size())) != PT_OK) return rc;
+    if (!prims.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_prims, prims.data(), prims.size() * sizeof(PrimRec), cudaMemcpyHostToDevice));
+    // materials + textures (r8g8b8a8_unorm, single mip; RaytracingPass.zig:490-518)
+    for (size_t i = 0; i < s->num_materials; ++i) {
+        const uint32_t t[4] = {s->materials[i].albedo_texture_index, s->materials[i].metal_roughness_texture_index,
+                               s->materials[i].emissive_texture_index, s->materials[i].normal_texture_index};
+        for (uint32_t v : t)
+            if (v != PT_INVALID_TEXTURE && v >= s->num_textures) { set_error("material " + std::to_string(i) + ": texture index out of range"); return PT_ERR_INVALID_ARGUMENT; }
+    }
+    if ((rc = dev_alloc(&r->d_materials, s->num_materials)) != PT_OK) return rc;
+    if (s->num_materials) PT_CUDA_CHECK(cudaMemcpy(r->d_materials, s->materials, s->num_materials * sizeof(PtMaterial), cudaMemcpyHostToDevice));
+    std::vector<TexRec> texs(s->num_textures);
+    r->d_texels.assign(s->num_textures, nullptr);
+    for (size_t i = 0; i < s->num_textures; ++i) {
+        const PtTexture& t = s->textures[i];
+        if (t.width == 0 || t.height == 0 || !t.rgba) { set_error("texture " + std::to_string(i) + ": empty"); return PT_ERR_INVALID_ARGUMENT; }
+        const size_t n = (size_t)t.width * t.height;
+        if ((rc = dev_alloc(&r->d_texels[i], n)) != PT_OK) return rc;
+        PT_CUDA_CHECK(cudaMemcpy(r->d_texels[i], t.rgba, n * 4, cudaMemcpyHostToDevice));
+        texs[i] = TexRec{r->d_texels[i], t.width, t.height};
+    }
+    if ((rc = dev_alloc(&r->d_textures, texs.size())) != PT_OK) return rc;
+    if (!texs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_textures, texs.data(), texs.size() * sizeof(TexRec), cudaMemcpyHostToDevice));
+    // meshes / instances
+    std::vector<PtMesh> meshes(s->meshes, s->meshes + s->num_meshes);
+    for (size_t m = 0; m < meshes.size(); ++m)
+        if (meshes[m].start > meshes[m].end || meshes[m].end > s->num_primitives) { set_error("mesh " + std::to_string(m) + ": primitive range out of bounds"); return PT_ERR_INVALID_ARGUMENT; }
+    std::vector<PtInstance> inst(s->instances, s->instances + s->num_instances);
+    for (size_t i = 0; i < inst.size(); ++i)
+        if (inst[i].mesh_index >= meshes.size()) { set_error("instance " + std::to_string(i) + ": mesh index out of range"); return PT_ERR_INVALID_ARGUMENT; }
+    if ((rc = dev_alloc(&r->d_instances_raw, inst.size())) != PT_OK) return rc;
+    if (!inst.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances_raw, inst.data(), inst.size() * sizeof(PtInstance), cudaMemcpyHostToDevice));
+    // acceleration structures (createBlases + Tlas.init)
+    if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, r->stream, &r->bvh)) != PT_OK) return rc;
+    // instance records: inverse of the 3x3 linear part (host, same formula as every other user)
+    std::vector<InstanceRec> recs(inst.size());
+    for (size_t i = 0; i < inst.size(); ++i) {
+        const float* t = inst[i].transform;   // rows of M; first 12 = 3x4 (Tlas.zig:33-41)
+        M3 A;
+        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) A.m[rr][c] = t[4 * rr + c];
+        const M3 Ai = inverse(A);
+        InstanceRec& ir = recs[i];
+        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) ir.inv[3 * rr + c] = Ai.m[rr][c];
+        ir.inv[9] = t[3]; ir.inv[10] = t[7]; ir.inv[11] = t[11];
+        const uint32_t m = (uint32_t)inst[i].mesh_index;
+        ir.mesh = m;
+        ir.blas_root = r->bvh.blas_root8[m];
+        ir.bvh2_root = r->bvh.tri_off[m];
+        ir.bvh2_tri_base = r->bvh.tri_off[m];
+    }
+    if ((rc = dev_alloc(&r->d_instances, recs.size())) != PT_OK) return rc;
+    if (!recs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances, recs.data(), recs.size() * sizeof(InstanceRec), cudaMemcpyHostToDevice));
+    DeviceScene& sc = r->scene;
+    sc.triangle_data = r->d_blob; sc.prims = r->d_prims; sc.materials = r->d_materials; sc.textures = r->d_textures;
+    sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
+    sc.nodes2 = r->bvh.nodes2; sc.tris2 = r->bvh.tris2; sc.tlas2 = r->bvh.tlas2; sc.tlas_root = r->bvh.tlas_root8;
+    sc.num_instances = (uint32_t)inst.size(); sc.num_prims = (uint32_t)prims.size();
+    sc.num_materials = (uint32_t)s->num_materials; sc.num_textures = (uint32_t)s->num_textures;
+    return PT_OK;
+}
+
+void destroy_impl(PtRenderer* r) {
+    if (!r) return;
+    cudaSetDevice(r->device);
+    if (r->stream) cudaStreamSynchronize(r->stream);
+    free_frame(r);
+    for (auto e : r->events) cudaEventDestroy(e);
+    for (auto p : r->d_texels) cudaFree(p);
+    cudaFree(r->d_blob); cudaFree(r->d_prims); cudaFree(r->d_materials); cudaFree(r->d_textures);
+    cudaFree(r->d_instances_raw); cudaFree(r->d_instances); cudaFree(r->d_cursor);
+    if (r->d_remote_image) cudaIpcCloseMemHandle(r->d_remote_image);
+    r->bvh.release();
+    if (r->stream) cudaStreamDestroy(r->stream);
+    delete r;
+}
+
+}  // namespace
+
+#define PT_REQUIRE(cond, msg) do { if (!(cond)) { set_error(msg); return PT_ERR_INVALID_ARGUMENT; } } while (0)
+
+extern "C" {
+
+const char* pt_last_error(void) { return g_last_error.c_str(); }
+
+const char* pt_version(void) { return "b200pt 0.1 (sm_100a)"; }
+
+int pt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+const char* pt_status_name(int s) {
+    switch (s) {
+        case PT_OK: return "Ok";
+        case PT_ERR_INVALID_ARGUMENT: return "InvalidArgument";
+        case PT_ERR_CUDA: return "CudaError";
+        case PT_ERR_OUT_OF_MEMORY: return "OutOfMemory";
+        case PT_ERR_IO: return "IoError";
+        case PT_ERR_INVALID_FILE_EXTENSION: return "InvalidFileExtension";
+        case PT_ERR_GLTF_PARSE: return "GltfParseError";
+        case PT_ERR_GLTF_NOT_TRIANGLES: return "GltfNotATriangleTopology";
+        case PT_ERR_GLTF_NO_INDICES: return "GltfNoIndices";
+        case PT_ERR_GLTF_NO_POSITIONS: return "GltfNoPositions";
+        case PT_ERR_GLTF_NO_NORMALS: return "GltfNoNormals";
+        case PT_ERR_GLTF_NO_TANGENTS: return "GltfNoTangents";
+        case PT_ERR_GLTF_NO_TEXCOORDS: return "GltfNoTextureCoordinates";
+        case PT_ERR_NO_MATERIAL: return "NoMaterial";
+        case PT_ERR_NO_BUFFER_VIEW: return "NoBufferView";
+        case PT_ERR_INVALID_ATTRIBUTE_TYPE: return "InvalidAttributeType";
+        case PT_ERR_NO_SCENE: return "NoScene";
+        case PT_ERR_TOO_MANY_SCENES: return "TooManyScenes";
+        case PT_ERR_IMAGE_DECODE: return "ImageDecodeError";
+        case PT_ERR_INVALID_INDEX_TYPE: return "InvalidIndexType";
+        case PT_ERR_NCCL: return "NcclError";
+        default: return "Unknown";
+    }
+}
+
+int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer** out) {
+    PT_REQUIRE(scene && config && out, "pt_create: null argument");
+    *out = nullptr;
+    PT_REQUIRE(config->width > 0 && config->height > 0, "pt_create: zero resolution");
+    PT_REQUIRE(config->num_samples < 65536 && config->num_bounces < 65536, "pt_create: num_samples / num_bounces must be < 65536");
+    PT_REQUIRE(config->partition == PT_PARTITION_NONE || (config->world >= 1 && config->rank >= 0 && config->rank < config->world),
+               "pt_create: invalid rank/world");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("pt_create: no CUDA device available (this library has no CPU fallback)");
+        return PT_ERR_CUDA;
+    }
+    PT_REQUIRE(config->device >= 0 && config->device < ndev, "pt_create: device ordinal out of range");
+    PtRenderer* r = new PtRenderer();
+    r->cfg = *config;
+    if (r->cfg.divider == 0) r->cfg.divider = 1;
+    r->device = config->device;
+    int rc = PT_OK;
+    do {
+        if (cudaSetDevice(r->device) != cudaSuccess) { set_error("cudaSetDevice failed"); rc = PT_ERR_CUDA; break; }
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, r->device) != cudaSuccess) { set_error("cudaGetDeviceProperties failed"); rc = PT_ERR_CUDA; break; }
+        r->num_sms = prop.multiProcessorCount;
+        if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); rc = PT_ERR_CUDA; break; }
+        if ((rc = upload_scene(r, scene)) != PT_OK) break;
+        if ((rc = alloc_frame(r, r->cfg.width, r->cfg.height, r->cfg.divider)) != PT_OK) break;
+        if ((rc = dev_alloc(&r->d_cursor, 4)) != PT_OK) break;
+        if (r->cfg.flags & PT_FLAG_TRACE_BVH2) r->trace_mode = TRACE_BVH2;
+    } while (0);
+    if (rc != PT_OK) { std::string keep = g_last_error; destroy_impl(r); g_last_error = keep; return rc; }
+    *out = r;
+    return PT_OK;
+}
+
+void pt_destroy(PtRenderer* r) { destroy_impl(r); }
+
+static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, TraceMode mode) {
+    PathBuffers& pb = r->pb;
+    FrameParams fp;
+    fp.cam = *camera;
+    fp.num_samples = r->cfg.num_samples; fp.num_bounces = r->cfg.num_bounces; fp.flags = r->cfg.flags;
+    fp.image = r->d_remote_image ? r->d_remote_image : r->d_image;
+    const size_t px = (size_t)r->pm.width * r->pm.height;
+    fp.id_inst = r->d_ids; fp.id_prim = r->d_ids + px; fp.id_tri = r->d_ids + 2 * px;
+    PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
+    PT_CUDA_CHECK(cudaMemsetAsync(pb.trace_next, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
+    if (r->pm.world > 1 && !r->d_remote_image) PT_CUDA_CHECK(cudaMemsetAsync(r->d_image, 0, px * 16, st));
+    size_t ev = 0;
+    auto mark = [&](int kind) {
+        if (!r->profiling) return;
+        if (ev + 2 > r->events.size()) {
+            cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+            r->events.push_back(a); r->events.push_back(b); r->event_kind.push_back(kind);
+        } else {
+            r->event_kind[ev / 2] = kind;
+        }
+        cudaEventRecord(r->events[ev], st);
+    };
+    auto mark_end = [&]() { if (r->profiling) { cudaEventRecord(r->events[ev + 1], st); ev += 2; } };
+    uint32_t launches = 0;
+    mark(2); launch_raygen(r->pm, pb, fp, st); mark_end(); ++launches;
+    for (uint32_t it = 0; it < r->max_iters; ++it) {
+        mark(0); launch_trace(r->scene, pb, it, mode, r->bvh.tlas2_count, r->bvh.tlas2_leaf_instance, r->num_sms, st); mark_end();
+        mark(1); launch_shade(r->scene, r->pm, pb, fp, it, r->num_sms, st); mark_end();
+        launches += 2;
+    }
+    if (r->accumulate) {
+        if (!r->d_accum) {
+            int rc = dev_alloc(&r->d_accum, px * 4);
+            if (rc != PT_OK) return rc;
+            PT_CUDA_CHECK(cudaMemsetAsync(r->d_accum, 0, px * 16, st));
+            r->accum_frames = 0;
+        }
+        mark(2); launch_accumulate(r->d_image, r->d_accum, (uint32_t)(px * 4), st); mark_end(); ++launches;
+        r->accum_frames++;
+    }
+    PT_CUDA_CHECK(cudaGetLastError());
+    r->last_iters = r->max_iters;
+    r->last_launches = launches;
+    r->last_cam = *camera;
+    r->have_last_cam = true;
+    return PT_OK;
+}
+
+int pt_render(PtRenderer* r, const PtCamera* camera, void* cuda_stream) {
+    PT_REQUIRE(r && camera, "pt_render: null argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : r->stream;
+    return render_impl(r, camera, st, r->trace_mode);
+}
+
+int pt_sync(PtRenderer* r) {
+    PT_REQUIRE(r, "pt_sync: null renderer");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    return PT_OK;
+}
+
+int pt_resize(PtRenderer* r, uint32_t width, uint32_t height) {
+    PT_REQUIRE(r && width > 0 && height > 0, "pt_resize: invalid argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    // Like the reference, the storage image is re-created at the full new extent: the divider is
+    // dropped (RaytracingPass.zig:684-697, quirk Q13).
+    r->cfg.width = width; r->cfg.height = height; r->cfg.divider = 1;
+    return alloc_frame(r, width, height, 1);
+}
+
+int pt_render_extent(const PtRenderer* r, uint32_t* width, uint32_t* height) {
+    PT_REQUIRE(r, "pt_render_extent: null renderer");
+    if (width) *width = r->pm.width;
+    if (height) *height = r->pm.height;
+    return PT_OK;
+}
+
+int pt_device_image(PtRenderer* r, float** device_ptr) {
+    PT_REQUIRE(r && device_ptr, "pt_device_image: null argument");
+    *device_ptr = r->d_image;
+    return PT_OK;
+}
+
+int pt_read_rgba32f_async(PtRenderer* r, float* dst, void* cuda_stream) {
+    PT_REQUIRE(r && dst, "pt_read_rgba32f_async: null argument");
+    cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : r->stream;
+    PT_CUDA_CHECK(cudaMemcpyAsync(dst, r->d_image, (size_t)r->pm.width * r->pm.height * 16, cudaMemcpyDeviceToHost, st));
+    return PT_OK;
+}
+
+int pt_read_rgba32f(PtRenderer* r, float* host_dst) {
+    int rc = pt_read_rgba32f_async(r, host_dst, nullptr);
+    if (rc != PT_OK) return rc;
+    return pt_sync(r);
+}
+
+int pt_read_bgra8_async(PtRenderer* r, uint8_t* dst, void* cuda_stream) {
+    PT_REQUIRE(r && dst, "pt_read_bgra8_async: null argument");
+    cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : r->stream;
+    const size_t px = (size_t)r->pm.width * r->pm.height;
+    if (!r->d_bgra) { int rc = dev_alloc(&r->d_bgra, px * 4); if (rc != PT_OK) return rc; }
+    launch_to_bgra8(r->d_image, r->d_bgra, (uint32_t)px, st);
+    PT_CUDA_CHECK(cudaMemcpyAsync(dst, r->d_bgra, px * 4, cudaMemcpyDeviceToHost, st));
+    return PT_OK;
+}
+
+int pt_read_bgra8(PtRenderer* r, uint8_t* host_dst) {
+    int rc = pt_read_bgra8_async(r, host_dst, nullptr);
+    if (rc != PT_OK) return rc;
+    return pt_sync(r);
+}
+
+int pt_read_ids(PtRenderer* r, uint32_t* instance, uint32_t* primitive, uint32_t* triangle) {
+    PT_REQUIRE(r, "pt_read_ids: null renderer");
+    const size_t px = (size_t)r->pm.width * r->pm.height;
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    if (instance) PT_CUDA_CHECK(cudaMemcpy(instance, r->d_ids, px * 4, cudaMemcpyDeviceToHost));
+    if (primitive) PT_CUDA_CHECK(cudaMemcpy(primitive, r->d_ids + px, px * 4, cudaMemcpyDeviceToHost));
+    if (triangle) PT_CUDA_CHECK(cudaMemcpy(triangle, r->d_ids + 2 * px, px * 4, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+int pt_read_rgba32f_upscaled(PtRenderer* r, float* host_dst) {
+    PT_REQUIRE(r && host_dst, "pt_read_rgba32f_upscaled: null argument");
+    if (r->pm.width == r->full_w && r->pm.height == r->full_h) return pt_read_rgba32f(r, host_dst);
+    const size_t px = (size_t)r->full_w * r->full_h;
+    if (!r->d_upscaled) { int rc = dev_alloc(&r->d_upscaled, px * 4); if (rc != PT_OK) return rc; }
+    launch_upscale(r->d_image, r->pm.width, r->pm.height, r->d_upscaled, r->full_w, r->full_h, r->stream);
+    PT_CUDA_CHECK(cudaMemcpyAsync(host_dst, r->d_upscaled, px * 16, cudaMemcpyDeviceToHost, r->stream));
+    return pt_sync(r);
+}
+
+int pt_set_accumulate(PtRenderer* r, int enabled) {
+    PT_REQUIRE(r, "pt_set_accumulate: null renderer");
+    r->accumulate = enabled != 0;
+    return PT_OK;
+}
+
+int pt_reset_accum(PtRenderer* r) {
+    PT_REQUIRE(r, "pt_reset_accum: null renderer");
+    if (r->d_accum) PT_CUDA_CHECK(cudaMemsetAsync(r->d_accum, 0, (size_t)r->pm.width * r->pm.height * 16, r->stream));
+    r->accum_frames = 0;
+    return PT_OK;
+}
+
+int pt_device_accum(PtRenderer* r, float** device_ptr, uint32_t* frames) {
+    PT_REQUIRE(r && device_ptr, "pt_device_accum: null argument");
+    if (!r->d_accum) {
+        const size_t px = (size_t)r->pm.width * r->pm.height;
+        int rc = dev_alloc(&r->d_accum, px * 4);
+        if (rc != PT_OK) return rc;
+        PT_CUDA_CHECK(cudaMemsetAsync(r->d_accum, 0, px * 16, r->stream));
+    }
+    *device_ptr = r->d_accum;
+    if (frames) *frames = r->accum_frames;
+    return PT_OK;
+}
+
+int pt_read_accum_mean(PtRenderer* r, float* host_dst, uint32_t total_frames) {
+    PT_REQUIRE(r && host_dst && r->d_accum, "pt_read_accum_mean: accumulation is not enabled");
+    const size_t px = (size_t)r->pm.width * r->pm.height;
+    const uint32_t frames = total_frames ? total_frames : r->accum_frames;
+    PT_REQUIRE(frames > 0, "pt_read_accum_mean: no frames accumulated");
+    if (!r->d_upscaled || r->full_w * r->full_h < px) { cudaFree(r->d_upscaled); r->d_upscaled = nullptr; int rc = dev_alloc(&r->d_upscaled, std::max(px, (size_t)r->full_w * r->full_h) * 4); if (rc != PT_OK) return rc; }
+    launch_scale(r->d_accum, r->d_upscaled, (uint32_t)(px * 4), 1.0f / (float)frames, r->stream);
+    PT_CUDA_CHECK(cudaMemcpyAsync(host_dst, r->d_upscaled, px * 16, cudaMemcpyDeviceToHost, r->stream));
+    return pt_sync(r);
+}
+
+int pt_set_profiling(PtRenderer* r, int enabled) {
+    PT_REQUIRE(r, "pt_set_profiling: null renderer");
+    r->profiling = enabled != 0;
+    return PT_OK;
+}
+
+int pt_get_stats(PtRenderer* r, PtStats* out) {
+    PT_REQUIRE(r && out, "pt_get_stats: null argument");
+    std::memset(out, 0, sizeof(*out));
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    std::vector<uint32_t> q((size_t)r->max_iters + 2, 0);
+    PT_CUDA_CHECK(cudaMemcpy(q.data(), r->pb.qcount, q.size() * 4, cudaMemcpyDeviceToHost));
+    uint32_t its = 0;
+    for (uint32_t i = 0; i < r->last_iters; ++i) { out->rays_traced += q[i]; if (q[i]) its = i + 1; }
+    out->wavefront_iterations = its;
+    out->kernel_launches = r->last_launches;
+    if (r->profiling) {
+        for (size_t e = 0; e + 1 < r->events.size() && e / 2 < r->event_kind.size(); e += 2) {
+            float ms = 0.0f;
+            if (cudaEventElapsedTime(&ms, r->events[e], r->events[e + 1]) != cudaSuccess) { cudaGetLastError(); continue; }
+            const int k = r->event_kind[e / 2];
+            if (k == 0) out->ms_trace += ms; else if (k == 1) out->ms_shade += ms; else out->ms_other += ms;
+        }
+        out->ms_total = out->ms_trace + out->ms_shade + out->ms_other;
+    }
+    out->bvh_nodes = r->bvh.num_nodes8;
+    out->bvh_bytes = (uint64_t)r->bvh.num_nodes8 * sizeof(Bvh8Node) + (uint64_t)r->bvh.num_tris * sizeof(Bvh8Tri);
+    out->num_triangles = r->num_triangles;
+    out->ms_build = r->bvh.ms_build;
+    return PT_OK;
+}
+
+int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
+    PT_REQUIRE(r && (n == 0 || (rays && hits)), "pt_trace_rays: null argument");
+    PT_REQUIRE(n < 0xFFFFFF00ull, "pt_trace_rays: too many rays");
+    if (n == 0) return PT_OK;
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    RayRec* d_rays = nullptr; HitRec* d_hits = nullptr;
+    int rc;
+    if ((rc = dev_alloc(&d_rays, n)) != PT_OK) return rc;
+    if ((rc = dev_alloc(&d_hits, n)) != PT_OK) { cudaFree(d_rays); return rc; }
+    static_assert(sizeof(PtRay) == sizeof(RayRec), "PtRay layout");
+    cudaError_t e = cudaMemcpyAsync(d_rays, rays, n * sizeof(RayRec), cudaMemcpyHostToDevice, r->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(r->d_cursor, 0, 4, r->stream);
+    if (e == cudaSuccess) {
+        launch_trace_rays(r->scene, d_rays, (uint32_t)n, d_hits, r->trace_mode == TRACE_BVH2 ? TRACE_BVH2 : TRACE_BVH8, r->bvh.tlas2_count,
+                          r->bvh.tlas2_leaf_instance, r->d_cursor, r->num_sms, r->stream);
+        e = cudaGetLastError();
+    }
+    std::vector<HitRec> tmp(n);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(tmp.data(), d_hits, n * sizeof(HitRec), cudaMemcpyDeviceToHost, r->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
+    cudaFree(d_rays); cudaFree(d_hits);
+    if (e != cudaSuccess) { set_error(std::string("pt_trace_rays: ") + cudaGetErrorString(e)); return PT_ERR_CUDA; }
+    for (size_t i = 0; i < n; ++i) {
+        hits[i].t = tmp[i].t; hits[i].b1 = tmp[i].b1; hits[i].b2 = tmp[i].b2; hits[i].instance = tmp[i].instance;
+        hits[i].primitive_index = tmp[i].primitive_index; hits[i].triangle_index = tmp[i].triangle_index;
+    }
+    return PT_OK;
+}
+
+int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t* rays) {
+    PT_REQUIRE(r && r->have_last_cam, "pt_count_traversal: call pt_render first");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    PT_CUDA_CHECK(cudaMemsetAsync(r->pb.trav_counters, 0, 16, r->stream));
+    const bool prof = r->profiling, acc = r->accumulate;
+    r->profiling = false; r->accumulate = false;
+    const PtCamera cam = r->last_cam;
+    int rc = render_impl(r, &cam, r->stream, TRACE_BVH8_COUNT);
+    r->profiling = prof; r->accumulate = acc;
+    if (rc != PT_OK) return rc;
+    unsigned long long c[2] = {0, 0};
+    PT_CUDA_CHECK(cudaMemcpyAsync(c, r->pb.trav_counters, 16, cudaMemcpyDeviceToHost, r->stream));
+    PtStats st;
+    rc = pt_get_stats(r, &st);
+    if (rc != PT_OK) return rc;
+    if (nodes) *nodes = c[0];
+    if (tris) *tris = c[1];
+    if (rays) *rays = st.rays_traced;
+    return PT_OK;
+}
+
+int pt_ipc_export_image(PtRenderer* r, uint8_t handle[64]) {
+    PT_REQUIRE(r && handle, "pt_ipc_export_image: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
+    cudaIpcMemHandle_t h;
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    PT_CUDA_CHECK(cudaIpcGetMemHandle(&h, r->d_image));
+    std::memcpy(handle, &h, 64);
+    return PT_OK;
+}
+
+int pt_ipc_open_root_image(PtRenderer* r, const uint8_t handle[64]) {
+    PT_REQUIRE(r && handle, "pt_ipc_open_root_image: null argument");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    void* p = nullptr;
+    PT_CUDA_CHECK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    r->d_remote_image = static_cast<float*>(p);
+    return PT_OK;
+}
+
+}  // extern "C"

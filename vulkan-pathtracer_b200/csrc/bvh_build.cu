@@ -1,0 +1,600 @@
+// bvh_build.cu — GPU acceleration-structure builder: replaces the driver BLAS build
+// (src/RaytracingPass.zig:316-361,451-456) and the TLAS build (src/Tlas.zig:25-53,79-162).
+//
+// Pipeline per mesh (one BLAS per glTF mesh, one geometry per primitive, RaytracingPass.zig:277-352)
+// and once more over the instances (TLAS):
+//   gather leaves -> 63-bit Morton codes -> radix sort (cub) -> Karras 2012 hierarchy -> bottom-up
+//   refit -> top-down collapse into 8-wide nodes with greedy surface-area expansion, octant slot
+//   assignment and 8-bit quantised child boxes (80-byte nodes, Ylitie et al. 2017).
+#include <cub/device/device_radix_sort.cuh>
+
+#include <algorithm>
+#include <vector>
+
+#include "bvh_build.h"
+
+namespace pt {
+
+namespace {
+
+constexpr int kThreads = 256;
+inline int blocks_for(size_t n) { return (int)((n + kThreads - 1) / kThreads); }
+
+// ------------------------------------------------------------------ float atomics on bounds
+__device__ __forceinline__ void atomic_min_f(float* a, float v) {
+    if (v >= 0.0f) atomicMin(reinterpret_cast<int*>(a), __float_as_int(v));
+    else atomicMax(reinterpret_cast<unsigned int*>(a), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_f(float* a, float v) {
+    if (v >= 0.0f) atomicMax(reinterpret_cast<int*>(a), __float_as_int(v));
+    else atomicMin(reinterpret_cast<unsigned int*>(a), __float_as_uint(v));
+}
+
+__global__ void k_init_bounds(float* b) {
+    if (threadIdx.x < 3) b[threadIdx.x] = 3.0e38f;
+    else if (threadIdx.x < 6) b[threadIdx.x] = -3.0e38f;
+}
+
+// ------------------------------------------------------------------ leaves of a BLAS: triangles
+// One thread per triangle of the mesh, (geometry, triangle) order.  prim_prefix[k] = number of
+// triangles in primitives [first_prim, first_prim + k).
+__global__ void k_gather_tris(const uint8_t* __restrict__ blob, const PrimRec* __restrict__ prims, uint32_t first_prim,
+                              uint32_t num_prims, const uint32_t* __restrict__ prim_prefix, uint32_t n,
+                              Bvh8Tri* __restrict__ out, float* __restrict__ leaf_lo, float* __restrict__ leaf_hi,
+                              float* __restrict__ bounds) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // binary search: last k with prim_prefix[k] <= i
+    uint32_t lo = 0, hi = num_prims;
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (prim_prefix[mid] <= i) lo = mid; else hi = mid;
+    }
+    const uint32_t prim = first_prim + lo;
+    const uint32_t tri = i - prim_prefix[lo];
+    const PrimRec p = prims[prim];
+    uint32_t id[3];
+    if ((p.info & PT_UINT32_INDICES_MASK) == 0) {
+        const uint16_t* q = reinterpret_cast<const uint16_t*>(blob + p.indices_offset) + 3u * tri;
+        id[0] = q[0]; id[1] = q[1]; id[2] = q[2];
+    } else {
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(blob + p.indices_offset) + 3u * tri;
+        id[0] = q[0]; id[1] = q[1]; id[2] = q[2];
+    }
+    float v[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float* q = reinterpret_cast<const float*>(blob + p.positions_offset + 12u * id[k]);
+        v[k][0] = q[0]; v[k][1] = q[1]; v[k][2] = q[2];
+    }
+    Bvh8Tri t;
+    t.v0 = make_float4(v[0][0], v[0][1], v[0][2], __uint_as_float(prim));
+    t.v1 = make_float4(v[1][0], v[1][1], v[1][2], __uint_as_float(tri));
+    t.v2 = make_float4(v[2][0], v[2][1], v[2][2], 0.0f);
+    out[i] = t;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        float mn = fminf(v[0][a], fminf(v[1][a], v[2][a]));
+        float mx = fmaxf(v[0][a], fmaxf(v[1][a], v[2][a]));
+        leaf_lo[3 * (size_t)i + a] = mn;
+        leaf_hi[3 * (size_t)i + a] = mx;
+        atomic_min_f(bounds + a, mn);
+        atomic_max_f(bounds + 3 + a, mx);
+    }
+}
+
+// ------------------------------------------------------------------ leaves of the TLAS: instances
+// World box of instance `ids[i]`: the 8 corners of the BLAS root box through the 3x4 transform,
+// evaluated in double and padded (conservative).
+__global__ void k_instance_boxes(const PtInstance* __restrict__ inst, const uint32_t* __restrict__ ids, uint32_t n,
+                                 const float* __restrict__ mesh_bounds /* 6 per mesh */, float* __restrict__ leaf_lo,
+                                 float* __restrict__ leaf_hi, float* __restrict__ bounds) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const PtInstance& in = inst[ids[i]];
+    const float* mb = mesh_bounds + 6 * in.mesh_index;
+    float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (int c = 0; c < 8; ++c) {
+        double p[3] = {(c & 1) ? mb[3] : mb[0], (c & 2) ? mb[4] : mb[1], (c & 4) ? mb[5] : mb[2]};
+        for (int r = 0; r < 3; ++r) {
+            double w = (double)in.transform[4 * r] * p[0] + (double)in.transform[4 * r + 1] * p[1] +
+                       (double)in.transform[4 * r + 2] * p[2] + (double)in.transform[4 * r + 3];
+            lo[r] = fminf(lo[r], __double2float_rd(w));
+            hi[r] = fmaxf(hi[r], __double2float_ru(w));
+        }
+    }
+    for (int a = 0; a < 3; ++a) {
+        float pad = 1e-5f * fmaxf(fmaxf(fabsf(lo[a]), fabsf(hi[a])), hi[a] - lo[a]) + 1e-30f;
+        lo[a] -= pad; hi[a] += pad;
+        leaf_lo[3 * (size_t)i + a] = lo[a];
+        leaf_hi[3 * (size_t)i + a] = hi[a];
+        atomic_min_f(bounds + a, lo[a]);
+        atomic_max_f(bounds + 3 + a, hi[a]);
+    }
+}
+
+// ------------------------------------------------------------------ Morton codes
+__device__ __forceinline__ uint64_t expand21(uint32_t v) {
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void k_morton(const float* __restrict__ leaf_lo, const float* __restrict__ leaf_hi, uint32_t n,
+                         const float* __restrict__ bounds, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t q[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        float lo = bounds[a], ext = bounds[3 + a] - bounds[a];
+        float c = 0.5f * (leaf_lo[3 * (size_t)i + a] + leaf_hi[3 * (size_t)i + a]);
+        float u = ext > 0.0f ? (c - lo) / ext : 0.0f;
+        u = fminf(fmaxf(u, 0.0f), 1.0f);
+        q[a] = min(2097151u, (uint32_t)(u * 2097152.0f));
+    }
+    keys[i] = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+    vals[i] = i;
+}
+
+// ------------------------------------------------------------------ Karras 2012 radix tree
+__device__ __forceinline__ int delta(const uint64_t* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clzll((long long)(a ^ b));
+}
+
+// Internal node i in [0, n-1); leaves are referenced as (index | 0x80000000).
+__global__ void k_karras(const uint64_t* __restrict__ keys, int n, Bvh2Node* __restrict__ nodes,
+                         uint32_t* __restrict__ parent /* n-1 internal + n leaves */, uint2* __restrict__ range) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int first = min(i, j), last = max(i, j);
+    uint32_t left = (first == gamma) ? ((uint32_t)gamma | 0x80000000u) : (uint32_t)gamma;
+    uint32_t right = (last == gamma + 1) ? ((uint32_t)(gamma + 1) | 0x80000000u) : (uint32_t)(gamma + 1);
+    nodes[i].left = left;
+    nodes[i].right = right;
+    range[i] = make_uint2((uint32_t)first, (uint32_t)last);
+    // parent links: internal j -> slot j, leaf j -> slot (n-1) + j
+    parent[(left & 0x80000000u) ? (n - 1) + (left & 0x7fffffffu) : left] = (uint32_t)i;
+    parent[(right & 0x80000000u) ? (n - 1) + (right & 0x7fffffffu) : right] = (uint32_t)i;
+    if (i == 0) parent[0] = 0xFFFFFFFFu;
+}
+
+// Bottom-up refit: one thread per (sorted) leaf; the second thread to reach a node continues.
+__global__ void k_refit(int n, const uint32_t* __restrict__ order, const float* __restrict__ leaf_lo,
+                        const float* __restrict__ leaf_hi, Bvh2Node* __restrict__ nodes,
+                        const uint32_t* __restrict__ parent, uint32_t* __restrict__ flags) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t cur = parent[(n - 1) + i];
+    while (cur != 0xFFFFFFFFu) {
+        __threadfence();
+        if (atomicAdd(&flags[cur], 1u) == 0u) return;  // first arrival: sibling not ready
+        __threadfence();
+        float lo[3], hi[3];
+        const uint32_t ch[2] = {nodes[cur].left, nodes[cur].right};
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { lo[a] = 3.0e38f; hi[a] = -3.0e38f; }
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            if (ch[c] & 0x80000000u) {
+                size_t src = order[ch[c] & 0x7fffffffu];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], leaf_lo[3 * src + a]); hi[a] = fmaxf(hi[a], leaf_hi[3 * src + a]); }
+            } else {
+                // volatile: written by another thread of this launch
+                const volatile Bvh2Node* cn = nodes + ch[c];
+#pragma unroll
+                for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], cn->lo[a]); hi[a] = fmaxf(hi[a], cn->hi[a]); }
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { nodes[cur].lo[a] = lo[a]; nodes[cur].hi[a] = hi[a]; }
+        cur = parent[cur];
+    }
+}
+
+// n == 1: a single internal node with one leaf child.
+__global__ void k_single_leaf(const float* __restrict__ leaf_lo, const float* __restrict__ leaf_hi, Bvh2Node* nodes, uint2* range) {
+    for (int a = 0; a < 3; ++a) { nodes[0].lo[a] = leaf_lo[a]; nodes[0].hi[a] = leaf_hi[a]; }
+    nodes[0].left = 0x80000000u;
+    nodes[0].right = 0xFFFFFFFFu;
+    range[0] = make_uint2(0u, 0u);
+}
+
+// Morton-ordered triangle array for the BVH2 walker
+__global__ void k_reorder_tris(const Bvh8Tri* __restrict__ in, const uint32_t* __restrict__ order, uint32_t n, Bvh8Tri* __restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[order[i]];
+}
+
+__global__ void k_gather_u32(const uint32_t* __restrict__ in, const uint32_t* __restrict__ order, uint32_t n, uint32_t* __restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[order[i]];
+}
+
+// ------------------------------------------------------------------ BVH2 -> BVH8 collapse
+struct CollapseArgs {
+    const Bvh2Node* nodes2;     // this tree's internal nodes (local indices)
+    const uint2* range;         // leaf range per internal node
+    const uint32_t* order;      // sorted leaf -> source leaf
+    const float* leaf_lo;       // source leaf boxes
+    const float* leaf_hi;
+    uint32_t max_leaf;          // 3 for a BLAS (triangles per leaf slot), 1 for the TLAS
+    // outputs
+    Bvh8Node* nodes8;           // global node array
+    uint32_t* node_counter;     // global
+    uint32_t* tri_counter;      // global (BLAS: tris8 entries; TLAS: leaf-instance entries)
+    const Bvh8Tri* tris_sorted; // BLAS: Morton-ordered triangles of this mesh
+    Bvh8Tri* tris8;             // BLAS leaf triangle output (global)
+    const uint32_t* leaf_ids;   // TLAS: source leaf -> instance id
+    uint32_t* leaf_out;         // TLAS leaf output
+    // work queue
+    uint32_t* wq2;
+    uint32_t* wq8;
+    uint32_t* tail;
+    uint32_t capacity;
+    uint32_t* overflow;
+};
+
+struct CChild { uint32_t ref, first, count; float lo[3], hi[3]; };
+
+__device__ __forceinline__ CChild load_child(const CollapseArgs& a, uint32_t ref) {
+    CChild c;
+    c.ref = ref;
+    if (ref & 0x80000000u) {
+        uint32_t j = ref & 0x7fffffffu;
+        size_t src = a.order[j];
+        for (int k = 0; k < 3; ++k) { c.lo[k] = a.leaf_lo[3 * src + k]; c.hi[k] = a.leaf_hi[3 * src + k]; }
+        c.first = j; c.count = 1;
+    } else {
+        const Bvh2Node& n = a.nodes2[ref];
+        for (int k = 0; k < 3; ++k) { c.lo[k] = n.lo[k]; c.hi[k] = n.hi[k]; }
+        uint2 r = a.range[ref];
+        c.first = r.x; c.count = r.y - r.x + 1;
+    }
+    return c;
+}
+
+__device__ __forceinline__ float half_area(const CChild& c) {
+    float dx = c.hi[0] - c.lo[0], dy = c.hi[1] - c.lo[1], dz = c.hi[2] - c.lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
+    uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= end) return;
+    const uint32_t b2 = a.wq2[w], b8 = a.wq8[w];
+    CChild ch[8];
+    int cnt = 0;
+    {
+        const Bvh2Node& n = a.nodes2[b2];
+        ch[cnt++] = load_child(a, n.left);
+        if (n.right != 0xFFFFFFFFu) ch[cnt++] = load_child(a, n.right);
+    }
+    // greedy surface-area expansion up to 8 children
+    while (cnt < 8) {
+        int best = -1; float best_a = -1.0f;
+        for (int c = 0; c < cnt; ++c) {
+            if ((ch[c].ref & 0x80000000u) || ch[c].count <= a.max_leaf) continue;
+            float ar = half_area(ch[c]);
+            if (ar > best_a) { best_a = ar; best = c; }
+        }
+        if (best < 0) break;
+        const Bvh2Node& n = a.nodes2[ch[best].ref];
+        const uint32_t l = n.left, r = n.right;
+        ch[best] = load_child(a, l);
+        ch[cnt++] = load_child(a, r);
+    }
+    // node frame
+    float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (int c = 0; c < cnt; ++c)
+        for (int k = 0; k < 3; ++k) { lo[k] = fminf(lo[k], ch[c].lo[k]); hi[k] = fmaxf(hi[k], ch[c].hi[k]); }
+    float p[3], scale[3]; int ebits[3];
+    for (int k = 0; k < 3; ++k) {
+        float ext = hi[k] - lo[k];
+        float mag = fmaxf(fabsf(lo[k]), fabsf(hi[k]));
+        ext = fmaxf(fmaxf(ext, mag * 1.2e-4f), 1e-30f) * 1.01f;  // grid step >= 4 ulp(mag)
+        int e;
+        frexpf(ext / 250.0f, &e);           // 2^e >= ext/250
+        e = max(-125, min(126, e));
+        ebits[k] = e + 127;
+        scale[k] = __int_as_float(ebits[k] << 23);
+        p[k] = lo[k] - 0.5f * scale[k];     // origin strictly below every child lo (half a grid step)
+    }
+    // slot assignment: maximise sum of dot(child centroid - node centroid, octant direction of slot)
+    int slot_of[8]; bool slot_used[8]; bool assigned[8];
+    for (int s = 0; s < 8; ++s) { slot_used[s] = false; assigned[s] = false; slot_of[s] = -1; }
+    float nc[3] = {0.5f * (lo[0] + hi[0]), 0.5f * (lo[1] + hi[1]), 0.5f * (lo[2] + hi[2])};
+    for (int it = 0; it < cnt; ++it) {
+        float best = -3.0e38f; int bc = -1, bs = -1;
+        for (int c = 0; c < cnt; ++c) {
+            if (assigned[c]) continue;
+            float dx = 0.5f * (ch[c].lo[0] + ch[c].hi[0]) - nc[0];
+            float dy = 0.5f * (ch[c].lo[1] + ch[c].hi[1]) - nc[1];
+            float dz = 0.5f * (ch[c].lo[2] + ch[c].hi[2]) - nc[2];
+            for (int s = 0; s < 8; ++s) {
+                if (slot_used[s]) continue;
+                float cost = ((s & 1) ? dx : -dx) + ((s & 2) ? dy : -dy) + ((s & 4) ? dz : -dz);
+                if (cost > best) { best = cost; bc = c; bs = s; }
+            }
+        }
+        assigned[bc] = true; slot_used[bs] = true; slot_of[bc] = bs;
+    }
+    int child_in_slot[8];
+    for (int s = 0; s < 8; ++s) child_in_slot[s] = -1;
+    for (int c = 0; c < cnt; ++c) child_in_slot[slot_of[c]] = c;
+
+    // classify, allocate
+    uint32_t n_inner = 0, n_leaf_items = 0;
+    for (int s = 0; s < 8; ++s) {
+        int c = child_in_slot[s];
+        if (c < 0) continue;
+        bool leaf = (ch[c].ref & 0x80000000u) || ch[c].count <= a.max_leaf;
+        if (leaf) n_leaf_items += ch[c].count; else n_inner++;
+    }
+    uint32_t child_base = n_inner ? atomicAdd(a.node_counter, n_inner) : 0u;
+    uint32_t tri_base = n_leaf_items ? atomicAdd(a.tri_counter, n_leaf_items) : 0u;
+    uint32_t q_base = n_inner ? atomicAdd(a.tail, n_inner) : 0u;
+    if (n_inner && q_base + n_inner > a.capacity) { atomicExch(a.overflow, 1u); return; }
+
+    Bvh8Node out;
+    out.px = p[0]; out.py = p[1]; out.pz = p[2];
+    out.ex = (uint8_t)ebits[0]; out.ey = (uint8_t)ebits[1]; out.ez = (uint8_t)ebits[2];
+    out.child_base = child_base; out.tri_base = tri_base;
+    uint32_t imask = 0, inner_rank = 0, leaf_off = 0;
+    const float delta = 1.0f / 1024.0f;   // quantisation slack (fraction of a grid step)
+    for (int s = 0; s < 8; ++s) {
+        int c = child_in_slot[s];
+        if (c < 0) {
+            out.meta[s] = 0;
+            out.qlo_x[s] = out.qlo_y[s] = out.qlo_z[s] = 255;   // inverted box: never hit
+            out.qhi_x[s] = out.qhi_y[s] = out.qhi_z[s] = 0;
+            continue;
+        }
+        uint8_t ql[3], qh[3];
+        for (int k = 0; k < 3; ++k) {
+            float fl = floorf((ch[c].lo[k] - p[k]) / scale[k] - delta);
+            float fh = ceilf((ch[c].hi[k] - p[k]) / scale[k] + delta);
+            ql[k] = (uint8_t)fminf(fmaxf(fl, 0.0f), 255.0f);
+            qh[k] = (uint8_t)fminf(fmaxf(fh, 0.0f), 255.0f);
+        }
+        out.qlo_x[s] = ql[0]; out.qlo_y[s] = ql[1]; out.qlo_z[s] = ql[2];
+        out.qhi_x[s] = qh[0]; out.qhi_y[s] = qh[1]; out.qhi_z[s] = qh[2];
+        bool leaf = (ch[c].ref & 0x80000000u) || ch[c].count <= a.max_leaf;
+        if (!leaf) {
+            imask |= 1u << s;
+            out.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
+            a.wq2[q_base + inner_rank] = ch[c].ref;
+            a.wq8[q_base + inner_rank] = child_base + inner_rank;
+            inner_rank++;
+        } else {
+            const uint32_t k = ch[c].count;
+            const uint32_t unary = (k == 1) ? 1u : (k == 2 ? 3u : 7u);
+            out.meta[s] = (uint8_t)((unary << 5) | leaf_off);
+            for (uint32_t t = 0; t < k; ++t) {
+                if (a.tris8) a.tris8[tri_base + leaf_off + t] = a.tris_sorted[ch[c].first + t];
+                else a.leaf_out[tri_base + leaf_off + t] = a.leaf_ids[a.order[ch[c].first + t]];
+            }
+            leaf_off += k;
+        }
+    }
+    out.imask = (uint8_t)imask;
+    a.nodes8[b8] = out;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host orchestration
+void SceneBvh::release() {
+    cudaFree(nodes8); cudaFree(tris8); cudaFree(tlas_leaf_instance); cudaFree(nodes2); cudaFree(tris2);
+    cudaFree(tlas2); cudaFree(tlas2_leaf_instance); cudaFree(mesh_bounds);
+    nodes8 = nullptr; tris8 = nullptr; tlas_leaf_instance = nullptr; nodes2 = nullptr; tris2 = nullptr;
+    tlas2 = nullptr; tlas2_leaf_instance = nullptr; mesh_bounds = nullptr;
+}
+
+namespace {
+
+struct Scratch {
+    Bvh8Tri* tmp_tris = nullptr;
+    float *leaf_lo = nullptr, *leaf_hi = nullptr, *bounds = nullptr;
+    uint64_t *keys_in = nullptr, *keys_out = nullptr;
+    uint32_t *vals_in = nullptr, *vals_out = nullptr, *parent = nullptr, *flags = nullptr, *wq2 = nullptr, *wq8 = nullptr;
+    uint32_t* counters = nullptr;  // [0] node counter, [1] tri counter, [2] tlas leaf counter, [3] queue tail, [4] overflow
+    uint2* range = nullptr;
+    uint32_t* prim_prefix = nullptr;
+    void* cub_temp = nullptr;
+    size_t cub_bytes = 0;
+    void release() {
+        cudaFree(tmp_tris); cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(bounds); cudaFree(keys_in); cudaFree(keys_out);
+        cudaFree(vals_in); cudaFree(vals_out); cudaFree(parent); cudaFree(flags); cudaFree(wq2); cudaFree(wq8);
+        cudaFree(counters); cudaFree(range); cudaFree(prim_prefix); cudaFree(cub_temp);
+    }
+};
+
+// sort + hierarchy + refit for n leaves whose boxes are in s.leaf_lo/hi and whose bounds are in s.bounds
+int build_tree(Scratch& s, uint32_t n, Bvh2Node* nodes2_out, cudaStream_t st) {
+    k_morton<<<blocks_for(n), kThreads, 0, st>>>(s.leaf_lo, s.leaf_hi, n, s.bounds, s.keys_in, s.vals_in);
+    PT_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(s.cub_temp, s.cub_bytes, s.keys_in, s.keys_out, s.vals_in, s.vals_out, (int)n, 0, 63, st));
+    if (n == 1) {
+        // vals_out[0] == 0
+        k_single_leaf<<<1, 1, 0, st>>>(s.leaf_lo, s.leaf_hi, nodes2_out, s.range);
+    } else {
+        PT_CUDA_CHECK(cudaMemsetAsync(s.flags, 0, sizeof(uint32_t) * n, st));
+        k_karras<<<blocks_for(n - 1), kThreads, 0, st>>>(s.keys_out, (int)n, nodes2_out, s.parent, s.range);
+        k_refit<<<blocks_for(n), kThreads, 0, st>>>((int)n, s.vals_out, s.leaf_lo, s.leaf_hi, nodes2_out, s.parent, s.flags);
+    }
+    PT_CUDA_CHECK(cudaGetLastError());
+    return PT_OK;
+}
+
+// level-synchronous collapse of the tree just built; returns the BVH8 root index
+int collapse_tree(Scratch& s, CollapseArgs a, uint32_t n, uint32_t* root_out, cudaStream_t st) {
+    // allocate the root node
+    uint32_t root;
+    PT_CUDA_CHECK(cudaMemcpyAsync(&root, a.node_counter, 4, cudaMemcpyDeviceToHost, st));
+    PT_CUDA_CHECK(cudaStreamSynchronize(st));
+    uint32_t init[2] = {root + 1, 0};
+    PT_CUDA_CHECK(cudaMemcpyAsync(a.node_counter, &init[0], 4, cudaMemcpyHostToDevice, st));
+    uint32_t zero = 0, one = 1;
+    PT_CUDA_CHECK(cudaMemcpyAsync(s.wq2, &zero, 4, cudaMemcpyHostToDevice, st));
+    PT_CUDA_CHECK(cudaMemcpyAsync(s.wq8, &root, 4, cudaMemcpyHostToDevice, st));
+    PT_CUDA_CHECK(cudaMemcpyAsync(a.tail, &one, 4, cudaMemcpyHostToDevice, st));
+    uint32_t begin = 0, end = 1;
+    while (begin < end) {
+        k_collapse<<<(int)((end - begin + 63) / 64), 64, 0, st>>>(a, begin, end);
+        uint32_t tail_ovf[2];
+        PT_CUDA_CHECK(cudaMemcpyAsync(tail_ovf, a.tail, 8, cudaMemcpyDeviceToHost, st));
+        PT_CUDA_CHECK(cudaStreamSynchronize(st));
+        if (tail_ovf[1]) { set_error("BVH collapse work queue overflow"); return PT_ERR_CUDA; }
+        begin = end; end = tail_ovf[0];
+    }
+    (void)n;
+    *root_out = root;
+    return PT_OK;
+}
+
+}  // namespace
+
+int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::vector<PrimRec>& h_prims,
+                    const std::vector<PtMesh>& meshes, const PtInstance* d_instances,
+                    const std::vector<PtInstance>& h_instances, cudaStream_t st, SceneBvh* out) {
+    const size_t M = meshes.size();
+    out->tri_off.assign(M, 0); out->tri_count.assign(M, 0); out->blas_root8.assign(M, kInvalidId);
+    uint32_t total = 0, max_n = 1;
+    size_t max_prims = 1;
+    for (size_t m = 0; m < M; ++m) {
+        uint32_t n = 0;
+        for (uint32_t p = meshes[m].start; p < meshes[m].end; ++p) n += h_prims[p].triangle_count;
+        out->tri_off[m] = total; out->tri_count[m] = n; total += n;
+        max_n = std::max(max_n, n);
+        max_prims = std::max<size_t>(max_prims, meshes[m].end - meshes[m].start);
+    }
+    std::vector<uint32_t> valid_inst;
+    for (size_t i = 0; i < h_instances.size(); ++i)
+        if (h_instances[i].mesh_index < M && out->tri_count[h_instances[i].mesh_index] > 0) valid_inst.push_back((uint32_t)i);
+    const uint32_t NI = (uint32_t)valid_inst.size();
+    const uint32_t L = std::max(max_n, std::max(NI, 1u));
+    out->num_tris = total;
+    out->tlas2_count = NI;
+
+    cudaEvent_t ev0, ev1;
+    PT_CUDA_CHECK(cudaEventCreate(&ev0)); PT_CUDA_CHECK(cudaEventCreate(&ev1));
+    PT_CUDA_CHECK(cudaEventRecord(ev0, st));
+
+    Scratch s;
+    int rc = PT_OK;
+    auto fail = [&](int code) { s.release(); cudaEventDestroy(ev0); cudaEventDestroy(ev1); return code; };
+#define PT_TRY(expr) do { rc = (expr); if (rc != PT_OK) return fail(rc); } while (0)
+#define PT_CU(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return fail(PT_ERR_CUDA); } } while (0)
+    PT_CU(cudaMalloc(&s.tmp_tris, sizeof(Bvh8Tri) * L));
+    PT_CU(cudaMalloc(&s.leaf_lo, sizeof(float) * 3 * L)); PT_CU(cudaMalloc(&s.leaf_hi, sizeof(float) * 3 * L));
+    PT_CU(cudaMalloc(&s.bounds, sizeof(float) * 8));
+    PT_CU(cudaMalloc(&s.keys_in, 8 * (size_t)L)); PT_CU(cudaMalloc(&s.keys_out, 8 * (size_t)L));
+    PT_CU(cudaMalloc(&s.vals_in, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.vals_out, 4 * (size_t)L));
+    PT_CU(cudaMalloc(&s.parent, 4 * (size_t)(2 * L + 2))); PT_CU(cudaMalloc(&s.flags, 4 * (size_t)L));
+    PT_CU(cudaMalloc(&s.wq2, 4 * (size_t)(L + 8))); PT_CU(cudaMalloc(&s.wq8, 4 * (size_t)(L + 8)));
+    PT_CU(cudaMalloc(&s.counters, 4 * 8)); PT_CU(cudaMemsetAsync(s.counters, 0, 32, st));
+    PT_CU(cudaMalloc(&s.range, sizeof(uint2) * L));
+    PT_CU(cudaMalloc(&s.prim_prefix, 4 * (max_prims + 1)));
+    PT_CU(cub::DeviceRadixSort::SortPairs(nullptr, s.cub_bytes, s.keys_in, s.keys_out, s.vals_in, s.vals_out, (int)L, 0, 63, st));
+    PT_CU(cudaMalloc(&s.cub_temp, std::max<size_t>(s.cub_bytes, 16)));
+
+    const size_t cap_nodes = (size_t)total + M + NI + 8;
+    PT_CU(cudaMalloc(&out->nodes8, sizeof(Bvh8Node) * cap_nodes));
+    PT_CU(cudaMalloc(&out->tris8, sizeof(Bvh8Tri) * std::max(total, 1u)));
+    PT_CU(cudaMalloc(&out->tris2, sizeof(Bvh8Tri) * std::max(total, 1u)));
+    PT_CU(cudaMalloc(&out->nodes2, sizeof(Bvh2Node) * std::max(total, 1u)));
+    PT_CU(cudaMalloc(&out->tlas2, sizeof(Bvh2Node) * std::max(NI, 1u)));
+    PT_CU(cudaMalloc(&out->tlas_leaf_instance, 4 * (size_t)std::max(NI, 1u)));
+    PT_CU(cudaMalloc(&out->tlas2_leaf_instance, 4 * (size_t)std::max(NI, 1u)));
+    PT_CU(cudaMalloc(&out->mesh_bounds, sizeof(float) * 6 * std::max<size_t>(M, 1)));
+
+    uint32_t* node_counter = s.counters + 0;
+    uint32_t* tri_counter = s.counters + 1;
+    uint32_t* tlas_leaf_counter = s.counters + 2;
+    uint32_t* tail = s.counters + 4;      // [4] tail, [5] overflow (read together)
+    uint32_t* overflow = s.counters + 5;
+
+    // ---- one BLAS per mesh
+    for (size_t m = 0; m < M; ++m) {
+        const uint32_t n = out->tri_count[m];
+        if (n == 0) continue;
+        const uint32_t np = meshes[m].end - meshes[m].start;
+        std::vector<uint32_t> prefix(np + 1, 0);
+        for (uint32_t k = 0; k < np; ++k) prefix[k + 1] = prefix[k] + h_prims[meshes[m].start + k].triangle_count;
+        PT_CU(cudaMemcpyAsync(s.prim_prefix, prefix.data(), 4 * (np + 1), cudaMemcpyHostToDevice, st));
+        PT_CU(cudaStreamSynchronize(st));  // prefix is a stack temporary
+        k_init_bounds<<<1, 32, 0, st>>>(s.bounds);
+        k_gather_tris<<<blocks_for(n), kThreads, 0, st>>>(d_blob, d_prims, meshes[m].start, np, s.prim_prefix, n, s.tmp_tris,
+                                                           s.leaf_lo, s.leaf_hi, s.bounds);
+        PT_CU(cudaMemcpyAsync(out->mesh_bounds + 6 * m, s.bounds, sizeof(float) * 6, cudaMemcpyDeviceToDevice, st));
+        Bvh2Node* n2 = out->nodes2 + out->tri_off[m];
+        PT_TRY(build_tree(s, n, n2, st));
+        k_reorder_tris<<<blocks_for(n), kThreads, 0, st>>>(s.tmp_tris, s.vals_out, n, out->tris2 + out->tri_off[m]);
+        CollapseArgs a{};
+        a.nodes2 = n2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
+        a.max_leaf = 3; a.nodes8 = out->nodes8; a.node_counter = node_counter; a.tri_counter = tri_counter;
+        a.tris_sorted = out->tris2 + out->tri_off[m]; a.tris8 = out->tris8; a.leaf_ids = nullptr; a.leaf_out = nullptr;
+        a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = tail; a.capacity = L + 8; a.overflow = overflow;
+        PT_TRY(collapse_tree(s, a, n, &out->blas_root8[m], st));
+    }
+    // ---- TLAS over the instances that reference a non-empty mesh
+    if (NI > 0) {
+        PT_CU(cudaMemcpyAsync(s.vals_in, valid_inst.data(), 4 * (size_t)NI, cudaMemcpyHostToDevice, st));
+        PT_CU(cudaStreamSynchronize(st));
+        // leaf ids live in flags' neighbour: reuse wq buffers is unsafe, keep a dedicated copy in tlas2_leaf_instance (unsorted for now)
+        uint32_t* ids_unsorted = nullptr;
+        PT_CU(cudaMalloc(&ids_unsorted, 4 * (size_t)NI));
+        PT_CU(cudaMemcpyAsync(ids_unsorted, s.vals_in, 4 * (size_t)NI, cudaMemcpyDeviceToDevice, st));
+        k_init_bounds<<<1, 32, 0, st>>>(s.bounds);
+        k_instance_boxes<<<blocks_for(NI), kThreads, 0, st>>>(d_instances, ids_unsorted, NI, out->mesh_bounds, s.leaf_lo, s.leaf_hi, s.bounds);
+        rc = build_tree(s, NI, out->tlas2, st);
+        if (rc == PT_OK) {
+            // sorted leaf j -> instance id
+            k_gather_u32<<<blocks_for(NI), kThreads, 0, st>>>(ids_unsorted, s.vals_out, NI, out->tlas2_leaf_instance);
+            CollapseArgs a{};
+            a.nodes2 = out->tlas2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
+            a.max_leaf = 1; a.nodes8 = out->nodes8; a.node_counter = node_counter; a.tri_counter = tlas_leaf_counter;
+            a.tris_sorted = nullptr; a.tris8 = nullptr; a.leaf_ids = ids_unsorted; a.leaf_out = out->tlas_leaf_instance;
+            a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = tail; a.capacity = L + 8; a.overflow = overflow;
+            rc = collapse_tree(s, a, NI, &out->tlas_root8, st);
+        }
+        cudaStreamSynchronize(st);
+        cudaFree(ids_unsorted);
+        if (rc != PT_OK) return fail(rc);
+    }
+    PT_CU(cudaMemcpyAsync(&out->num_nodes8, node_counter, 4, cudaMemcpyDeviceToHost, st));
+    PT_CU(cudaEventRecord(ev1, st));
+    PT_CU(cudaStreamSynchronize(st));
+    cudaEventElapsedTime(&out->ms_build, ev0, ev1);
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    s.release();
+#undef PT_TRY
+#undef PT_CU
+    return PT_OK;
+}
+
+}  // namespace pt

@@ -1,0 +1,332 @@
+// render.cu — the wavefront trace loop: K-raygen, K-trace, K-shade (+ fused queue compaction and
+// pixel accumulation) and the image post-processing kernels.  Restates
+// src/shaders/ray_gen.rgen:33-105 as a per-pixel state machine driven by ray queues.
+#include "render.h"
+#include "shade.cuh"
+#include "trace.cuh"
+
+namespace pt {
+
+namespace {
+
+constexpr int kTraceThreads = 128;
+constexpr int kShadeThreads = 128;
+
+PT_D bool slot_to_pixel(const PixelMap& pm, uint32_t slot, uint32_t& x, uint32_t& y) {
+    const uint32_t k = slot >> 8, within = slot & 255u;
+    const uint32_t tile = pm.rank + k * pm.world;
+    const uint32_t tx = tile % pm.tiles_x, ty = tile / pm.tiles_x;
+    const uint32_t w = within >> 5, l = within & 31u;
+    x = tx * 32u + (w & 3u) * 8u + (l & 7u);
+    y = ty * 8u + (w >> 2) * 4u + (l >> 3);
+    return ty < pm.tiles_y && x < pm.width && y < pm.height;
+}
+
+// ray_gen.rgen:34-36,48
+PT_D V3 primary_direction(const PtCamera& cam, uint32_t x, uint32_t y, uint32_t W, uint32_t H) {
+    const float px = (float)x + 0.5f, py = (float)y + 0.5f;
+    const float u = px / (float)W, v = py / (float)H;
+    const float dx = u * 2.0f - 1.0f, dy = v * 2.0f - 1.0f;
+    const V3 hor = v3(cam.horizontal[0], cam.horizontal[1], cam.horizontal[2]);
+    const V3 ver = v3(cam.vertical[0], cam.vertical[1], cam.vertical[2]);
+    const V3 fwd = v3(cam.forward[0], cam.forward[1], cam.forward[2]);
+    return normalize(fwd + hor * dx - ver * dy);
+}
+
+// warp-aggregated append of `slot` to a queue; must be reached by all 32 lanes of the warp
+PT_D void queue_push(uint32_t* __restrict__ queue, uint32_t* __restrict__ count, bool pred, uint32_t slot) {
+    const uint32_t active = 0xffffffffu;
+    const uint32_t mask = __ballot_sync(active, pred);
+    if (mask == 0u) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    const int leader = __ffs((int)mask) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(count, (uint32_t)__popc(mask));
+    base = __shfl_sync(active, base, leader);
+    if (pred) queue[base + __popc(mask & ((1u << lane) - 1u))] = slot;
+}
+
+PT_D void write_pixel(const FrameParams& fp, uint32_t W, uint32_t x, uint32_t y, V3 final_color) {
+    const float s = (float)fp.num_samples;
+    const V3 c = final_color / s;                                       // ray_gen.rgen:102
+    reinterpret_cast<float4*>(fp.image)[(size_t)y * W + x] = make_float4(c.x, c.y, c.z, 1.0f);  // :104
+}
+
+// ------------------------------------------------------------------ K-raygen  (ray_gen.rgen:34-48)
+__global__ void __launch_bounds__(256) k_raygen(PixelMap pm, PathBuffers pb, FrameParams fp) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t x = 0, y = 0;
+    bool valid = slot < pm.num_slots && slot_to_pixel(pm, slot, x, y);
+    bool live = valid;
+    if (valid) {
+        if (fp.num_samples == 0u || fp.num_bounces == 0u) {
+            write_pixel(fp, pm.width, x, y, v3s(0.0f));
+            const size_t pi = (size_t)y * pm.width + x;
+            fp.id_inst[pi] = kInvalidId; fp.id_prim[pi] = kInvalidId; fp.id_tri[pi] = kInvalidId;
+            live = false;
+        } else {
+            const U2 seed = prng_seed(x, y, fp.cam.frame_count);            // :41
+            const V3 d = primary_direction(fp.cam, x, y, pm.width, pm.height);
+            pb.ray_o[slot] = make_float4(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2], 0.001f);   // :38,47
+            pb.ray_d[slot] = make_float4(d.x, d.y, d.z, 10000.0f);                                               // :39,48
+            pb.atten_sx[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(seed.x));                          // :46
+            pb.color_sy[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(seed.y));                          // :45
+            pb.final_sb[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0u));                              // :43
+        }
+    }
+    queue_push(pb.queue[0], pb.qcount + 0, live, slot);
+}
+
+// ------------------------------------------------------------------ K-trace
+// Persistent warps; every warp fetches batches of 32 queue entries through one atomic.
+template <int MODE>
+__global__ void __launch_bounds__(kTraceThreads) k_trace(DeviceScene sc, PathBuffers pb, uint32_t iter, uint32_t tlas2_count,
+                                                         const uint32_t* __restrict__ tlas2_leaf_instance) {
+    const uint32_t n = pb.qcount[iter];
+    const uint32_t* __restrict__ queue = pb.queue[iter & 1u];
+    uint32_t* cursor = pb.trace_next + iter;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t cnt_nodes = 0, cnt_tris = 0;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const uint32_t idx = base + lane;
+        if (idx < n) {
+            const uint32_t slot = queue[idx];
+            const float4 ro = pb.ray_o[slot], rd = pb.ray_d[slot];
+            Hit h;
+            if (MODE == TRACE_BVH2) trace_bvh2(sc, tlas2_count, tlas2_leaf_instance, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h);
+            else if (MODE == TRACE_BVH8_COUNT) trace_bvh8<true>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, &cnt_nodes, &cnt_tris);
+            else trace_bvh8<false>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, nullptr, nullptr);
+            pb.hit_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.inst));
+            pb.hit_b[slot] = make_uint2(h.prim, h.tri);
+        }
+    }
+    if (MODE == TRACE_BVH8_COUNT) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(pb.trav_counters), (unsigned long long)cnt_nodes);
+        atomicAdd(reinterpret_cast<unsigned long long*>(pb.trav_counters) + 1, (unsigned long long)cnt_tris);
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kTraceThreads) k_trace_rays(DeviceScene sc, const RayRec* __restrict__ rays, uint32_t n,
+                                                              HitRec* __restrict__ hits, uint32_t tlas2_count,
+                                                              const uint32_t* __restrict__ tlas2_leaf_instance, uint32_t* cursor) {
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const uint32_t idx = base + lane;
+        if (idx < n) {
+            const RayRec r = rays[idx];
+            Hit h;
+            if (MODE == TRACE_BVH2) trace_bvh2(sc, tlas2_count, tlas2_leaf_instance, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax, h);
+            else trace_bvh8<false>(sc, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax, h, nullptr, nullptr);
+            HitRec o;
+            o.t = h.t; o.b1 = h.b1; o.b2 = h.b2; o.instance = h.inst; o.primitive_index = h.prim; o.triangle_index = h.tri;
+            o._pad0 = 0; o._pad1 = 0;
+            hits[idx] = o;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ K-shade
+// One thread per live path.  Consumes the hit of segment (sample s, bounce j), runs the body of the
+// bounce loop (ray_gen.rgen:65-97), and either emits the next ray (appended to the next queue) or
+// ends the sample; a finished sample restarts from the cached primary hit (every sample of a pixel
+// shoots the same primary ray, quirk Q1) until NUM_SAMPLES are done, then the pixel is stored.
+__global__ void __launch_bounds__(kShadeThreads) k_shade(DeviceScene sc, PixelMap pm, PathBuffers pb, FrameParams fp, uint32_t iter) {
+    const uint32_t n = pb.qcount[iter];
+    const uint32_t* __restrict__ qin = pb.queue[iter & 1u];
+    uint32_t* __restrict__ qout = pb.queue[(iter + 1u) & 1u];
+    uint32_t* qout_count = pb.qcount + iter + 1u;
+    const uint32_t S = fp.num_samples, B = fp.num_bounces;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    // whole warps iterate together (queue_push is warp-collective over the active mask)
+    for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += stride) {
+        const uint32_t idx = base + (threadIdx.x & 31u);
+        bool emit = false;
+        uint32_t slot = 0;
+        if (idx < n) {
+            slot = qin[idx];
+            uint32_t x, y;
+            slot_to_pixel(pm, slot, x, y);
+            const float4 a4 = pb.atten_sx[slot], c4 = pb.color_sy[slot], f4 = pb.final_sb[slot];
+            V3 atten = v3(a4.x, a4.y, a4.z), color = v3(c4.x, c4.y, c4.z), final_color = v3(f4.x, f4.y, f4.z);
+            U2 seed; seed.x = __float_as_uint(a4.w); seed.y = __float_as_uint(c4.w);
+            uint32_t s = __float_as_uint(f4.w) & 0xffffu, j = __float_as_uint(f4.w) >> 16;
+            const float4 ro = pb.ray_o[slot], rd = pb.ray_d[slot];
+            V3 origin = v3(ro.x, ro.y, ro.z), direction = v3(rd.x, rd.y, rd.z);
+            HitRec h;
+            {
+                const float4 ha = pb.hit_a[slot]; const uint2 hb = pb.hit_b[slot];
+                h.t = ha.x; h.b1 = ha.y; h.b2 = ha.z; h.instance = __float_as_uint(ha.w);
+                h.primitive_index = hb.x; h.triangle_index = hb.y;
+            }
+            if (s == 0u && j == 0u) {
+                // first segment of the pixel: this is the primary hit
+                pb.prim_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.instance));
+                pb.prim_b[slot] = make_uint2(h.primitive_index, h.triangle_index);
+                const size_t pi = (size_t)y * pm.width + x;
+                fp.id_inst[pi] = h.instance; fp.id_prim[pi] = h.primitive_index; fp.id_tri[pi] = h.triangle_index;
+            }
+            for (;;) {
+                bool end_sample = false;
+                if (h.t == kMissT) {                                                        // :65-70
+                    const float t = 0.5f * (direction.y + 1.0f);
+                    color = color + atten * mix(v3(1.0f, 1.0f, 1.0f), v3(0.5f, 0.7f, 1.0f), t);
+                    end_sample = true;
+                } else {
+                    const TriangleData td = get_triangle_data(sc, h);                       // :72
+                    const MaterialData md = get_material_data(sc, td);                      // :73
+                    color = color + md.emissive * 10.0f * atten;                            // :75
+                    if (j + 1u < B) {                                                       // :77
+                        ShadingInfo si;
+                        si.out_dir = -direction;                                            // :79
+                        si.normal = md.normal;                                              // :80
+                        si.lambert_out = dot(si.normal, si.out_dir);                        // :81
+                        const V3 alb = v3(md.albedo.x, md.albedo.y, md.albedo.z);
+                        si.fresnel_0 = mix(v3s(0.02f), alb, md.metallic);                   // :82
+                        si.diffuse_albedo = alb - md.metallic * alb;                        // :83
+                        si.roughness = gmax(0.006f, md.roughness);                          // :84
+                        origin = origin + h.t * direction + td.geometry_normal * 0.00001f;  // :86
+                        direction = sample_brdf(si, pcg2d(seed));                           // :87
+                        const float density = get_brdf_density(si, direction);              // :89
+                        const float lambert_in = dot(si.normal, direction);                 // :90
+                        if (lambert_in <= 0.0f) {                                           // :91-93
+                            end_sample = true;
+                        } else {
+                            atten = atten * (brdf(si, direction) * lambert_in / density);   // :95
+                            ++j;
+                            emit = true;
+                        }
+                    } else {
+                        end_sample = true;   // last segment: loop bound reached (:49)
+                    }
+                }
+                if (!end_sample) break;      // next segment must be traced
+                final_color = final_color + color;                                          // :99
+                ++s;
+                if (s == S) { write_pixel(fp, pm.width, x, y, final_color); break; }        // :102-104
+                // next sample (:44-48)
+                color = v3s(0.0f); atten = v3s(1.0f); j = 0u;
+                origin = v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]);
+                direction = primary_direction(fp.cam, x, y, pm.width, pm.height);
+                if (fp.flags & PT_FLAG_NO_PRIMARY_REUSE) { emit = true; break; }
+                const float4 ha = pb.prim_a[slot]; const uint2 hb = pb.prim_b[slot];
+                h.t = ha.x; h.b1 = ha.y; h.b2 = ha.z; h.instance = __float_as_uint(ha.w);
+                h.primitive_index = hb.x; h.triangle_index = hb.y;
+            }
+            if (emit) {
+                pb.ray_o[slot] = make_float4(origin.x, origin.y, origin.z, 0.001f);
+                pb.ray_d[slot] = make_float4(direction.x, direction.y, direction.z, 10000.0f);
+                pb.atten_sx[slot] = make_float4(atten.x, atten.y, atten.z, __uint_as_float(seed.x));
+                pb.color_sy[slot] = make_float4(color.x, color.y, color.z, __uint_as_float(seed.y));
+                pb.final_sb[slot] = make_float4(final_color.x, final_color.y, final_color.z, __uint_as_float(s | (j << 16)));
+            }
+        }
+        queue_push(qout, qout_count, emit, slot);
+    }
+}
+
+// ------------------------------------------------------------------ post-processing
+// fp32 RGBA -> b8g8r8a8_unorm as the reference's storage image does (Swapchain.zig:115-118):
+// NaN -> 0, clamp to [0,1], round to nearest.
+__global__ void k_to_bgra8(const float4* __restrict__ in, uchar4* __restrict__ out, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 v = in[i];
+    auto q = [](float f) -> unsigned char {
+        if (!(f == f)) f = 0.0f;
+        f = fminf(fmaxf(f, 0.0f), 1.0f);
+        return (unsigned char)(f * 255.0f + 0.5f);
+    };
+    out[i] = make_uchar4(q(v.z), q(v.y), q(v.x), q(v.w));
+}
+
+// nearest up-scale (the blit at RaytracingPass.zig:599-635)
+__global__ void k_upscale(const float4* __restrict__ src, uint32_t sw, uint32_t sh, float4* __restrict__ dst, uint32_t dw, uint32_t dh) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= dw * dh) return;
+    const uint32_t x = i % dw, y = i / dw;
+    const uint32_t sx = min(sw - 1u, (uint32_t)(((uint64_t)x * sw) / dw)), sy = min(sh - 1u, (uint32_t)(((uint64_t)y * sh) / dh));
+    dst[i] = src[(size_t)sy * sw + sx];
+}
+
+__global__ void k_accumulate(const float4* __restrict__ frame, float4* __restrict__ accum, uint32_t n4) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const float4 a = accum[i], f = frame[i];
+    accum[i] = make_float4(a.x + f.x, a.y + f.y, a.z + f.z, a.w + f.w);
+}
+
+__global__ void k_scale(const float4* __restrict__ in, float4* __restrict__ out, uint32_t n4, float s) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const float4 a = in[i];
+    out[i] = make_float4(a.x * s, a.y * s, a.z * s, a.w * s);
+}
+
+template <typename K>
+int persistent_blocks(K kernel, int threads, int num_sms) {
+    int per_sm = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0);
+    if (per_sm < 1) per_sm = 1;
+    return per_sm * num_sms;
+}
+
+}  // namespace
+
+void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st) {
+    if (pm.num_slots == 0) return;
+    k_raygen<<<(pm.num_slots + 255) / 256, 256, 0, st>>>(pm, pb, fp);
+}
+
+void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
+                  const uint32_t* tlas2_leaf_instance, int num_sms, cudaStream_t st) {
+    static int blocks[3] = {0, 0, 0};
+    if (!blocks[0]) {
+        blocks[0] = persistent_blocks(k_trace<TRACE_BVH8>, kTraceThreads, num_sms);
+        blocks[1] = persistent_blocks(k_trace<TRACE_BVH2>, kTraceThreads, num_sms);
+        blocks[2] = persistent_blocks(k_trace<TRACE_BVH8_COUNT>, kTraceThreads, num_sms);
+    }
+    if (mode == TRACE_BVH2) k_trace<TRACE_BVH2><<<blocks[1], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
+    else if (mode == TRACE_BVH8_COUNT) k_trace<TRACE_BVH8_COUNT><<<blocks[2], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
+    else k_trace<TRACE_BVH8><<<blocks[0], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
+}
+
+void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
+                  int num_sms, cudaStream_t st) {
+    static int blocks = 0;
+    if (!blocks) blocks = persistent_blocks(k_shade, kShadeThreads, num_sms);
+    k_shade<<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+}
+
+void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
+                       uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, int num_sms, cudaStream_t st) {
+    const int blocks = num_sms * 4;
+    if (mode == TRACE_BVH2) k_trace_rays<TRACE_BVH2><<<blocks, kTraceThreads, 0, st>>>(sc, rays, n, hits, tlas2_count, tlas2_leaf_instance, cursor);
+    else k_trace_rays<TRACE_BVH8><<<blocks, kTraceThreads, 0, st>>>(sc, rays, n, hits, tlas2_count, tlas2_leaf_instance, cursor);
+}
+
+void launch_to_bgra8(const float* rgba, uint8_t* bgra, uint32_t n_pixels, cudaStream_t st) {
+    if (n_pixels) k_to_bgra8<<<(n_pixels + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(rgba), reinterpret_cast<uchar4*>(bgra), n_pixels);
+}
+void launch_upscale(const float* src, uint32_t sw, uint32_t sh, float* dst, uint32_t dw, uint32_t dh, cudaStream_t st) {
+    const uint32_t n = dw * dh;
+    if (n) k_upscale<<<(n + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(src), sw, sh, reinterpret_cast<float4*>(dst), dw, dh);
+}
+void launch_accumulate(const float* frame, float* accum, uint32_t n_floats, cudaStream_t st) {
+    const uint32_t n4 = n_floats / 4;
+    if (n4) k_accumulate<<<(n4 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(frame), reinterpret_cast<float4*>(accum), n4);
+}
+void launch_scale(const float* accum, float* out, uint32_t n_floats, float scale, cudaStream_t st) {
+    const uint32_t n4 = n_floats / 4;
+    if (n4) k_scale<<<(n4 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(accum), reinterpret_cast<float4*>(out), n4, scale);
+}
+
+}  // namespace pt

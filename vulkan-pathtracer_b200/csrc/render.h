@@ -1,0 +1,59 @@
+// render.h — wavefront frame state and kernel launchers (render.cu).
+#pragma once
+#include "pt_internal.h"
+
+namespace pt {
+
+// Tile-ordered pixel slots: tile = 32x8 pixels, 8 warps per tile, each warp an 8x4 block (coherent
+// rays per warp).  Slot i of this rank -> owned tile (rank + (i/256)*world).
+struct PixelMap {
+    uint32_t width, height;       // render extent
+    uint32_t tiles_x, tiles_y;
+    uint32_t rank, world;         // world == 1: every tile is owned
+    uint32_t num_slots;           // owned tiles * 256
+};
+
+// Per-slot path state in HBM (SoA of 16-byte records).
+struct PathBuffers {
+    float4* ray_o;       // origin.xyz, tmin
+    float4* ray_d;       // direction.xyz, tmax
+    float4* hit_a;       // t, b1, b2, instance (bits)
+    uint2* hit_b;        // primitive_index, triangle_index
+    float4* prim_a;      // cached primary hit (reused for every sample, quirk Q1)
+    uint2* prim_b;
+    float4* atten_sx;    // atten.rgb, seed.x (bits)
+    float4* color_sy;    // color.rgb, seed.y (bits)
+    float4* final_sb;    // final_color.rgb, sample | bounce << 16 (bits)
+    uint32_t* queue[2];  // slot indices of live paths, double buffered
+    uint32_t* qcount;    // [max_iters + 1] entries of queue k (zeroed per frame)
+    uint32_t* trace_next;// [max_iters] dynamic-fetch cursors of the persistent trace kernel
+    uint32_t* trav_counters;  // [2] nodes, tris (counting walker)
+};
+
+struct FrameParams {
+    PtCamera cam;
+    uint32_t num_samples, num_bounces;
+    uint32_t flags;
+    float* image;        // W*H*4 fp32 (full image; non-owned pixels untouched)
+    uint32_t* id_inst;   // W*H each
+    uint32_t* id_prim;
+    uint32_t* id_tri;
+};
+
+enum TraceMode { TRACE_BVH8 = 0, TRACE_BVH2 = 1, TRACE_BVH8_COUNT = 2 };
+
+void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st);
+void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
+                  const uint32_t* tlas2_leaf_instance, int num_sms, cudaStream_t st);
+void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
+                  int num_sms, cudaStream_t st);
+// standalone closest-hit queries (pt_trace_rays)
+void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
+                       uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, int num_sms, cudaStream_t st);
+// image post-processing
+void launch_to_bgra8(const float* rgba, uint8_t* bgra, uint32_t n_pixels, cudaStream_t st);
+void launch_upscale(const float* src, uint32_t sw, uint32_t sh, float* dst, uint32_t dw, uint32_t dh, cudaStream_t st);
+void launch_accumulate(const float* frame, float* accum, uint32_t n_floats, cudaStream_t st);
+void launch_scale(const float* accum, float* out, uint32_t n_floats, float scale, cudaStream_t st);
+
+}  // namespace pt
