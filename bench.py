@@ -1,0 +1,314 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the trace loop (BASELINE.json metric: Mrays/s & spp/s at 1080p, 2 bounces).
+
+    python bench.py --gpus N --steps K --warmup W        (N>1: launched under torch.distributed.run)
+    python bench.py --impl reference ...                 (CPU oracle on the host cores)
+
+A step = one frame of the hot path (raygen -> [trace -> shade]* -> image) of the synthetic
+Sponza-scale scene (config C2: ~260 k triangles, 25 textured PBR materials, 1920x1080, 1 spp,
+2 ray segments) with frame_count = step index.  At N>1 every rank renders its own frame_count
+(sample-range partitioning: rank r renders frames r, r+N, ...) and the per-rank images are combined
+with an NCCL reduce(sum) to rank 0 inside the timed region (weak scaling).
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "vulkan-pathtracer_b200"))
+
+from tools import scene as S  # noqa: E402
+
+WORKLOADS = {
+    # name: (builder kwargs, W, H, spp, segments)
+    "c1": ("cornell", 512, 512, 1, 2),
+    "c2": ("sponza_scale", 1920, 1080, 1, 2),
+    "c3": ("sponza_scale", 3840, 2160, 64, 8),
+    "c4": ("instanced", 1920, 1080, 4, 4),
+    "c5": ("heavy_material", 1920, 1080, 16, 6),
+}
+WORKLOAD_DESC = {
+    "c1": "C1 synthetic Cornell box 512x512 1spp 2 segments",
+    "c2": "C2 synthetic Sponza-scale glTF (~260k tris, 25 textured PBR materials) 1920x1080 1spp 2 segments",
+    "c3": "C3 synthetic Sponza-scale 3840x2160 64spp 8 segments",
+    "c4": "C4 1000 instances x 10k-tri mesh 1920x1080 4spp 4 segments",
+    "c5": "C5 ~1M tris, 4096^2 textures, 1920x1080 16spp 6 segments",
+}
+
+
+def build_scene(name):
+    t = time.time()
+    sb = getattr(S, WORKLOADS[name][0])(1234)
+    ps = sb.pack()
+    return ps, time.time() - t
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.gpu_index = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path is unavailable (Zig +
+    Vulkan) so the CPU oracle (kind "port") is timed on all host threads."""
+    if rank != 0:
+        return 0
+    from oracle import orc
+    name = args.workload
+    ps, _ = build_scene(name)
+    _, W, H, spp, seg = WORKLOADS[name]
+    osc = orc.OracleScene(ps, True)
+    cfg = S.render_config(W, H, 1, seg)   # 1 spp per step (Mrays/s is a rate)
+    nt = orc.lib().orc_hardware_threads()
+    # bounded sample: every `row_step`-th scanline so that one step stays around a few CPU-seconds per thread
+    row_step = max(1, int(round((W * H * seg / 2.0e6) / max(1, nt) / 2.0)))
+    rays_total, t_total = 0, 0.0
+    for i in range(args.warmup + args.steps):
+        cam = S.camera_default(W, H, i)
+        t0 = time.perf_counter()
+        _, rays = osc.render_rows(cfg, cam, 0, H, row_step, nt)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            rays_total += rays; t_total += dt
+    mrays = rays_total / t_total / 1e6
+    rows = len(range(0, H, row_step))
+    frac = rows / H
+    sample = f"{rows} of {H} scanlines (every {row_step}th) of {WORKLOAD_DESC[name]} at 1 spp per step, {nt} threads"
+    line = {"impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps / frac, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_DESC[name], "note": "reference Vulkan/lavapipe path unavailable on this box; CPU oracle (C++ restatement of the shaders + binned-SAH BVH2) timed instead; ms_per_step extrapolated to the full frame"},
+            "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": nt, "kind": "port", "sample": sample},
+            "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "spp_per_s": (args.steps * frac) / t_total}
+    print(json.dumps(line))
+    return 0
+
+
+class DevArray:
+    """__cuda_array_interface__ view of a device buffer owned by the renderer."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-l2-flush", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    import b200pt
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the b200 arm has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    name = args.workload
+    _, W, H, spp, seg = WORKLOADS[name]
+    ps, t_gen = build_scene(name)
+    t0 = time.time()
+    r = b200pt.Renderer(ps, W, H, spp, seg, device=local_rank, flags=args.flags)
+    t_create = time.time() - t0
+    st0 = r.stats()
+    # a non-default torch stream: its handle is passed to pt_render so that torch.cuda.Event timing and
+    # NCCL ordering see the renderer's kernels (the NULL handle would mean "the renderer's own stream")
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    sp = C.c_void_p(stream.cuda_stream)
+    assert sp.value, "expected a non-default CUDA stream"
+    img_t = torch.as_tensor(DevArray(r.device_image_ptr(), (H, W, 4)), device=f"cuda:{local_rank}")
+    flush = None if args.no_l2_flush else torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")
+    total_steps = args.warmup + args.steps
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def frame_of(i):
+        return i * world + rank
+
+    def step(i):
+        r.record(S.camera_default(W, H, frame_of(i)), sp)
+        if world > 1:
+            dist.reduce(img_t, dst=0, op=dist.ReduceOp.SUM)
+
+    # ---------------- device-timed region: inputs resident, per-step CUDA events, L2 flushed between steps
+    r.set_profiling(True)
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    trace_ms = shade_ms = other_ms = 0.0
+    launches = 0
+    rays_local = 0
+    for k in range(args.steps):
+        if flush is not None:
+            flush.fill_(float(k))
+        ev[k][0].record(stream)
+        step(args.warmup + k)
+        ev[k][1].record(stream)
+        # stats of this frame (synchronises; outside the event bracket)
+        s = r.stats()
+        trace_ms += s.ms_trace; shade_ms += s.ms_shade; other_ms += s.ms_other
+        launches += s.kernel_launches
+        rays_local += s.rays_traced
+    barrier()
+    clocks = sampler.stop()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([dev_ms, float(rays_local)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        dev_ms, rays_total = float(tmax[0]), float(tsum[1])
+    else:
+        rays_total = float(rays_local)
+    r.set_profiling(False)
+    mrays = rays_total / (dev_ms * 1e-3) / 1e6
+    spp_s = spp * args.steps * world / (dev_ms * 1e-3)
+
+    # ---------------- end-to-end: public API with host buffers (camera in, image out through pinned memory)
+    host_img = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_rays = 0
+    for k in range(args.steps):
+        cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
+        r.record(cam, sp)
+        if world > 1:
+            dist.reduce(img_t, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            b200pt.check(b200pt.lib().pt_read_rgba32f_async(r.handle, host_img.data_ptr(), sp))
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te[0])
+    e2e_mrays = rays_total / e2e_s / 1e6   # same frames => same ray counts as the device-timed region
+
+    # ---------------- roofline of the dominant kernel (K-trace): algorithmic bytes / event-timed duration
+    pk, pk_src = peaks()
+    roof = cpu = None
+    if rank == 0:
+        nodes, tris, crays = r.count_traversal()            # independent one-thread-per-ray walker, last frame
+        bytes_per_ray = (80.0 * nodes + 48.0 * tris) / max(1, crays)
+        n_trace_launches = args.steps * seg if spp == 1 else None
+        achieved = bytes_per_ray * rays_local / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else 0.0
+        roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+                "traffic": None, "kernel": "k_trace<BVH8>", "peak_source": pk_src,
+                "algorithmic_bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),
+                "trace_ms_per_step": trace_ms / args.steps, "shade_ms_per_step": shade_ms / args.steps, "other_ms_per_step": other_ms / args.steps,
+                "trace_mrays_per_s": rays_local / (trace_ms * 1e-3) / 1e6 if trace_ms > 0 else 0.0,
+                "note": "BVH (nodes+triangles) is L2-resident on B200; the HBM peak is the contract's denominator, see DESIGN.md"}
+        if not args.no_cpu_baseline and world == 1:
+            from oracle import orc
+            osc = orc.OracleScene(ps, True)
+            nt = orc.lib().orc_hardware_threads()
+            cfg = S.render_config(W, H, 1, seg)
+            row_step = max(1, int(round((W * H * seg / 2.0e6) / max(1, nt) / 4.0)))
+            t1 = time.perf_counter()
+            _, crays2 = osc.render_rows(cfg, S.camera_default(W, H, 0), 0, H, row_step, nt)
+            dt = time.perf_counter() - t1
+            rows = len(range(0, H, row_step))
+            cpu = {"value": crays2 / dt / 1e6, "unit": "Mrays/s", "cores": nt, "kind": "port",
+                   "sample": f"{rows} of {H} scanlines (every {row_step}th) of frame 0 at 1 spp, CPU oracle, {nt} threads, {dt:.2f} s"}
+    if rank == 0:
+        line = {"metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": WORKLOAD_DESC[name], "partition": "frames (rank r renders frame_count r, r+N, ...) + NCCL reduce(sum) to rank 0" if world > 1 else "none",
+                           "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed; per-step path state (365 MB) exceeds L2",
+                           "triangles": int(st0.num_triangles), "bvh8_nodes": int(st0.bvh_nodes), "bvh_build_ms": st0.ms_build,
+                           "scene_gen_s": t_gen, "create_s": t_create},
+                "spp_per_s": spp_s, "rays_per_step": rays_total / args.steps / world,
+                "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(S.PtCamera), "d2h_bytes_per_step": W * H * 16,
+                        "ms_per_step": 1e3 * e2e_s / args.steps, "spp_per_s": spp * args.steps * world / e2e_s},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(line))
+    r.deinit()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

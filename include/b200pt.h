@@ -263,6 +263,17 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits);
  * 80*nodes + 48*tris).  Counts the ray set of the last pt_render. */
 int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t* rays);
 
+/* Device evaluation of the shading restatement on caller-supplied records (host pointers), for
+ * pinning the CUDA BSDF / RNG / texture filter against the reference's shader code:
+ *   sample_brdf -> L, get_brdf_density -> pdf, brdf -> f   (src/shaders/brdf.glsl:22-150)
+ *   prng_seed + `draws` x pcg2d                            (src/shaders/rand.glsl:76-94)
+ *   texture(): bilinear REPEAT RGBA8                        (src/RayTracingPipeline.zig:54-70) */
+int pt_debug_bsdf(int device, size_t n, const float* normal3, const float* view3, const float* diffuse3,
+                  const float* f0_3, const float* roughness, const float* xi2, float* L3, float* pdf, float* f3);
+int pt_debug_rng(int device, size_t n, const uint32_t* pixel_xy_frame3, uint32_t draws, uint32_t* state2, float* xi2);
+int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t height, size_t n, const float* uv2,
+                     float* rgba4);
+
 /* Multi-GPU (one process per GPU).  Peer stores: rank 0 exports its image buffer as a CUDA IPC
  * handle, the other ranks open it and their accumulate kernel writes owned tiles straight into it
  * over NVLink.  `handle` is 64 bytes. */

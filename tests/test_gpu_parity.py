@@ -1,0 +1,283 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the CPU oracle, the
+golden fixtures and size-independent properties at full BASELINE.json sizes.
+
+Bar: primary-hit ids bit-exact; radiance bit-exact too (the arithmetic contract of DESIGN.md makes
+the fp32 expression trees identical: no FMA contraction, IEEE sqrt/div, correctly rounded sin/cos);
+NaNs compare equal to NaNs.  north_star allows <=0.01 % edge-tie pixels and a radiance tolerance; the
+tests hold the stricter bar and say so when they relax it."""
+import os
+
+import numpy as np
+import pytest
+
+import b200pt
+from oracle import orc
+from parity_util import bits_equal, hits_mismatch, random_rays
+from tools import scene as S
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def render(ps, W, H, spp, seg, frame=0, **kw):
+    r = b200pt.Renderer(ps, W, H, spp, seg, **kw)
+    cam = S.camera_default(r.width * max(1, kw.get("divider", 1)), r.height * max(1, kw.get("divider", 1)), frame)
+    r.record(cam)
+    r.sync()
+    out = r.image(), r.ids(), r.stats()
+    r.deinit()
+    return out
+
+
+def assert_matches_oracle(ps, W, H, spp, seg, frame=0, use_bvh=True, **kw):
+    img, ids, st = render(ps, W, H, spp, seg, frame, **kw)
+    oimg, oids, orays = orc.OracleScene(ps, True).render(S.render_config(W, H, spp, seg), S.camera_default(W, H, frame), use_bvh)
+    for name, a, b in zip(("instance", "primitive", "triangle"), ids, oids):
+        assert (a == b).all(), f"{name} ids differ in {int((a != b).sum())} pixels"
+    eq = bits_equal(img, oimg)
+    assert eq.all(), f"{int((~eq.all(axis=2)).sum())} of {W * H} pixels differ from the oracle"
+    return st, orays
+
+
+# ------------------------------------------------------------------ shading restatement vs reference GLSL vectors
+def test_bsdf_kernel_matches_reference_glsl_vectors():
+    g = np.load(os.path.join(GOLD, "bsdf_ref_vectors.npz"))
+    L, pdf, f = b200pt.debug_bsdf(g["N"], g["V"], g["kd"], g["f0"], g["rough"], g["xi"])
+    assert bits_equal(L, g["L"]).all() and bits_equal(pdf, g["pdf"]).all() and bits_equal(f, g["f"]).all()
+
+
+def test_bsdf_kernel_matches_oracle_on_a_million_records():
+    from tools.make_golden import bsdf_inputs
+    N, V, kd, f0, rough, xi = bsdf_inputs(4242, 1_000_000)
+    a = b200pt.debug_bsdf(N, V, kd, f0, rough, xi)
+    b = orc.bsdf_batch(orc.lib(), N, V, kd, f0, rough, xi, "orc")
+    for name, u, v in zip(("L", "pdf", "f"), a, b):
+        bad = ~bits_equal(u, v)
+        # sin/cos are "correctly rounded" on both sides but computed by different double libms:
+        # a double-rounding tie can differ with probability ~1e-8 per call
+        assert bad.sum() <= 2, f"{name}: {int(bad.sum())} words differ"
+
+
+def test_rng_kernel_matches_reference_glsl_vectors():
+    g = np.load(os.path.join(GOLD, "bsdf_ref_vectors.npz"))
+    for k in range(3):
+        state, xi = b200pt.debug_rng(g["px"], k + 1)
+        assert (state == g["states"][:, k]).all() and bits_equal(xi, g["xis"][:, k]).all()
+    state, _ = b200pt.debug_rng(g["px"], 0)
+    assert (state == g["seeds"]).all()
+
+
+def test_texture_filter_matches_oracle():
+    import ctypes as C
+    rng = np.random.default_rng(0)
+    for (w, h) in ((2, 2), (5, 3), (64, 64), (1, 7)):
+        tex = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        uv = ((rng.random((4000, 2)) - 0.3) * 3).astype(np.float32)
+        uv[:8] = [[0, 0], [1, 1], [0.5, 0.5], [-1, -1], [1e6, -1e6], [0.25, 0.75], [1 / w, 1 / h], [3e9, 1]]
+        got = b200pt.debug_texture(tex, uv)
+        out = (C.c_float * 4)()
+        ref = np.empty_like(got)
+        for i, (u, v) in enumerate(uv):
+            orc.lib().orc_sample_texture(tex.ctypes.data_as(C.c_void_p), w, h, C.c_float(u), C.c_float(v), out)
+            ref[i] = list(out)
+        assert bits_equal(got, ref).all()
+
+
+# ------------------------------------------------------------------ traversal kernel vs brute force
+@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_BVH2])
+@pytest.mark.parametrize("seed,ntri,nmesh,ninst", [(3, 3000, 3, 7), (5, 3, 3, 4), (11, 20000, 2, 40), (12, 64, 5, 1)])
+def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
+    ps = S.random_soup(seed, ntri, nmesh, ninst).pack()
+    r = b200pt.Renderer(ps, 32, 32, 1, 1, flags=flags)
+    rays = random_rays(seed, 100000, dtype=b200pt.PtRay_dtype)
+    # axis-parallel and zero-component directions, rays starting on geometry
+    rays["dir"][:300] = np.tile(np.eye(3, dtype=np.float32), (100, 1))
+    rays["dir"][300:600] = -np.tile(np.eye(3, dtype=np.float32), (100, 1))
+    hg = r.trace(rays)
+    ho = orc.OracleScene(ps, False).trace(rays, use_bvh=False)
+    bad = hits_mismatch(hg, ho)
+    assert not bad.any(), f"{int(bad.sum())} of {len(rays)} rays differ from brute force"
+    r.deinit()
+
+
+def test_trace_edge_cases():
+    ps = S.cornell().pack()
+    r = b200pt.Renderer(ps, 32, 32, 1, 1)
+    assert len(r.trace(np.zeros(0, b200pt.PtRay_dtype))) == 0
+    rays = np.zeros(4, b200pt.PtRay_dtype)
+    rays["origin"] = [0, 0, 0]; rays["dir"] = [0, 0, 1]
+    rays["tmin"] = [1e-3, 3.0, 1e-3, 2.9]; rays["tmax"] = [1e4, 1e4, 3.0, 3.1]     # back wall at z = 3: open interval
+    h = r.trace(rays)
+    ho = orc.OracleScene(ps, False).trace(rays, use_bvh=False)
+    assert not hits_mismatch(h, ho).any()
+    assert h["t"][1] == np.float32(1e32) and h["t"][2] == np.float32(1e32) and h["t"][3] == 3.0 and h["instance"][1] == 0xFFFFFFFF
+    r.deinit()
+
+
+def test_empty_scene_renders_sky():
+    sb = S.SceneBuilder(); sb.add_material()
+    ps = sb.pack()
+    img, ids, st = render(ps, 64, 32, 2, 3)
+    oimg, oids, _ = orc.OracleScene(ps, True).render(S.render_config(64, 32, 2, 3), S.camera_default(64, 32, 0), True)
+    assert bits_equal(img, oimg).all() and (ids[0] == 0xFFFFFFFF).all()
+
+
+# ------------------------------------------------------------------ the trace loop vs the oracle
+def test_cornell_golden_fixture():
+    g = np.load(os.path.join(GOLD, "cornell_64.npz"))
+    img, ids, st = render(S.cornell().pack(), 64, 64, 2, 3, frame=5)
+    assert bits_equal(img, g["img"]).all()
+    assert (ids[0] == g["inst"]).all() and (ids[1] == g["prim"]).all() and (ids[2] == g["tri"]).all()
+
+
+def test_config_c1_cornell_512():
+    st, orays = assert_matches_oracle(S.cornell().pack(), 512, 512, 1, 2, use_bvh=False)
+    assert st.rays_traced == orays          # 1 spp: no primary reuse, identical ray counts
+
+
+@pytest.mark.parametrize("W,H,spp,seg,frame", [(96, 64, 4, 5, 0), (100, 60, 2, 3, 3), (33, 9, 3, 1, 1), (31, 7, 1, 8, 2)])
+def test_cornell_sample_and_bounce_loops(W, H, spp, seg, frame):
+    assert_matches_oracle(S.cornell().pack(), W, H, spp, seg, frame)
+
+
+def test_random_soup_with_scaled_rotated_instances():
+    # exercises the literal A^-1 "normal matrix" (quirk Q3/Q4) under rotation + non-uniform scale
+    assert_matches_oracle(S.random_soup(3, 3000, 3, 7).pack(), 160, 90, 2, 4, use_bvh=False)
+
+
+def test_instancing_scene_small():
+    assert_matches_oracle(S.instanced(1234, 4, 64).pack(), 320, 180, 2, 4)
+
+
+@pytest.fixture(scope="module")
+def sponza():
+    return S.sponza_scale().pack()
+
+
+def test_config_c2_sponza_scale_1080p_vs_oracle(sponza):
+    """BASELINE.json configs[1] at full size, against the multi-threaded oracle."""
+    st, orays = assert_matches_oracle(sponza, 1920, 1080, 1, 2)
+    assert st.rays_traced == orays and st.num_triangles == sponza.num_triangles
+
+
+def test_c2_reference_walker_and_no_reuse_equivalence(sponza):
+    """Size-independent properties at 1080p: the BVH2 reference walker, and re-tracing the primary
+    ray for every sample, give the same image as the BVH8 kernel with primary-hit reuse."""
+    a, ia, sa = render(sponza, 1920, 1080, 3, 3, frame=1)
+    b, ib, sb_ = render(sponza, 1920, 1080, 3, 3, frame=1, flags=b200pt.PT_FLAG_TRACE_BVH2)
+    c, ic, sc = render(sponza, 1920, 1080, 3, 3, frame=1, flags=b200pt.PT_FLAG_NO_PRIMARY_REUSE)
+    assert bits_equal(a, b).all() and bits_equal(a, c).all()
+    assert all((x == y).all() and (x == z).all() for x, y, z in zip(ia, ib, ic))
+    assert sc.rays_traced > sa.rays_traced        # reuse saves (S-1) primary rays per pixel
+
+
+def test_tile_partition_sums_to_single_gpu_image(sponza):
+    """N-rank tile partitioning emulated on one GPU (ranks run one after the other): the sum of the
+    per-rank images equals the 1-rank image bit for bit, and every pixel is owned once."""
+    W, H = 1000, 500    # ragged edge tiles (1000 % 32 != 0, 500 % 8 != 0)
+    full, _, _ = render(sponza, W, H, 2, 3, frame=2)
+    for world in (2, 3, 8):
+        acc = np.zeros_like(full); owned = np.zeros((H, W), np.int32)
+        for rank in range(world):
+            img, _, _ = render(sponza, W, H, 2, 3, frame=2, rank=rank, world=world, partition=b200pt.PT_PARTITION_TILES)
+            acc += img; owned += (img[..., 3] != 0)
+        assert (owned == 1).all()
+        assert bits_equal(acc, full).all()
+
+
+def test_ray_counts_and_stats(sponza):
+    img, ids, st = render(sponza, 640, 360, 1, 2)
+    hit = int((ids[0] != 0xFFFFFFFF).sum())
+    assert 640 * 360 <= st.rays_traced <= 640 * 360 + hit
+    assert st.kernel_launches == 1 + 2 * 2 and st.bvh_nodes > 0 and st.ms_build > 0
+
+
+# ------------------------------------------------------------------ outputs and the rest of the RaytracingPass surface
+def test_bgra8_is_the_reference_storage_format():
+    ps = S.cornell().pack()
+    r = b200pt.Renderer(ps, 128, 64, 2, 3)
+    r.record(S.camera_default(128, 64, 0)); r.sync()
+    img = r.image(); b = r.image_bgra8()
+    q = (np.clip(np.nan_to_num(img, nan=0.0), 0, 1) * np.float32(255.0) + np.float32(0.5)).astype(np.uint8)
+    assert np.array_equal(b[..., 0], q[..., 2]) and np.array_equal(b[..., 1], q[..., 1]) and np.array_equal(b[..., 2], q[..., 0])
+    assert (b[..., 3] == 255).all()
+    r.deinit()
+
+
+def test_divider_upscale_and_resize():
+    ps = S.cornell().pack()
+    r = b200pt.Renderer(ps, 256, 128, 1, 2, divider=2)
+    assert (r.width, r.height) == (128, 64)                  # storage image = extent / divider (RaytracingPass.zig:149-152)
+    cam = S.camera_default(256, 128, 0)                      # aspect from the window extent (main.zig:222)
+    r.record(cam); r.sync()
+    small = r.image(); up = r.image_upscaled()
+    assert up.shape == (128, 256, 4)
+    assert np.array_equal(up, np.repeat(np.repeat(small, 2, axis=0), 2, axis=1))     # nearest blit (:599-635)
+    osc = orc.OracleScene(ps, True)
+    oimg, _, _ = osc.render(S.render_config(256, 128, 1, 2, divider=2), cam, True)
+    assert bits_equal(small, oimg).all()
+    r.resize(96, 48)                                          # resize drops the divider (quirk Q13)
+    assert (r.width, r.height) == (96, 48)
+    cam2 = S.camera_default(96, 48, 1)
+    r.record(cam2); r.sync()
+    oimg2, _, _ = osc.render(S.render_config(96, 48, 1, 2), cam2, True)
+    assert bits_equal(r.image(), oimg2).all()
+    r.deinit()
+
+
+def test_progressive_accumulation_converges_to_oracle_mean():
+    """Converged-image criterion of north_star: mean over frames within 1 % of the oracle's mean
+    (here exactly equal per frame, so the means agree to rounding)."""
+    ps = S.cornell().pack()
+    W, H, frames = 64, 64, 16
+    r = b200pt.Renderer(ps, W, H, 1, 3)
+    r.set_accumulate(True)
+    osc = orc.OracleScene(ps, True)
+    acc = np.zeros((H, W, 4), np.float32)
+    for f in range(frames):
+        cam = S.camera_default(W, H, f)
+        r.record(cam)
+        acc += osc.render(S.render_config(W, H, 1, 3), cam, True)[0]
+    mean = r.accum_mean()
+    assert bits_equal(mean, acc * np.float32(1.0 / frames)).all()
+    assert abs(np.nanmean(mean[..., :3]) / np.nanmean((acc / frames)[..., :3]) - 1) < 0.01
+    r.deinit()
+
+
+def test_render_is_asynchronous_and_repeatable():
+    ps = S.cornell().pack()
+    r = b200pt.Renderer(ps, 200, 100, 2, 4)
+    cams = [S.camera_default(200, 100, f) for f in range(3)]
+    for c in cams:                       # queued back to back, no sync in between
+        r.record(c)
+    r.sync()
+    last = r.image()
+    r.record(cams[2]); r.sync()
+    assert bits_equal(last, r.image()).all()
+    r.deinit()
+
+
+def test_invalid_scene_is_rejected():
+    import ctypes as C
+    ps = S.cornell().pack()
+    d = ps.desc()
+    bad = (S.PtPrimitive * len(ps.primitives))(*ps.primitives)
+    bad[0].positions_offset = ps.triangle_data.size            # out of the blob
+    d.primitives = C.cast(bad, C.POINTER(S.PtPrimitive))
+
+    class Fake:
+        def desc(self):
+            return d
+    with pytest.raises(b200pt.PtError) as e:
+        b200pt.Renderer(Fake(), 32, 32)
+    assert e.value.status == -1
+
+
+def test_traversal_byte_counter(sponza):
+    r = b200pt.Renderer(sponza, 640, 360, 1, 2)
+    r.record(S.camera_default(640, 360, 0)); r.sync()
+    before = r.image()
+    nodes, tris, rays = r.count_traversal()
+    assert rays == r.stats().rays_traced and nodes > rays and tris > 0
+    assert bits_equal(before, r.image()).all()      # the counting walker renders the same frame
+    r.deinit()

@@ -1,0 +1,133 @@
+"""Oracle pinned against (1) the known-answer vectors of SURVEY.md Appendix C, (2) golden vectors
+produced by the reference's own brdf.glsl / rand.glsl compiled as C++ (tests/golden, made by
+tools/make_golden.py) and (3) the live reference build when oracle/_ref exists."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from oracle import orc
+from parity_util import bits_equal
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _seed(lib, prefix, x, y, f):
+    s = (C.c_uint32 * 2)()
+    getattr(lib, prefix + "_prng_seed")(x, y, f, s)
+    return s
+
+
+def _pcg(lib, prefix, s):
+    o = (C.c_float * 2)()
+    getattr(lib, prefix + "_pcg2d")(s, o)
+    return np.float32(o[0]), np.float32(o[1])
+
+
+# SURVEY.md Appendix C (derived from rand.glsl:76-94 by two independent routes)
+APPENDIX_C = [
+    ((0, 0, 0), (0x00000000, 0x00000000), (0x18e431a7, 0x055df4d1), (0.0972319618, 0.0209649093), (0xae860441, 0x69b5769c), (0.681732416, 0.412925154)),
+    ((3, 7, 0), (0x448749e5, 0x2ad72673), (0x33c2987b, 0xf32032a2), (0.202188045, 0.949710071), (0x93bab5ce, 0xd19dd79b), (0.577067733, 0.818814754)),
+    ((1919, 1079, 5), (0x269eec2d, 0xffe67ee6), (0x24af6a4e, 0x2228d776), (0.143301621, 0.133435696), (0x10af92b6, 0x73571d2d), (0.0651790351, 0.450547993)),
+]
+
+
+@pytest.mark.parametrize("case", APPENDIX_C)
+def test_rng_known_answers(oracle_lib, case):
+    (x, y, f), seed, st1, xi1, st2, xi2 = case
+    s = _seed(oracle_lib, "orc", x, y, f)
+    assert tuple(s) == seed
+    a = _pcg(oracle_lib, "orc", s)
+    assert tuple(s) == st1 and a == (np.float32(xi1[0]), np.float32(xi1[1]))
+    b = _pcg(oracle_lib, "orc", s)
+    assert tuple(s) == st2 and b == (np.float32(xi2[0]), np.float32(xi2[1]))
+
+
+def test_pcg2d_can_return_one():
+    # uint -> float is round-to-nearest: 0xFFFFFFFF * 2^-32 == 1.0f exactly (SURVEY a-10)
+    assert np.float32(np.uint32(0xFFFFFFFF)) * np.float32(2.32830643654e-10) == np.float32(1.0)
+
+
+def test_rng_golden_from_reference_glsl(oracle_lib):
+    g = np.load(os.path.join(GOLD, "bsdf_ref_vectors.npz"))
+    for i, (x, y, f) in enumerate(g["px"]):
+        s = _seed(oracle_lib, "orc", int(x), int(y), int(f))
+        assert tuple(s) == tuple(g["seeds"][i])
+        for k in range(3):
+            xi = _pcg(oracle_lib, "orc", s)
+            assert tuple(s) == tuple(g["states"][i, k])
+            assert xi == (g["xis"][i, k, 0], g["xis"][i, k, 1])
+
+
+def test_bsdf_golden_from_reference_glsl(oracle_lib):
+    g = np.load(os.path.join(GOLD, "bsdf_ref_vectors.npz"))
+    L, pdf, f = orc.bsdf_batch(oracle_lib, g["N"], g["V"], g["kd"], g["f0"], g["rough"], g["xi"], "orc")
+    assert bits_equal(L, g["L"]).all()
+    assert bits_equal(pdf, g["pdf"]).all()
+    assert bits_equal(f, g["f"]).all()
+
+
+def test_bsdf_live_against_reference_glsl(oracle_lib, ref_glsl):
+    """10^6 random records: the restatement equals the reference shader code bit for bit."""
+    from tools.make_golden import bsdf_inputs
+    N, V, kd, f0, rough, xi = bsdf_inputs(99, 1_000_000)
+    a = orc.bsdf_batch(oracle_lib, N, V, kd, f0, rough, xi, "orc")
+    b = orc.bsdf_batch(ref_glsl, N, V, kd, f0, rough, xi, "ref")
+    for u, v in zip(a, b):
+        assert bits_equal(u, v).all()
+
+
+def test_rng_live_against_reference_glsl(oracle_lib, ref_glsl):
+    rng = np.random.default_rng(5)
+    for _ in range(2000):
+        x, y, f = int(rng.integers(0, 8192)), int(rng.integers(0, 8192)), int(rng.integers(0, 2 ** 32))
+        s1, s2 = _seed(oracle_lib, "orc", x, y, f), _seed(ref_glsl, "ref", x, y, f)
+        assert tuple(s1) == tuple(s2)
+        assert _pcg(oracle_lib, "orc", s1) == _pcg(ref_glsl, "ref", s2) and tuple(s1) == tuple(s2)
+
+
+def test_float_spot_values(oracle_lib):
+    # SURVEY.md Appendix C floating-point spot values (±2 ulp: they were produced with glibc sinf/cosf)
+    out = (C.c_float * 3)()
+    oracle_lib.orc_fresnel_schlick((C.c_float * 3)(0.04, 0.04, 0.04), (C.c_float * 3)(1, 1, 1), C.c_float(0.5), out)
+    assert abs(out[0] - 0.0700000003) < 1e-8
+    m = (C.c_float * 9)()
+    oracle_lib.orc_shading_space((C.c_float * 3)(0, 0, 1), m)
+    assert list(m) == [1, 0, 0, 0, 1, 0, 0, 0, 1]
+    oracle_lib.orc_shading_space((C.c_float * 3)(0, 0, -1), m)
+    assert list(m) == [1, 0, 0, 0, -1, 0, 0, 0, -1]
+    n = np.array([0.1, 0.2, 1.0]); n /= np.linalg.norm(n)
+    v = np.array([0.3, -0.1, 0.9]); v /= np.linalg.norm(v)
+    L, pdf, f = orc.bsdf_batch(oracle_lib, n[None].astype(np.float32), v[None].astype(np.float32), np.array([[0.6, 0.5, 0.4]], np.float32),
+                               np.array([[0.04, 0.04, 0.04]], np.float32), np.array([0.3], np.float32),
+                               np.array([[0.202188045, 0.949710071]], np.float32))
+    assert np.allclose(L[0], [-0.783413112, 0.591820419, 0.189769357], rtol=0, atol=2e-6)
+    assert abs(pdf[0] - 0.0775616914) < 2e-7
+    assert np.allclose(f[0], [0.205958679, 0.176263198, 0.146567732], rtol=0, atol=2e-7)
+
+
+def test_shading_space_orthonormal(oracle_lib):
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        n = rng.normal(size=3); n /= np.linalg.norm(n)
+        m = (C.c_float * 9)()
+        oracle_lib.orc_shading_space((C.c_float * 3)(*n), m)
+        M = np.array(list(m)).reshape(3, 3)
+        assert np.allclose(M @ M.T, np.eye(3), atol=2e-6)
+
+
+def test_furnace_bound(oracle_lib):
+    """White diffuse furnace: the Monte-Carlo estimate of brdf*cos/pdf stays <= 1 (+ noise)."""
+    n = 200000
+    rng = np.random.default_rng(1)
+    N = np.tile(np.array([[0, 0, 1]], np.float32), (n, 1))
+    V = np.tile(np.array([[0.3, 0.2, 0.9327379]], np.float32), (n, 1))
+    kd = np.ones((n, 3), np.float32); f0 = np.full((n, 3), 0.02, np.float32)
+    rough = np.full(n, 0.5, np.float32); xi = rng.random((n, 2)).astype(np.float32)
+    L, pdf, f = orc.bsdf_batch(oracle_lib, N, V, kd, f0, rough, xi, "orc")
+    cos = L[:, 2]
+    ok = (cos > 0) & (pdf > 0)
+    w = np.where(ok, f[:, 0] * cos / np.where(ok, pdf, 1), 0)
+    assert np.isfinite(w).all()
+    assert w.mean() < 1.05

@@ -749,7 +749,8 @@ def atrium(seed=1234, target_tris=260_000, n_materials=25, tex_size=1024, rough_
             break
     rng.bit_generator.state = state
     build(mid, soups)
-    prims = [soups[m].prim(m) for m in mats + [m_light] if soups[m].nv > 0]
+    # both index widths occur (like real assets): big primitives use u32 indices, small ones u16
+    prims = [soups[m].prim(m, force_u32=soups[m].nv > 20000) for m in mats + [m_light] if soups[m].nv > 0]
     mesh = sb.add_mesh(prims)
     sb.add_node(mesh)
     return sb

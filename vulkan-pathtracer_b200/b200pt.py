@@ -235,6 +235,36 @@ class Renderer:
         return n.value, t.value, r.value
 
 
+def debug_bsdf(N, V, kd, f0, rough, xi, device=0):
+    """sample_brdf / get_brdf_density / brdf evaluated by the CUDA restatement."""
+    n = len(rough)
+    a = [np.ascontiguousarray(x, np.float32) for x in (N, V, kd, f0, rough, xi)]
+    L, pdf, f = np.empty((n, 3), np.float32), np.empty(n, np.float32), np.empty((n, 3), np.float32)
+    fn = lib().pt_debug_bsdf
+    fn.argtypes = [C.c_int, C.c_size_t] + [C.c_void_p] * 9
+    check(fn(device, n, *[x.ctypes.data for x in a], L.ctypes.data, pdf.ctypes.data, f.ctypes.data))
+    return L, pdf, f
+
+
+def debug_rng(pixel_xy_frame, draws, device=0):
+    p = np.ascontiguousarray(pixel_xy_frame, np.uint32).reshape(-1, 3)
+    state, xi = np.empty((len(p), 2), np.uint32), np.empty((len(p), 2), np.float32)
+    fn = lib().pt_debug_rng
+    fn.argtypes = [C.c_int, C.c_size_t, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+    check(fn(device, len(p), p.ctypes.data, draws, state.ctypes.data, xi.ctypes.data))
+    return state, xi
+
+
+def debug_texture(rgba, uv, device=0):
+    rgba = np.ascontiguousarray(rgba, np.uint8)
+    uv = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+    out = np.empty((len(uv), 4), np.float32)
+    fn = lib().pt_debug_texture
+    fn.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p]
+    check(fn(device, rgba.ctypes.data, rgba.shape[1], rgba.shape[0], len(uv), uv.ctypes.data, out.ctypes.data))
+    return out
+
+
 def write_pfm(path, rgba):
     rgba = np.ascontiguousarray(rgba, np.float32)
     check(lib().pt_write_pfm(os.fsencode(path), rgba.ctypes.data, rgba.shape[1], rgba.shape[0]))

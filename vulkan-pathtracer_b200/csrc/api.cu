@@ -557,6 +557,74 @@ int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t*
     return PT_OK;
 }
 
+}  // extern "C"
+
+namespace {
+// scoped device buffers for the pt_debug_* entry points
+struct DevBufs {
+    std::vector<void*> ptrs;
+    ~DevBufs() { for (void* p : ptrs) cudaFree(p); }
+    template <typename T> T* in(const T* host, size_t count) {
+        void* d = nullptr;
+        if (cudaMalloc(&d, std::max<size_t>(count, 1) * sizeof(T)) != cudaSuccess) return nullptr;
+        ptrs.push_back(d);
+        if (host && count && cudaMemcpy(d, host, count * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) return nullptr;
+        return static_cast<T*>(d);
+    }
+};
+int debug_begin(int device) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { set_error("no CUDA device available (no CPU fallback)"); return PT_ERR_CUDA; }
+    if (device < 0 || device >= ndev) { set_error("device ordinal out of range"); return PT_ERR_INVALID_ARGUMENT; }
+    PT_CUDA_CHECK(cudaSetDevice(device));
+    return PT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int pt_debug_bsdf(int device, size_t n, const float* N, const float* V, const float* kd, const float* f0, const float* rough,
+                  const float* xi, float* L, float* pdf, float* f) {
+    PT_REQUIRE(n == 0 || (N && V && kd && f0 && rough && xi && L && pdf && f), "pt_debug_bsdf: null argument");
+    int rc = debug_begin(device); if (rc != PT_OK) return rc;
+    if (n == 0) return PT_OK;
+    DevBufs b;
+    float *dN = b.in(N, 3 * n), *dV = b.in(V, 3 * n), *dk = b.in(kd, 3 * n), *d0 = b.in(f0, 3 * n), *dr = b.in(rough, n), *dx = b.in(xi, 2 * n);
+    float *dL = b.in<float>(nullptr, 3 * n), *dp = b.in<float>(nullptr, n), *df = b.in<float>(nullptr, 3 * n);
+    if (!dN || !dV || !dk || !d0 || !dr || !dx || !dL || !dp || !df) { set_error("pt_debug_bsdf: device allocation/copy failed"); return PT_ERR_CUDA; }
+    launch_debug_bsdf((uint32_t)n, dN, dV, dk, d0, dr, dx, dL, dp, df, nullptr);
+    PT_CUDA_CHECK(cudaMemcpy(L, dL, 12 * n, cudaMemcpyDeviceToHost));
+    PT_CUDA_CHECK(cudaMemcpy(pdf, dp, 4 * n, cudaMemcpyDeviceToHost));
+    PT_CUDA_CHECK(cudaMemcpy(f, df, 12 * n, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+int pt_debug_rng(int device, size_t n, const uint32_t* pxf, uint32_t draws, uint32_t* state, float* xi) {
+    PT_REQUIRE(n == 0 || (pxf && state && xi), "pt_debug_rng: null argument");
+    int rc = debug_begin(device); if (rc != PT_OK) return rc;
+    if (n == 0) return PT_OK;
+    DevBufs b;
+    uint32_t* dp = b.in(pxf, 3 * n); uint32_t* ds = b.in<uint32_t>(nullptr, 2 * n); float* dx = b.in<float>(nullptr, 2 * n);
+    if (!dp || !ds || !dx) { set_error("pt_debug_rng: device allocation/copy failed"); return PT_ERR_CUDA; }
+    launch_debug_rng((uint32_t)n, dp, draws, ds, dx, nullptr);
+    PT_CUDA_CHECK(cudaMemcpy(state, ds, 8 * n, cudaMemcpyDeviceToHost));
+    PT_CUDA_CHECK(cudaMemcpy(xi, dx, 8 * n, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t height, size_t n, const float* uv, float* out) {
+    PT_REQUIRE(rgba && width && height && (n == 0 || (uv && out)), "pt_debug_texture: invalid argument");
+    int rc = debug_begin(device); if (rc != PT_OK) return rc;
+    if (n == 0) return PT_OK;
+    DevBufs b;
+    uint32_t* dt = b.in(reinterpret_cast<const uint32_t*>(rgba), (size_t)width * height);
+    float* du = b.in(uv, 2 * n); float* dout = b.in<float>(nullptr, 4 * n);
+    if (!dt || !du || !dout) { set_error("pt_debug_texture: device allocation/copy failed"); return PT_ERR_CUDA; }
+    launch_debug_texture(TexRec{dt, width, height}, (uint32_t)n, du, dout, nullptr);
+    PT_CUDA_CHECK(cudaMemcpy(out, dout, 16 * n, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
 int pt_ipc_export_image(PtRenderer* r, uint8_t handle[64]) {
     PT_REQUIRE(r && handle, "pt_ipc_export_image: null argument");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");

@@ -271,6 +271,44 @@ __global__ void k_scale(const float4* __restrict__ in, float4* __restrict__ out,
     out[i] = make_float4(a.x * s, a.y * s, a.z * s, a.w * s);
 }
 
+__global__ void k_debug_bsdf(uint32_t n, const float* N, const float* V, const float* kd, const float* f0, const float* rough,
+                             const float* xi, float* L, float* pdf, float* f) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    ShadingInfo s;
+    s.normal = v3(N[3 * i], N[3 * i + 1], N[3 * i + 2]);
+    s.out_dir = v3(V[3 * i], V[3 * i + 1], V[3 * i + 2]);
+    s.lambert_out = dot(s.normal, s.out_dir);
+    s.diffuse_albedo = v3(kd[3 * i], kd[3 * i + 1], kd[3 * i + 2]);
+    s.fresnel_0 = v3(f0[3 * i], f0[3 * i + 1], f0[3 * i + 2]);
+    s.roughness = rough[i];
+    V2 r; r.x = xi[2 * i]; r.y = xi[2 * i + 1];
+    const V3 l = sample_brdf(s, r);
+    const float p = get_brdf_density(s, l);
+    const V3 v = brdf(s, l);
+    L[3 * i] = l.x; L[3 * i + 1] = l.y; L[3 * i + 2] = l.z;
+    pdf[i] = p;
+    f[3 * i] = v.x; f[3 * i + 1] = v.y; f[3 * i + 2] = v.z;
+}
+
+__global__ void k_debug_rng(uint32_t n, const uint32_t* pxf, uint32_t draws, uint32_t* state, float* xi) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    U2 s = prng_seed(pxf[3 * i], pxf[3 * i + 1], pxf[3 * i + 2]);
+    V2 r; r.x = 0.0f; r.y = 0.0f;
+    for (uint32_t k = 0; k < draws; ++k) r = pcg2d(s);
+    state[2 * i] = s.x; state[2 * i + 1] = s.y;
+    xi[2 * i] = r.x; xi[2 * i + 1] = r.y;
+}
+
+__global__ void k_debug_texture(TexRec tex, uint32_t n, const float* uv, float* out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    V2 c; c.x = uv[2 * i]; c.y = uv[2 * i + 1];
+    const V4 t = sample_texture(tex, c);
+    out[4 * i] = t.x; out[4 * i + 1] = t.y; out[4 * i + 2] = t.z; out[4 * i + 3] = t.w;
+}
+
 template <typename K>
 int persistent_blocks(K kernel, int threads, int num_sms) {
     int per_sm = 0;
@@ -311,6 +349,17 @@ void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, Hi
     const int blocks = num_sms * 4;
     if (mode == TRACE_BVH2) k_trace_rays<TRACE_BVH2><<<blocks, kTraceThreads, 0, st>>>(sc, rays, n, hits, tlas2_count, tlas2_leaf_instance, cursor);
     else k_trace_rays<TRACE_BVH8><<<blocks, kTraceThreads, 0, st>>>(sc, rays, n, hits, tlas2_count, tlas2_leaf_instance, cursor);
+}
+
+void launch_debug_bsdf(uint32_t n, const float* N, const float* V, const float* kd, const float* f0, const float* rough,
+                       const float* xi, float* L, float* pdf, float* f, cudaStream_t st) {
+    if (n) k_debug_bsdf<<<(n + 127) / 128, 128, 0, st>>>(n, N, V, kd, f0, rough, xi, L, pdf, f);
+}
+void launch_debug_rng(uint32_t n, const uint32_t* pxf, uint32_t draws, uint32_t* state, float* xi, cudaStream_t st) {
+    if (n) k_debug_rng<<<(n + 127) / 128, 128, 0, st>>>(n, pxf, draws, state, xi);
+}
+void launch_debug_texture(TexRec tex, uint32_t n, const float* uv, float* out, cudaStream_t st) {
+    if (n) k_debug_texture<<<(n + 127) / 128, 128, 0, st>>>(tex, n, uv, out);
 }
 
 void launch_to_bgra8(const float* rgba, uint8_t* bgra, uint32_t n_pixels, cudaStream_t st) {

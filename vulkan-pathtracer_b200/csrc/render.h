@@ -56,4 +56,10 @@ void launch_upscale(const float* src, uint32_t sw, uint32_t sh, float* dst, uint
 void launch_accumulate(const float* frame, float* accum, uint32_t n_floats, cudaStream_t st);
 void launch_scale(const float* accum, float* out, uint32_t n_floats, float scale, cudaStream_t st);
 
+// shading restatement on raw records (pt_debug_*)
+void launch_debug_bsdf(uint32_t n, const float* N, const float* V, const float* kd, const float* f0, const float* rough,
+                       const float* xi, float* L, float* pdf, float* f, cudaStream_t st);
+void launch_debug_rng(uint32_t n, const uint32_t* pxf, uint32_t draws, uint32_t* state, float* xi, cudaStream_t st);
+void launch_debug_texture(TexRec tex, uint32_t n, const float* uv, float* out, cudaStream_t st);
+
 }  // namespace pt
