@@ -105,7 +105,7 @@ def test_trace_edge_cases():
     r = b200pt.Renderer(ps, 32, 32, 1, 1)
     assert len(r.trace(np.zeros(0, b200pt.PtRay_dtype))) == 0
     rays = np.zeros(4, b200pt.PtRay_dtype)
-    rays["origin"] = [0, 0, 0]; rays["dir"] = [0, 0, 1]
+    rays["origin"] = [0.9, 0.9, 0]; rays["dir"] = [0, 0, 1]       # sees only the back wall
     rays["tmin"] = [1e-3, 3.0, 1e-3, 2.9]; rays["tmax"] = [1e4, 1e4, 3.0, 3.1]     # back wall at z = 3: open interval
     h = r.trace(rays)
     ho = orc.OracleScene(ps, False).trace(rays, use_bvh=False)

@@ -24,6 +24,7 @@ struct PtRenderer {
     int device = 0;
     int num_sms = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t last_stream = nullptr;   // stream of the most recent pt_render (caller's or our own)
     // scene on the device
     uint8_t* d_blob = nullptr;
     PrimRec* d_prims = nullptr;
@@ -225,6 +226,12 @@ void destroy_impl(PtRenderer* r) {
 
 }  // namespace
 
+// stream for follow-up work on the image: the caller's, else the stream of the last pt_render
+static inline cudaStream_t follow_stream(PtRenderer* r, void* user) {
+    if (user) return static_cast<cudaStream_t>(user);
+    return r->last_stream ? r->last_stream : r->stream;
+}
+
 #define PT_REQUIRE(cond, msg) do { if (!(cond)) { set_error(msg); return PT_ERR_INVALID_ARGUMENT; } } while (0)
 
 extern "C" {
@@ -347,6 +354,7 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     r->last_launches = launches;
     r->last_cam = *camera;
     r->have_last_cam = true;
+    r->last_stream = st;
     return PT_OK;
 }
 
@@ -360,14 +368,14 @@ int pt_render(PtRenderer* r, const PtCamera* camera, void* cuda_stream) {
 int pt_sync(PtRenderer* r) {
     PT_REQUIRE(r, "pt_sync: null renderer");
     PT_CUDA_CHECK(cudaSetDevice(r->device));
+    if (r->last_stream && r->last_stream != r->stream) PT_CUDA_CHECK(cudaStreamSynchronize(r->last_stream));
     PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
     return PT_OK;
 }
 
 int pt_resize(PtRenderer* r, uint32_t width, uint32_t height) {
     PT_REQUIRE(r && width > 0 && height > 0, "pt_resize: invalid argument");
-    PT_CUDA_CHECK(cudaSetDevice(r->device));
-    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     // Like the reference, the storage image is re-created at the full new extent: the divider is
     // dropped (RaytracingPass.zig:684-697, quirk Q13).
     r->cfg.width = width; r->cfg.height = height; r->cfg.divider = 1;
@@ -389,7 +397,7 @@ int pt_device_image(PtRenderer* r, float** device_ptr) {
 
 int pt_read_rgba32f_async(PtRenderer* r, float* dst, void* cuda_stream) {
     PT_REQUIRE(r && dst, "pt_read_rgba32f_async: null argument");
-    cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : r->stream;
+    cudaStream_t st = follow_stream(r, cuda_stream);
     PT_CUDA_CHECK(cudaMemcpyAsync(dst, r->d_image, (size_t)r->pm.width * r->pm.height * 16, cudaMemcpyDeviceToHost, st));
     return PT_OK;
 }
@@ -402,7 +410,7 @@ int pt_read_rgba32f(PtRenderer* r, float* host_dst) {
 
 int pt_read_bgra8_async(PtRenderer* r, uint8_t* dst, void* cuda_stream) {
     PT_REQUIRE(r && dst, "pt_read_bgra8_async: null argument");
-    cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : r->stream;
+    cudaStream_t st = follow_stream(r, cuda_stream);
     const size_t px = (size_t)r->pm.width * r->pm.height;
     if (!r->d_bgra) { int rc = dev_alloc(&r->d_bgra, px * 4); if (rc != PT_OK) return rc; }
     launch_to_bgra8(r->d_image, r->d_bgra, (uint32_t)px, st);
@@ -419,7 +427,7 @@ int pt_read_bgra8(PtRenderer* r, uint8_t* host_dst) {
 int pt_read_ids(PtRenderer* r, uint32_t* instance, uint32_t* primitive, uint32_t* triangle) {
     PT_REQUIRE(r, "pt_read_ids: null renderer");
     const size_t px = (size_t)r->pm.width * r->pm.height;
-    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     if (instance) PT_CUDA_CHECK(cudaMemcpy(instance, r->d_ids, px * 4, cudaMemcpyDeviceToHost));
     if (primitive) PT_CUDA_CHECK(cudaMemcpy(primitive, r->d_ids + px, px * 4, cudaMemcpyDeviceToHost));
     if (triangle) PT_CUDA_CHECK(cudaMemcpy(triangle, r->d_ids + 2 * px, px * 4, cudaMemcpyDeviceToHost));
@@ -431,8 +439,9 @@ int pt_read_rgba32f_upscaled(PtRenderer* r, float* host_dst) {
     if (r->pm.width == r->full_w && r->pm.height == r->full_h) return pt_read_rgba32f(r, host_dst);
     const size_t px = (size_t)r->full_w * r->full_h;
     if (!r->d_upscaled) { int rc = dev_alloc(&r->d_upscaled, px * 4); if (rc != PT_OK) return rc; }
-    launch_upscale(r->d_image, r->pm.width, r->pm.height, r->d_upscaled, r->full_w, r->full_h, r->stream);
-    PT_CUDA_CHECK(cudaMemcpyAsync(host_dst, r->d_upscaled, px * 16, cudaMemcpyDeviceToHost, r->stream));
+    cudaStream_t st = follow_stream(r, nullptr);
+    launch_upscale(r->d_image, r->pm.width, r->pm.height, r->d_upscaled, r->full_w, r->full_h, st);
+    PT_CUDA_CHECK(cudaMemcpyAsync(host_dst, r->d_upscaled, px * 16, cudaMemcpyDeviceToHost, st));
     return pt_sync(r);
 }
 
@@ -444,7 +453,7 @@ int pt_set_accumulate(PtRenderer* r, int enabled) {
 
 int pt_reset_accum(PtRenderer* r) {
     PT_REQUIRE(r, "pt_reset_accum: null renderer");
-    if (r->d_accum) PT_CUDA_CHECK(cudaMemsetAsync(r->d_accum, 0, (size_t)r->pm.width * r->pm.height * 16, r->stream));
+    if (r->d_accum) PT_CUDA_CHECK(cudaMemsetAsync(r->d_accum, 0, (size_t)r->pm.width * r->pm.height * 16, follow_stream(r, nullptr)));
     r->accum_frames = 0;
     return PT_OK;
 }
@@ -468,8 +477,9 @@ int pt_read_accum_mean(PtRenderer* r, float* host_dst, uint32_t total_frames) {
     const uint32_t frames = total_frames ? total_frames : r->accum_frames;
     PT_REQUIRE(frames > 0, "pt_read_accum_mean: no frames accumulated");
     if (!r->d_upscaled || r->full_w * r->full_h < px) { cudaFree(r->d_upscaled); r->d_upscaled = nullptr; int rc = dev_alloc(&r->d_upscaled, std::max(px, (size_t)r->full_w * r->full_h) * 4); if (rc != PT_OK) return rc; }
-    launch_scale(r->d_accum, r->d_upscaled, (uint32_t)(px * 4), 1.0f / (float)frames, r->stream);
-    PT_CUDA_CHECK(cudaMemcpyAsync(host_dst, r->d_upscaled, px * 16, cudaMemcpyDeviceToHost, r->stream));
+    cudaStream_t st = follow_stream(r, nullptr);
+    launch_scale(r->d_accum, r->d_upscaled, (uint32_t)(px * 4), 1.0f / (float)frames, st);
+    PT_CUDA_CHECK(cudaMemcpyAsync(host_dst, r->d_upscaled, px * 16, cudaMemcpyDeviceToHost, st));
     return pt_sync(r);
 }
 
@@ -482,8 +492,7 @@ int pt_set_profiling(PtRenderer* r, int enabled) {
 int pt_get_stats(PtRenderer* r, PtStats* out) {
     PT_REQUIRE(r && out, "pt_get_stats: null argument");
     std::memset(out, 0, sizeof(*out));
-    PT_CUDA_CHECK(cudaSetDevice(r->device));
-    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     std::vector<uint32_t> q((size_t)r->max_iters + 2, 0);
     PT_CUDA_CHECK(cudaMemcpy(q.data(), r->pb.qcount, q.size() * 4, cudaMemcpyDeviceToHost));
     uint32_t its = 0;
@@ -537,8 +546,7 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
 
 int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t* rays) {
     PT_REQUIRE(r && r->have_last_cam, "pt_count_traversal: call pt_render first");
-    PT_CUDA_CHECK(cudaSetDevice(r->device));
-    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     PT_CUDA_CHECK(cudaMemsetAsync(r->pb.trav_counters, 0, 16, r->stream));
     const bool prof = r->profiling, acc = r->accumulate;
     r->profiling = false; r->accumulate = false;
