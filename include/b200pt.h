@@ -130,7 +130,8 @@ enum {
 enum {
     PT_FLAG_SORT_BY_MATERIAL = 1u << 0,   /* material-sorted shading queue */
     PT_FLAG_TRACE_BVH2 = 1u << 1,         /* use the simple BVH2 reference walker, not the BVH8 kernel */
-    PT_FLAG_NO_PRIMARY_REUSE = 1u << 2    /* re-trace the (identical) primary ray for every sample */
+    PT_FLAG_NO_PRIMARY_REUSE = 1u << 2,   /* re-trace the (identical) primary ray for every sample */
+    PT_FLAG_TRACE_WALKER = 1u << 3        /* simple one-ray-per-thread BVH8 walker instead of the persistent kernel */
 };
 
 typedef struct PtRenderConfig {
@@ -273,6 +274,10 @@ int pt_debug_bsdf(int device, size_t n, const float* normal3, const float* view3
 int pt_debug_rng(int device, size_t n, const uint32_t* pixel_xy_frame3, uint32_t draws, uint32_t* state2, float* xi2);
 int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t height, size_t n, const float* uv2,
                      float* rgba4);
+
+/* Process-wide kernel tuning knobs (measurement only; results never depend on them).
+ *   "postpone": K-trace postpones triangle tests while fewer than this many lanes have one pending. */
+int pt_set_option(const char* key, int value);
 
 /* Multi-GPU (one process per GPU).  Peer stores: rank 0 exports its image buffer as a CUDA IPC
  * handle, the other ranks open it and their accumulate kernel writes owned tiles straight into it

@@ -458,9 +458,11 @@ static inline RayPre ray_precompute(V3 d) {
     int ky = kx + 1; if (ky == 3) ky = 0;
     if (idx(d, kz) < 0.0f) std::swap(kx, ky);
     r.kx = kx; r.ky = ky; r.kz = kz;
-    r.Sx = idx(d, kx) / idx(d, kz);
-    r.Sy = idx(d, ky) / idx(d, kz);
+    // one correctly rounded division; the shear constants only have to be the same for every
+    // triangle the ray meets (that is what makes the test watertight), not exact quotients
     r.Sz = 1.0f / idx(d, kz);
+    r.Sx = idx(d, kx) * r.Sz;
+    r.Sy = idx(d, ky) * r.Sz;
     return r;
 }
 

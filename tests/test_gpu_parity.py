@@ -84,7 +84,7 @@ def test_texture_filter_matches_oracle():
 
 
 # ------------------------------------------------------------------ traversal kernel vs brute force
-@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_BVH2])
+@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2])
 @pytest.mark.parametrize("seed,ntri,nmesh,ninst", [(3, 3000, 3, 7), (5, 3, 3, 4), (11, 20000, 2, 40), (12, 64, 5, 1)])
 def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
     ps = S.random_soup(seed, ntri, nmesh, ninst).pack()
@@ -165,6 +165,8 @@ def test_c2_reference_walker_and_no_reuse_equivalence(sponza):
     ray for every sample, give the same image as the BVH8 kernel with primary-hit reuse."""
     a, ia, sa = render(sponza, 1920, 1080, 3, 3, frame=1)
     b, ib, sb_ = render(sponza, 1920, 1080, 3, 3, frame=1, flags=b200pt.PT_FLAG_TRACE_BVH2)
+    w, iw, sw = render(sponza, 1920, 1080, 3, 3, frame=1, flags=b200pt.PT_FLAG_TRACE_WALKER)
+    assert bits_equal(a, w).all() and all((x == y).all() for x, y in zip(ia, iw))
     c, ic, sc = render(sponza, 1920, 1080, 3, 3, frame=1, flags=b200pt.PT_FLAG_NO_PRIMARY_REUSE)
     assert bits_equal(a, b).all() and bits_equal(a, c).all()
     assert all((x == y).all() and (x == z).all() for x, y, z in zip(ia, ib, ic))

@@ -1,0 +1,42 @@
+"""Kernel-time sweeps on the C2 workload (run under gpurun): per-kernel CUDA-event times from pt_get_stats."""
+import os, sys, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "vulkan-pathtracer_b200"))
+import b200pt
+from tools import scene as S
+
+def measure(r, W, H, frames=8, warm=2):
+    r.set_profiling(True)
+    tr = sh = ot = 0.0; rays = 0
+    for f in range(warm + frames):
+        r.record(S.camera_default(W, H, f)); st = r.stats()
+        if f >= warm:
+            tr += st.ms_trace; sh += st.ms_shade; ot += st.ms_other; rays += st.rays_traced
+    return tr / frames, sh / frames, ot / frames, rays / frames
+
+def main():
+    what = sys.argv[1] if len(sys.argv) > 1 else "postpone"
+    name = sys.argv[2] if len(sys.argv) > 2 else "c2"
+    builder, W, H, spp, seg = S.CONFIGS[name]
+    ps = builder(1234).pack()
+    if what == "postpone":
+        r = b200pt.Renderer(ps, W, H, spp, seg)
+        ref = None
+        for v in (0, 2, 4, 6, 8, 12, 16, 20, 24, 33):
+            b200pt.set_option("postpone", v)
+            tr, sh, ot, rays = measure(r, W, H)
+            img = r.image()
+            if ref is None: ref = img
+            same = np.array_equal(ref.view(np.uint32), img.view(np.uint32))
+            print(f"postpone<{v:2d}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays  {rays/(tr*1e3):.0f} Mrays/s(trace)  same_image={same}")
+        r.deinit()
+    elif what == "modes":
+        for flags, label in ((0, "persistent"), (8, "walker"), (2, "bvh2")):
+            r = b200pt.Renderer(ps, W, H, spp, seg, flags=flags)
+            tr, sh, ot, rays = measure(r, W, H)
+            print(f"{label:10s}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}")
+            r.deinit()
+
+if __name__ == "__main__":
+    main()

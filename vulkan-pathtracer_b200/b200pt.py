@@ -27,7 +27,7 @@ from tools.scene import (PtCamera, PtInstance, PtMaterial, PtMesh, PtPrimitive, 
 LIB_PATH = os.path.join(_HERE, "libb200pt.so")
 
 PT_PARTITION_NONE, PT_PARTITION_TILES = 0, 1
-PT_FLAG_SORT_BY_MATERIAL, PT_FLAG_TRACE_BVH2, PT_FLAG_NO_PRIMARY_REUSE = 1, 2, 4
+PT_FLAG_SORT_BY_MATERIAL, PT_FLAG_TRACE_BVH2, PT_FLAG_NO_PRIMARY_REUSE, PT_FLAG_TRACE_WALKER = 1, 2, 4, 8
 
 PtHit_dtype = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("instance", "<u4"), ("primitive_index", "<u4"),
                         ("triangle_index", "<u4")])
@@ -263,6 +263,12 @@ def debug_texture(rgba, uv, device=0):
     fn.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p]
     check(fn(device, rgba.ctypes.data, rgba.shape[1], rgba.shape[0], len(uv), uv.ctypes.data, out.ctypes.data))
     return out
+
+
+def set_option(key, value):
+    fn = lib().pt_set_option
+    fn.argtypes = [C.c_char_p, C.c_int]
+    check(fn(key.encode(), int(value)))
 
 
 def write_pfm(path, rgba):

@@ -301,6 +301,7 @@ int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer
         if ((rc = alloc_frame(r, r->cfg.width, r->cfg.height, r->cfg.divider)) != PT_OK) break;
         if ((rc = dev_alloc(&r->d_cursor, 4)) != PT_OK) break;
         if (r->cfg.flags & PT_FLAG_TRACE_BVH2) r->trace_mode = TRACE_BVH2;
+        else if (r->cfg.flags & PT_FLAG_TRACE_WALKER) r->trace_mode = TRACE_BVH8_WALKER;
     } while (0);
     if (rc != PT_OK) { std::string keep = g_last_error; destroy_impl(r); g_last_error = keep; return rc; }
     *out = r;
@@ -528,7 +529,7 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
     cudaError_t e = cudaMemcpyAsync(d_rays, rays, n * sizeof(RayRec), cudaMemcpyHostToDevice, r->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(r->d_cursor, 0, 4, r->stream);
     if (e == cudaSuccess) {
-        launch_trace_rays(r->scene, d_rays, (uint32_t)n, d_hits, r->trace_mode == TRACE_BVH2 ? TRACE_BVH2 : TRACE_BVH8, r->bvh.tlas2_count,
+        launch_trace_rays(r->scene, d_rays, (uint32_t)n, d_hits, r->trace_mode, r->bvh.tlas2_count,
                           r->bvh.tlas2_leaf_instance, r->d_cursor, r->num_sms, r->stream);
         e = cudaGetLastError();
     }
@@ -630,6 +631,12 @@ int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t h
     if (!dt || !du || !dout) { set_error("pt_debug_texture: device allocation/copy failed"); return PT_ERR_CUDA; }
     launch_debug_texture(TexRec{dt, width, height}, (uint32_t)n, du, dout, nullptr);
     PT_CUDA_CHECK(cudaMemcpy(out, dout, 16 * n, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+int pt_set_option(const char* key, int value) {
+    PT_REQUIRE(key, "pt_set_option: null key");
+    if (set_option(key, value) != 0) { set_error(std::string("pt_set_option: unknown key ") + key); return PT_ERR_INVALID_ARGUMENT; }
     return PT_OK;
 }
 

@@ -1,9 +1,13 @@
 // render.cu — the wavefront trace loop: K-raygen, K-trace, K-shade (+ fused queue compaction and
 // pixel accumulation) and the image post-processing kernels.  Restates
 // src/shaders/ray_gen.rgen:33-105 as a per-pixel state machine driven by ray queues.
+#include <cstdlib>
+#include <cstring>
+
 #include "render.h"
 #include "shade.cuh"
 #include "trace.cuh"
+#include "trace_kernel.cuh"
 
 namespace pt {
 
@@ -319,6 +323,14 @@ int persistent_blocks(K kernel, int threads, int num_sms) {
 
 }  // namespace
 
+// tuning knobs (defaults chosen from the sweeps in profiles/); see pt_set_option
+static int g_postpone = 8;
+static uint32_t trace_postpone_threshold() { return (uint32_t)g_postpone; }
+int set_option(const char* key, int value) {
+    if (!strcmp(key, "postpone")) { g_postpone = value < 0 ? 0 : (value > 33 ? 33 : value); return 0; }
+    return -1;
+}
+
 void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st) {
     if (pm.num_slots == 0) return;
     k_raygen<<<(pm.num_slots + 255) / 256, 256, 0, st>>>(pm, pb, fp);
@@ -326,11 +338,20 @@ void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams&
 
 void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
                   const uint32_t* tlas2_leaf_instance, int num_sms, cudaStream_t st) {
-    static int blocks[3] = {0, 0, 0};
+    static int blocks[4] = {0, 0, 0, 0};
     if (!blocks[0]) {
         blocks[0] = persistent_blocks(k_trace<TRACE_BVH8>, kTraceThreads, num_sms);
         blocks[1] = persistent_blocks(k_trace<TRACE_BVH2>, kTraceThreads, num_sms);
         blocks[2] = persistent_blocks(k_trace<TRACE_BVH8_COUNT>, kTraceThreads, num_sms);
+        blocks[3] = persistent_blocks(k_trace_persistent, kTraceBlock, num_sms);
+    }
+    if (mode == TRACE_BVH8) {
+        TraceIO io;
+        io.queue = pb.queue[iter & 1u]; io.count_ptr = pb.qcount + iter; io.count = 0; io.cursor = pb.trace_next + iter;
+        io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
+        io.ray_stride = 1; io.hit_a_stride = 1; io.hit_b_stride = 1; io.postpone_below = trace_postpone_threshold();
+        k_trace_persistent<<<blocks[3], kTraceBlock, 0, st>>>(sc, io);
+        return;
     }
     if (mode == TRACE_BVH2) k_trace<TRACE_BVH2><<<blocks[1], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
     else if (mode == TRACE_BVH8_COUNT) k_trace<TRACE_BVH8_COUNT><<<blocks[2], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
@@ -347,6 +368,16 @@ void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& 
 void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
                        uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, int num_sms, cudaStream_t st) {
     const int blocks = num_sms * 4;
+    if (mode == TRACE_BVH8) {
+        static_assert(sizeof(RayRec) == 32 && sizeof(HitRec) == 32, "AoS strides");
+        TraceIO io;
+        io.queue = nullptr; io.count_ptr = nullptr; io.count = n; io.cursor = cursor;
+        io.ray_o = reinterpret_cast<const float4*>(rays); io.ray_d = io.ray_o + 1; io.ray_stride = 2;
+        io.hit_a = reinterpret_cast<float4*>(hits); io.hit_a_stride = 2;
+        io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4; io.postpone_below = trace_postpone_threshold();
+        k_trace_persistent<<<blocks, kTraceBlock, 0, st>>>(sc, io);
+        return;
+    }
     if (mode == TRACE_BVH2) k_trace_rays<TRACE_BVH2><<<blocks, kTraceThreads, 0, st>>>(sc, rays, n, hits, tlas2_count, tlas2_leaf_instance, cursor);
     else k_trace_rays<TRACE_BVH8><<<blocks, kTraceThreads, 0, st>>>(sc, rays, n, hits, tlas2_count, tlas2_leaf_instance, cursor);
 }

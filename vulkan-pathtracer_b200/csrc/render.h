@@ -40,7 +40,10 @@ struct FrameParams {
     uint32_t* id_tri;
 };
 
-enum TraceMode { TRACE_BVH8 = 0, TRACE_BVH2 = 1, TRACE_BVH8_COUNT = 2 };
+// TRACE_BVH8: persistent dynamic-fetch kernel (trace_kernel.cuh); TRACE_BVH8_WALKER: the simple
+// one-ray-per-thread walker of trace.cuh (TRACE_BVH8_COUNT: same, counting nodes/triangles);
+// TRACE_BVH2: walker over the LBVH binary trees.
+enum TraceMode { TRACE_BVH8 = 0, TRACE_BVH2 = 1, TRACE_BVH8_COUNT = 2, TRACE_BVH8_WALKER = 3 };
 
 void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st);
 void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
@@ -55,6 +58,9 @@ void launch_to_bgra8(const float* rgba, uint8_t* bgra, uint32_t n_pixels, cudaSt
 void launch_upscale(const float* src, uint32_t sw, uint32_t sh, float* dst, uint32_t dw, uint32_t dh, cudaStream_t st);
 void launch_accumulate(const float* frame, float* accum, uint32_t n_floats, cudaStream_t st);
 void launch_scale(const float* accum, float* out, uint32_t n_floats, float scale, cudaStream_t st);
+
+// kernel tuning knobs (pt_set_option)
+int set_option(const char* key, int value);
 
 // shading restatement on raw records (pt_debug_*)
 void launch_debug_bsdf(uint32_t n, const float* N, const float* V, const float* kd, const float* f0, const float* rough,

@@ -20,9 +20,11 @@ PT_D RayPre ray_precompute(V3 d) {
     int ky = kx + 1; if (ky == 3) ky = 0;
     if (comp(d, kz) < 0.0f) { int t = kx; kx = ky; ky = t; }
     r.kx = kx; r.ky = ky; r.kz = kz;
-    r.Sx = comp(d, kx) / comp(d, kz);
-    r.Sy = comp(d, ky) / comp(d, kz);
+    // one correctly rounded division (same definition as the oracle): watertightness only needs the
+    // same shear constants for every triangle the ray meets
     r.Sz = 1.0f / comp(d, kz);
+    r.Sx = comp(d, kx) * r.Sz;
+    r.Sy = comp(d, ky) * r.Sz;
     return r;
 }
 
@@ -84,9 +86,12 @@ struct RayFrame {
     uint32_t rs;     // octant: bit k set when d[k] >= 0
 };
 
+// reciprocal for the (conservative) box tests only: MUFU.RCP, <= 1 ulp, covered by the 2^-20 slab padding
 PT_D float safe_rcp(float d) {
     const float a = fabsf(d) < 1e-20f ? copysignf(1e-20f, d) : d;
-    return 1.0f / a;
+    float r;
+    asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
 }
 PT_D void frame_set(RayFrame& f, V3 o, V3 d) {
     f.o = o; f.d = d;

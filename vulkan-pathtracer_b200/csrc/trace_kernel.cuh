@@ -1,0 +1,225 @@
+// trace_kernel.cuh — K-trace: the persistent-thread BVH8 traversal kernel of the wavefront loop.
+//
+// Structure (evidence for each choice is in profiles/ and DESIGN.md §K-trace):
+//  * persistent warps; each warp owns a chunk of the ray queue taken with ONE global atomic per 128
+//    rays; lanes whose ray has terminated are refilled from the warp's chunk with a ballot (dynamic
+//    fetch, Aila & Laine 2009), so a warp never waits for its slowest ray;
+//  * every loop iteration a lane does at most one leaf item (triangle test / instance entry) and
+//    one node test, in two warp-wide phases, so lanes in the same phase execute together;
+//  * node test: 80-byte node as 5 x LDG.128, 8-bit planes converted with PRMT + FADD (no I2F on
+//    the quarter-rate pipe), branch-free hit-mask assembly, conservative slabs (explicit FMAs);
+//  * the traversal stack (node / leaf groups, 8 bytes each) lives in thread-local memory.
+// The closest-hit semantics are exactly those of trace_bvh8() in trace.cuh (the simple walker that
+// the tests and the algorithmic-byte counter use).
+#pragma once
+#include "trace.cuh"
+
+namespace pt {
+
+// byte j of `word` as the exact float 2^23 + q (bit pattern 0x4B0000qq): one PRMT, no I2F.  The
+// bias is folded into the plane offsets (c = b - 2^23*a, rounded away from the box), so
+// t = fma(2^23 + q, a, c) needs no subtraction; the directed rounding of c costs at most one grid
+// step of slack per plane.
+PT_D float q2f(uint32_t word, uint32_t j) {
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u | j));
+}
+
+PT_D uint32_t node_test_fast(const Bvh8Node* __restrict__ nodes, uint32_t idx, const RayFrame& f, float tmin, float tmax,
+                             uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
+    const uint4* q = reinterpret_cast<const uint4*>(nodes + idx);
+    const uint4 n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2), n3 = __ldg(q + 3), n4 = __ldg(q + 4);
+    child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24;
+    const float eps = 9.5367431640625e-7f;  // 2^-20
+    float anx, any, anz, afx, afy, afz, bnx, bny, bnz, bfx, bfy, bfz;
+    {
+        const float sx = __uint_as_float((n0.w & 0xffu) << 23), sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23),
+                    sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23);
+        const float ax = sx * f.idir.x, ay = sy * f.idir.y, az = sz * f.idir.z;
+        const float bx = (__uint_as_float(n0.x) - f.o.x) * f.idir.x, by = (__uint_as_float(n0.y) - f.o.y) * f.idir.y,
+                    bz = (__uint_as_float(n0.z) - f.o.z) * f.idir.z;
+        const float B23 = 8388608.0f;
+        anx = ax - fabsf(ax) * eps; afx = ax + fabsf(ax) * eps;
+        any = ay - fabsf(ay) * eps; afy = ay + fabsf(ay) * eps;
+        anz = az - fabsf(az) * eps; afz = az + fabsf(az) * eps;
+        bnx = __fsub_rd(bx - fabsf(bx) * eps, B23 * anx); bfx = __fsub_ru(bx + fabsf(bx) * eps, B23 * afx);
+        bny = __fsub_rd(by - fabsf(by) * eps, B23 * any); bfy = __fsub_ru(by + fabsf(by) * eps, B23 * afy);
+        bnz = __fsub_rd(bz - fabsf(bz) * eps, B23 * anz); bfz = __fsub_ru(bz + fabsf(bz) * eps, B23 * afz);
+    }
+    const bool px = (f.rs & 1u) != 0, py = (f.rs & 2u) != 0, pz = (f.rs & 4u) != 0;
+    const uint32_t rs4 = f.rs * 0x01010101u;
+    uint32_t hits = 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        // words holding children 4h..4h+3
+        const uint32_t lox = h ? n2.y : n2.x, loy = h ? n2.w : n2.z, loz = h ? n3.y : n3.x;
+        const uint32_t hix = h ? n3.w : n3.z, hiy = h ? n4.y : n4.x, hiz = h ? n4.w : n4.z;
+        const uint32_t nxw = px ? lox : hix, fxw = px ? hix : lox;
+        const uint32_t nyw = py ? loy : hiy, fyw = py ? hiy : loy;
+        const uint32_t nzw = pz ? loz : hiz, fzw = pz ? hiz : loz;
+        // hit-mask bit positions of the four children at once (byte-parallel): a child contributes
+        // (meta >> 5) << ((meta ^ x) & 31) with x = rs for inner slots (low5 = 24 + slot), 0 for leaves;
+        // empty slots (meta == 0) contribute nothing.
+        const uint32_t meta = h ? n1.w : n1.z;
+        const uint32_t inner4 = (meta & (meta << 1)) & 0x10101010u;        // low5 >= 24 <=> bits 3 and 4 set
+        const uint32_t idx4 = (meta ^ (((inner4 >> 4) * 7u) & rs4)) & 0x1F1F1F1Fu;
+        const uint32_t cnt4 = (meta >> 5) & 0x07070707u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float t0x = __fmaf_rn(q2f(nxw, j), anx, bnx), t0y = __fmaf_rn(q2f(nyw, j), any, bny), t0z = __fmaf_rn(q2f(nzw, j), anz, bnz);
+            const float t1x = __fmaf_rn(q2f(fxw, j), afx, bfx), t1y = __fmaf_rn(q2f(fyw, j), afy, bfy), t1z = __fmaf_rn(q2f(fzw, j), afz, bfz);
+            const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+            const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+            const uint32_t bits = ((cnt4 >> (8 * j)) & 0xffu) << ((idx4 >> (8 * j)) & 0xffu);
+            hits |= (tn <= tf) ? bits : 0u;
+        }
+    }
+    return hits;
+}
+
+struct TraceIO {
+    const uint32_t* queue;      // slot per queue entry, or nullptr for identity
+    const uint32_t* count_ptr;  // number of entries (device), or nullptr -> count
+    uint32_t count;
+    uint32_t* cursor;           // dynamic-fetch cursor (zeroed before the launch)
+    const float4* ray_o;        // per slot: origin.xyz, tmin
+    const float4* ray_d;        // per slot: direction.xyz, tmax
+    float4* hit_a;              // per slot: t, b1, b2, instance
+    uint2* hit_b;               // per slot: primitive_index, triangle_index
+    uint32_t ray_stride;        // in float4: 1 = SoA path buffers, 2 = RayRec array (ray_d = ray_o + 1)
+    uint32_t hit_a_stride;      // in float4: 1 = SoA, 2 = HitRec array
+    uint32_t hit_b_stride;      // in uint2:  1 = SoA, 4 = HitRec array (hit_b = base + 2)
+    uint32_t postpone_below;    // triangle tests are postponed while fewer lanes than this have one pending
+};
+
+constexpr int kTraceBlock = 128;
+constexpr uint32_t kChunk = 128;   // rays per global atomic
+constexpr int kStackSize = 64;
+
+__global__ void __launch_bounds__(kTraceBlock) k_trace_persistent(DeviceScene sc, TraceIO io) {
+    const uint32_t n = io.count_ptr ? *io.count_ptr : io.count;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    if (sc.tlas_root == kInvalidId) {
+        // no geometry: every ray misses
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+            const uint32_t slot = io.queue ? io.queue[i] : i;
+            io.hit_a[(size_t)slot * io.hit_a_stride] = make_float4(kMissT, 0.0f, 0.0f, __uint_as_float(kInvalidId));
+            io.hit_b[(size_t)slot * io.hit_b_stride] = make_uint2(kInvalidId, kInvalidId);
+        }
+        return;
+    }
+    // warp-uniform chunk of the queue
+    uint32_t w_next = 0, w_end = 0;
+    bool exhausted = false;
+    // per-lane ray state
+    bool active = false;
+    uint32_t slot = 0;
+    RayFrame world, f;
+    RayPre rp;
+    float tmin = 0.0f, tmax = 0.0f;
+    uint32_t cur_inst = kInvalidId;
+    Hit best;
+    uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
+    uint2 stack[kStackSize];
+    int sp = 0;
+    hit_init(best);
+    frame_set(world, v3s(0.0f), v3(0.0f, 0.0f, 1.0f));
+    f = world;
+    rp = ray_precompute(world.d);
+
+    for (;;) {
+        // ---- dynamic fetch: refill idle lanes from the warp's chunk
+        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        if (idle != 0u && !exhausted) {
+            if (w_next == w_end) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(io.cursor, kChunk);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (base >= n) exhausted = true;
+                else { w_next = base; w_end = min(base + kChunk, n); }
+            }
+            if (!exhausted) {
+                const uint32_t want = __popc(idle);
+                const uint32_t avail = w_end - w_next;
+                if (!active) {
+                    const uint32_t rank = __popc(idle & lt_mask);
+                    if (rank < avail) {
+                        const uint32_t qi = w_next + rank;
+                        slot = io.queue ? io.queue[qi] : qi;
+                        const float4 ro = io.ray_o[(size_t)slot * io.ray_stride], rd = io.ray_d[(size_t)slot * io.ray_stride];
+                        frame_set(world, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z));
+                        f = world;
+                        tmin = ro.w; tmax = rd.w;
+                        cur_inst = kInvalidId;
+                        hit_init(best);
+                        sp = 0;
+                        G = make_uint2(sc.tlas_root, 0x80000000u);
+                        T = make_uint2(0u, 0u);
+                        active = true;
+                    }
+                }
+                w_next += min(want, avail);
+            }
+        }
+        if (idle == 0xffffffffu && __ballot_sync(0xffffffffu, active) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        // ---- phase 1: one leaf item.  Triangle tests run at low SIMD utilisation when only a few
+        // lanes have one pending: such lanes postpone the group (push it) and keep descending
+        // (Ylitie et al. 2017, "postponing"); a popped group is always tested (no node work left).
+        const bool has_t = active && T.y != 0u;
+        const uint32_t n_t = __popc(__ballot_sync(0xffffffffu, has_t));
+        if (has_t && n_t < io.postpone_below && cur_inst != kInvalidId && (G.y & 0xFF000000u) != 0u && sp < kStackSize) {
+            stack[sp++] = T;
+            T.y = 0u;
+        } else if (has_t) {
+            const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
+            T.y &= T.y - 1u;
+            if (cur_inst != kInvalidId) {
+                test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
+            } else {
+                // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
+                if (T.y && sp < kStackSize) stack[sp++] = T;
+                if ((G.y & 0xFF000000u) && sp < kStackSize) stack[sp++] = G;
+                if (sp < kStackSize) stack[sp++] = make_uint2(0xFFFFFFFFu, 0u);
+                cur_inst = __ldg(sc.tlas_leaf_instance + T.x + b);
+                V3 oo, dd;
+                to_object(sc.instances, cur_inst, world.o, world.d, oo, dd);
+                frame_set(f, oo, dd);
+                rp = ray_precompute(dd);
+                G = make_uint2(__ldg(&sc.instances[cur_inst].blas_root), 0x80000000u);
+                T = make_uint2(0u, 0u);
+            }
+        }
+        // ---- pop when there is nothing else to do
+        if (active && T.y == 0u && (G.y & 0xFF000000u) == 0u) {
+            for (;;) {
+                if (sp == 0) {
+                    io.hit_a[(size_t)slot * io.hit_a_stride] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.inst));
+                    io.hit_b[(size_t)slot * io.hit_b_stride] = make_uint2(best.prim, best.tri);
+                    active = false;
+                    break;
+                }
+                const uint2 e = stack[--sp];
+                if (e.x == 0xFFFFFFFFu && e.y == 0u) { f = world; cur_inst = kInvalidId; continue; }
+                if (e.y & 0xFF000000u) { G = e; } else { T = e; }
+                break;
+            }
+        }
+        // ---- phase 2: one node test
+        if (active && T.y == 0u && (G.y & 0xFF000000u) != 0u) {
+            const uint32_t k = 31u - (uint32_t)__clz(G.y);
+            G.y &= ~(1u << k);
+            const uint32_t s = (k - 24u) ^ f.rs;
+            const uint32_t node = G.x + __popc(G.y & 0xffu & ((1u << s) - 1u));
+            if ((G.y & 0xFF000000u) && sp < kStackSize) stack[sp++] = G;
+            uint32_t cb, tb, im;
+            const uint32_t hits = node_test_fast(sc.nodes, node, f, tmin, fminf(tmax, best.t), cb, tb, im);
+            G = make_uint2(cb, (hits & 0xFF000000u) | im);
+            T = make_uint2(tb, hits & 0x00FFFFFFu);
+        }
+    }
+}
+
+}  // namespace pt
