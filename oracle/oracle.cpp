@@ -55,7 +55,8 @@ static inline float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; 
 static inline V3 cross(V3 a, V3 b) {
     return V3{a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y};
 }
-static inline V3 normalize(V3 a) { return a / std::sqrt(dot(a, a)); }
+// normalize(v) = v * (1 / sqrt(dot(v, v))): one correctly rounded division (arithmetic contract)
+static inline V3 normalize(V3 a) { return a * (1.0f / std::sqrt(dot(a, a))); }
 static inline float gmin(float x, float y) { return (y < x) ? y : x; }
 static inline float gmax(float x, float y) { return (x < y) ? y : x; }
 static inline float mixf(float a, float b, float t) { return a * (1.0f - t) + b * t; }

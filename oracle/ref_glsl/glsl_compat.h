@@ -60,7 +60,7 @@ inline float min(float x, float y) { return (y < x) ? y : x; }     // GLSL 8.3
 inline float max(float x, float y) { return (x < y) ? y : x; }
 inline float mix(float a, float b, float t) { return a * (1.0f - t) + b * t; }
 inline vec3 mix(vec3 a, vec3 b, float t) { return vec3(mix(a.x, b.x, t), mix(a.y, b.y, t), mix(a.z, b.z, t)); }
-inline vec3 normalize(vec3 v) { return v / sqrt(dot(v, v)); }
+inline vec3 normalize(vec3 v) { return v * (1.0f / sqrt(dot(v, v))); }   // contract: one division
 inline vec3 reflect(vec3 I, vec3 N) { return I - 2.0f * dot(N, I) * N; }
 
 struct mat3 {

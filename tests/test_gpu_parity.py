@@ -83,6 +83,17 @@ def test_texture_filter_matches_oracle():
         assert bits_equal(got, ref).all()
 
 
+def test_unorm8_conversion_is_exact():
+    """texel / 255.0 is evaluated without the IEEE division sequence; it must equal it for all 256 bytes."""
+    tex = np.zeros((1, 256, 4), np.uint8)
+    v = np.arange(256, dtype=np.uint8)
+    tex[0, :, 0] = v; tex[0, :, 1] = v[::-1]; tex[0, :, 2] = v ^ 0x55; tex[0, :, 3] = 255 - (v >> 1)
+    uv = np.stack([(np.arange(256) + 0.5) / 256.0, np.full(256, 0.5)], axis=1).astype(np.float32)   # texel centres: weights 1,0,0,0
+    got = b200pt.debug_texture(tex, uv)
+    want = tex[0].astype(np.float32) / np.float32(255.0)
+    assert bits_equal(got, want).all()
+
+
 # ------------------------------------------------------------------ traversal kernel vs brute force
 @pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2])
 @pytest.mark.parametrize("seed,ntri,nmesh,ninst", [(3, 3000, 3, 7), (5, 3, 3, 4), (11, 20000, 2, 40), (12, 64, 5, 1)])

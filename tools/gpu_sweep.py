@@ -31,6 +31,11 @@ def main():
             same = np.array_equal(ref.view(np.uint32), img.view(np.uint32))
             print(f"postpone<{v:2d}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays  {rays/(tr*1e3):.0f} Mrays/s(trace)  same_image={same}")
         r.deinit()
+    elif what == "one":
+        r = b200pt.Renderer(ps, W, H, spp, seg)
+        tr, sh, ot, rays = measure(r, W, H)
+        print(f"trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays")
+        r.deinit()
     elif what == "modes":
         for flags, label in ((0, "persistent"), (8, "walker"), (2, "bvh2")):
             r = b200pt.Renderer(ps, W, H, spp, seg, flags=flags)

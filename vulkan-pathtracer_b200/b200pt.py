@@ -24,7 +24,8 @@ if _ROOT not in sys.path:
 from tools.scene import (PtCamera, PtInstance, PtMaterial, PtMesh, PtPrimitive, PtRenderConfig,  # noqa: E402,F401
                          PtSceneDesc, PtTexture)
 
-LIB_PATH = os.path.join(_HERE, "libb200pt.so")
+# B200PT_LIB selects an alternative build of the same library (A/B kernel experiments)
+LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(_HERE, "libb200pt.so")
 
 PT_PARTITION_NONE, PT_PARTITION_TILES = 0, 1
 PT_FLAG_SORT_BY_MATERIAL, PT_FLAG_TRACE_BVH2, PT_FLAG_NO_PRIMARY_REUSE, PT_FLAG_TRACE_WALKER = 1, 2, 4, 8

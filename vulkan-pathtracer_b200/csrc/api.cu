@@ -28,7 +28,7 @@ struct PtRenderer {
     // scene on the device
     uint8_t* d_blob = nullptr;
     PrimRec* d_prims = nullptr;
-    PtMaterial* d_materials = nullptr;
+    MatRec* d_materials = nullptr;
     TexRec* d_textures = nullptr;
     std::vector<uint32_t*> d_texels;
     PtInstance* d_instances_raw = nullptr;
@@ -157,8 +157,6 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
         for (uint32_t v : t)
             if (v != PT_INVALID_TEXTURE && v >= s->num_textures) { set_error("material " + std::to_string(i) + ": texture index out of range"); return PT_ERR_INVALID_ARGUMENT; }
     }
-    if ((rc = dev_alloc(&r->d_materials, s->num_materials)) != PT_OK) return rc;
-    if (s->num_materials) PT_CUDA_CHECK(cudaMemcpy(r->d_materials, s->materials, s->num_materials * sizeof(PtMaterial), cudaMemcpyHostToDevice));
     std::vector<TexRec> texs(s->num_textures);
     r->d_texels.assign(s->num_textures, nullptr);
     for (size_t i = 0; i < s->num_textures; ++i) {
@@ -171,6 +169,16 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     }
     if ((rc = dev_alloc(&r->d_textures, texs.size())) != PT_OK) return rc;
     if (!texs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_textures, texs.data(), texs.size() * sizeof(TexRec), cudaMemcpyHostToDevice));
+    std::vector<MatRec> mats(s->num_materials);
+    for (size_t i = 0; i < s->num_materials; ++i) {
+        const PtMaterial& m = s->materials[i];
+        MatRec& d = mats[i];
+        d.albedo_factor = m.albedo_factor; d.metal_roughness_factor = m.metal_roughness_factor; d.emissive_factor = m.emissive_factor; d._pad = 0;
+        const uint32_t t[4] = {m.albedo_texture_index, m.metal_roughness_texture_index, m.emissive_texture_index, m.normal_texture_index};
+        for (int k = 0; k < 4; ++k) d.tex[k] = (t[k] == PT_INVALID_TEXTURE) ? TexRec{nullptr, 0, 0} : texs[t[k]];
+    }
+    if ((rc = dev_alloc(&r->d_materials, mats.size())) != PT_OK) return rc;
+    if (!mats.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_materials, mats.data(), mats.size() * sizeof(MatRec), cudaMemcpyHostToDevice));
     // meshes / instances
     std::vector<PtMesh> meshes(s->meshes, s->meshes + s->num_meshes);
     for (size_t m = 0; m < meshes.size(); ++m)

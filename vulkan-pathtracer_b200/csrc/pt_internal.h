@@ -73,10 +73,19 @@ struct __align__(16) PrimRec {
 
 struct TexRec { const uint32_t* texels; uint32_t width, height; };  // RGBA8 packed, row 0 first
 
+// Device material: the reference's 28-byte Material (material.glsl:7-16) with the four texture
+// indices resolved to texel pointers + extents (texels == nullptr: no texture), so that shading
+// needs one dependent load less per texture.  80 bytes, 16-byte aligned.
+struct __align__(16) MatRec {
+    uint32_t albedo_factor, metal_roughness_factor, emissive_factor, _pad;
+    TexRec tex[4];   // albedo, metal-roughness, emissive, normal
+};
+static_assert(sizeof(MatRec) == 80, "MatRec must be 80 bytes");
+
 struct DeviceScene {
     const uint8_t* triangle_data;
     const PrimRec* prims;
-    const PtMaterial* materials;
+    const MatRec* materials;
     const TexRec* textures;
     const InstanceRec* instances;
     const Bvh8Node* nodes;       // all BLASes + TLAS

@@ -30,7 +30,8 @@ PT_HD V3 operator/(V3 a, float s) { return v3(a.x / s, a.y / s, a.z / s); }
 PT_HD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
 PT_HD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 PT_HD V3 cross(V3 a, V3 b) { return v3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
-PT_HD V3 normalize(V3 a) { return a / sqrtf(dot(a, a)); }
+// normalize(v) = v * (1 / sqrt(dot(v, v))): one correctly rounded division (arithmetic contract)
+PT_HD V3 normalize(V3 a) { return a * (1.0f / sqrtf(dot(a, a))); }
 PT_HD float gmin(float x, float y) { return (y < x) ? y : x; }
 PT_HD float gmax(float x, float y) { return (x < y) ? y : x; }
 PT_HD float mixf(float a, float b, float t) { return a * (1.0f - t) + b * t; }

@@ -143,7 +143,12 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_rays(DeviceScene sc, co
 // bounce loop (ray_gen.rgen:65-97), and either emits the next ray (appended to the next queue) or
 // ends the sample; a finished sample restarts from the cached primary hit (every sample of a pixel
 // shoots the same primary ray, quirk Q1) until NUM_SAMPLES are done, then the pixel is stored.
-__global__ void __launch_bounds__(kShadeThreads) k_shade(DeviceScene sc, PixelMap pm, PathBuffers pb, FrameParams fp, uint32_t iter) {
+#ifdef PT_SHADE_MIN_BLOCKS
+#define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, PT_SHADE_MIN_BLOCKS)
+#else
+#define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, 4)   // 128 regs, no spills: with all texel loads in flight ILP beats occupancy (profiles/)
+#endif
+__global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers pb, FrameParams fp, uint32_t iter) {
     const uint32_t n = pb.qcount[iter];
     const uint32_t* __restrict__ qin = pb.queue[iter & 1u];
     uint32_t* __restrict__ qout = pb.queue[(iter + 1u) & 1u];

@@ -237,10 +237,20 @@ PT_D TriangleData get_triangle_data(const DeviceScene& sc, const HitRec& h) {
 }
 
 // ------------------------------------------------------------------ material.glsl
+// x / 255.0f, correctly rounded, for x in 0..255 without the IEEE division sequence: q = x * RN(1/255)
+// followed by one Newton correction with exact remainders (explicit FMAs).  Exhaustively equal to
+// (float)x / 255.0f for all 256 inputs (tests/test_gpu_parity.py::test_unorm8_conversion_is_exact).
+PT_D float unorm8(uint32_t x) {
+    const float xf = __uint_as_float(0x4B000000u | x) - 8388608.0f;   // exact int -> float without I2F
+    const float r = 1.0f / 255.0f;
+    const float q = xf * r;
+    const float rem = __fmaf_rn(-q, 255.0f, xf);
+    return __fmaf_rn(rem, r, q);
+}
 PT_D V4 unpack_unorm4x8(uint32_t p) {
     V4 r;
-    r.x = (float)(p & 0xff) / 255.0f; r.y = (float)((p >> 8) & 0xff) / 255.0f;
-    r.z = (float)((p >> 16) & 0xff) / 255.0f; r.w = (float)(p >> 24) / 255.0f;
+    r.x = unorm8(p & 0xff); r.y = unorm8((p >> 8) & 0xff);
+    r.z = unorm8((p >> 16) & 0xff); r.w = unorm8(p >> 24);
     return r;
 }
 
@@ -249,22 +259,31 @@ PT_D V4 unpack_unorm4x8(uint32_t p) {
 // four point fetches (the hardware bilinear path uses 1.8 fixed-point weights).
 PT_D uint32_t wrap_texel(float f, uint32_t n) {
     if (!(f >= -2147483648.0f && f < 2147483648.0f)) return 0u;
-    int i = (int)f;
+    const int i = (int)f;
+    if ((n & (n - 1u)) == 0u) return (uint32_t)i & (n - 1u);   // power of two: same result as the modulo
     int m = i % (int)n;
     if (m < 0) m += (int)n;
     return (uint32_t)m;
 }
-PT_D V4 sample_texture(const TexRec& tex, V2 uv) {
+// The four texel fetches of one bilinear tap, separated from the filter arithmetic so that the loads
+// of all textures of a material are in flight together (the kernel is latency bound).
+struct Taps { uint32_t t00, t10, t01, t11; float a, b; };
+PT_D Taps fetch_taps(const TexRec& tex, V2 uv) {
     const float W = (float)tex.width, H = (float)tex.height;
     const float u = uv.x * W - 0.5f, v = uv.y * H - 0.5f;
     const float fu = floorf(u), fv = floorf(v);
-    const float a = u - fu, b = v - fv;
+    Taps t;
+    t.a = u - fu; t.b = v - fv;
     const uint32_t x0 = wrap_texel(fu, tex.width), x1 = (x0 + 1 == tex.width) ? 0u : x0 + 1;
     const uint32_t y0 = wrap_texel(fv, tex.height), y1 = (y0 + 1 == tex.height) ? 0u : y0 + 1;
     const uint32_t* r0 = tex.texels + (size_t)y0 * tex.width;
     const uint32_t* r1 = tex.texels + (size_t)y1 * tex.width;
-    const V4 t00 = unpack_unorm4x8(__ldg(r0 + x0)), t10 = unpack_unorm4x8(__ldg(r0 + x1));
-    const V4 t01 = unpack_unorm4x8(__ldg(r1 + x0)), t11 = unpack_unorm4x8(__ldg(r1 + x1));
+    t.t00 = __ldg(r0 + x0); t.t10 = __ldg(r0 + x1); t.t01 = __ldg(r1 + x0); t.t11 = __ldg(r1 + x1);
+    return t;
+}
+PT_D V4 filter_taps(const Taps& t) {
+    const V4 t00 = unpack_unorm4x8(t.t00), t10 = unpack_unorm4x8(t.t10), t01 = unpack_unorm4x8(t.t01), t11 = unpack_unorm4x8(t.t11);
+    const float a = t.a, b = t.b;
     const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
     V4 r;
     r.x = t00.x * w00 + t10.x * w10 + t01.x * w01 + t11.x * w11;
@@ -273,33 +292,46 @@ PT_D V4 sample_texture(const TexRec& tex, V2 uv) {
     r.w = t00.w * w00 + t10.w * w10 + t01.w * w01 + t11.w * w11;
     return r;
 }
+PT_D V4 sample_texture(const TexRec& tex, V2 uv) { return filter_taps(fetch_taps(tex, uv)); }
 
 struct MaterialData { V4 albedo; V3 normal, emissive; float roughness, metallic; };
 
 // material.glsl:31-69
 PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& td) {
-    const PtMaterial m = sc.materials[td.material_index];
+    const MatRec* mp = sc.materials + td.material_index;
+    const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));     // factors
+    TexRec tex[4];
+    Taps taps[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint4 w = __ldg(reinterpret_cast<const uint4*>(mp) + 1 + k);
+        tex[k].texels = reinterpret_cast<const uint32_t*>(((uint64_t)w.y << 32) | w.x);
+        tex[k].width = w.z; tex[k].height = w.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (tex[k].texels) taps[k] = fetch_taps(tex[k], td.uv);
     MaterialData md;
-    md.albedo = unpack_unorm4x8(m.albedo_factor);                                       // :36
-    if (m.albedo_texture_index != PT_INVALID_TEXTURE) {                                  // :37-39
-        V4 t = sample_texture(sc.textures[m.albedo_texture_index], td.uv);
+    md.albedo = unpack_unorm4x8(fac.x);                                                  // :36
+    if (tex[0].texels) {                                                                 // :37-39
+        const V4 t = filter_taps(taps[0]);
         md.albedo.x *= t.x; md.albedo.y *= t.y; md.albedo.z *= t.z; md.albedo.w *= t.w;
     }
-    const V4 mr = unpack_unorm4x8(m.metal_roughness_factor);                             // :41-43
+    const V4 mr = unpack_unorm4x8(fac.y);                                                // :41-43
     md.roughness = mr.y; md.metallic = mr.z;
-    if (m.metal_roughness_texture_index != PT_INVALID_TEXTURE) {                         // :44-48
-        V4 t = sample_texture(sc.textures[m.metal_roughness_texture_index], td.uv);
+    if (tex[1].texels) {                                                                 // :44-48
+        const V4 t = filter_taps(taps[1]);
         md.roughness *= t.y; md.metallic *= t.z;
     }
-    const V4 e = unpack_unorm4x8(m.emissive_factor);                                     // :50
+    const V4 e = unpack_unorm4x8(fac.z);                                                 // :50
     md.emissive = v3(e.x, e.y, e.z);
-    if (m.emissive_texture_index != PT_INVALID_TEXTURE) {                                // :51-53
-        V4 t = sample_texture(sc.textures[m.emissive_texture_index], td.uv);
+    if (tex[2].texels) {                                                                 // :51-53
+        const V4 t = filter_taps(taps[2]);
         md.emissive = md.emissive * v3(t.x, t.y, t.z);
     }
     md.normal = td.normal;                                                               // :55
-    if (m.normal_texture_index != PT_INVALID_TEXTURE) {                                  // :56-66
-        V4 t = sample_texture(sc.textures[m.normal_texture_index], td.uv);
+    if (tex[3].texels) {                                                                 // :56-66
+        const V4 t = filter_taps(taps[3]);
         const V3 nts = v3(t.x, t.y, t.z);
         const V3 T = v3(td.tangent.x, td.tangent.y, td.tangent.z);
         const V3 bitangent = cross(td.normal, T) * td.tangent.w;

@@ -95,7 +95,12 @@ constexpr int kTraceBlock = 128;
 constexpr uint32_t kChunk = 128;   // rays per global atomic
 constexpr int kStackSize = 64;
 
-__global__ void __launch_bounds__(kTraceBlock) k_trace_persistent(DeviceScene sc, TraceIO io) {
+#ifdef PT_TRACE_MIN_BLOCKS
+#define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock, PT_TRACE_MIN_BLOCKS)
+#else
+#define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock)
+#endif
+__global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     const uint32_t n = io.count_ptr ? *io.count_ptr : io.count;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
