@@ -76,7 +76,7 @@ int dev_alloc(T** p, size_t count) {
 
 void free_frame(PtRenderer* r) {
     PathBuffers& b = r->pb;
-    cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b);
+    cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.ray_e); cudaFree(b.ray_s); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b);
     cudaFree(b.atten_sx); cudaFree(b.color_sy); cudaFree(b.final_sb); cudaFree(b.queue[0]); cudaFree(b.queue[1]);
     cudaFree(b.qcount); cudaFree(b.trace_next); cudaFree(b.trav_counters);
     b = PathBuffers{};
@@ -108,7 +108,7 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
     PathBuffers& b = r->pb;
     int rc;
 #define A(ptr, cnt) if ((rc = dev_alloc(&(ptr), (cnt))) != PT_OK) return rc
-    A(b.ray_o, n); A(b.ray_d, n); A(b.hit_a, n); A(b.hit_b, n); A(b.prim_a, n); A(b.prim_b, n);
+    A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.hit_a, n); A(b.hit_b, n); A(b.prim_a, n); A(b.prim_b, n);
     A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n);
     A(b.qcount, (size_t)r->max_iters + 2); A(b.trace_next, (size_t)r->max_iters + 2); A(b.trav_counters, 4);
     const size_t px = (size_t)pm.width * pm.height;
@@ -201,7 +201,9 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
         for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) ir.inv[3 * rr + c] = Ai.m[rr][c];
         ir.inv[9] = t[3]; ir.inv[10] = t[7]; ir.inv[11] = t[11];
         const uint32_t m = (uint32_t)inst[i].mesh_index;
-        ir.mesh = m;
+        bool identity = t[3] == 0.0f && t[7] == 0.0f && t[11] == 0.0f;
+        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) identity = identity && Ai.m[rr][c] == (rr == c ? 1.0f : 0.0f);
+        ir.mesh = m | (identity ? kInstIdentity : 0u);
         ir.blas_root = r->bvh.blas_root8[m];
         ir.bvh2_root = r->bvh.tri_off[m];
         ir.bvh2_tri_base = r->bvh.tri_off[m];
@@ -529,22 +531,23 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
     PT_REQUIRE(n < 0xFFFFFF00ull, "pt_trace_rays: too many rays");
     if (n == 0) return PT_OK;
     PT_CUDA_CHECK(cudaSetDevice(r->device));
-    RayRec* d_rays = nullptr; HitRec* d_hits = nullptr;
+    RayRec* d_rays = nullptr; HitRec* d_hits = nullptr; float4* d_setup = nullptr;
     int rc;
     if ((rc = dev_alloc(&d_rays, n)) != PT_OK) return rc;
     if ((rc = dev_alloc(&d_hits, n)) != PT_OK) { cudaFree(d_rays); return rc; }
+    if ((rc = dev_alloc(&d_setup, 4 * n)) != PT_OK) { cudaFree(d_rays); cudaFree(d_hits); return rc; }
     static_assert(sizeof(PtRay) == sizeof(RayRec), "PtRay layout");
     cudaError_t e = cudaMemcpyAsync(d_rays, rays, n * sizeof(RayRec), cudaMemcpyHostToDevice, r->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(r->d_cursor, 0, 4, r->stream);
     if (e == cudaSuccess) {
         launch_trace_rays(r->scene, d_rays, (uint32_t)n, d_hits, r->trace_mode, r->bvh.tlas2_count,
-                          r->bvh.tlas2_leaf_instance, r->d_cursor, r->num_sms, r->stream);
+                          r->bvh.tlas2_leaf_instance, r->d_cursor, d_setup, r->num_sms, r->stream);
         e = cudaGetLastError();
     }
     std::vector<HitRec> tmp(n);
     if (e == cudaSuccess) e = cudaMemcpyAsync(tmp.data(), d_hits, n * sizeof(HitRec), cudaMemcpyDeviceToHost, r->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
-    cudaFree(d_rays); cudaFree(d_hits);
+    cudaFree(d_rays); cudaFree(d_hits); cudaFree(d_setup);
     if (e != cudaSuccess) { set_error(std::string("pt_trace_rays: ") + cudaGetErrorString(e)); return PT_ERR_CUDA; }
     for (size_t i = 0; i < n; ++i) {
         hits[i].t = tmp[i].t; hits[i].b1 = tmp[i].b1; hits[i].b2 = tmp[i].b2; hits[i].instance = tmp[i].instance;

@@ -59,10 +59,13 @@ struct __align__(16) InstanceRec {
     float inv[12];       // rows of [Ainv | -Ainv*T is NOT folded: o' = Ainv*(o - T)]: inv[0..8] = Ainv row-major, inv[9..11] = T
     uint32_t blas_root;  // BVH8 node index of the mesh's root
     uint32_t bvh2_root;  // BVH2 node index (reference walker)
-    uint32_t mesh;
+    uint32_t mesh;       // mesh index | kInstIdentity
     uint32_t bvh2_tri_base;  // first sorted triangle of the mesh (BVH2 leaves)
 };
 static_assert(sizeof(InstanceRec) == 64, "InstanceRec must be 64 bytes");
+// set in InstanceRec::mesh when Ainv is exactly the identity and T is zero: object space == world
+// space bit for bit, so K-trace enters the BLAS without re-deriving the ray frame
+constexpr uint32_t kInstIdentity = 0x80000000u;
 
 // Device-side primitive record: byte offsets into the triangle_data blob (the reference keeps 5
 // device addresses, RaytracingPass.zig:18-31; offsets suffice with one blob).  32 bytes.

@@ -99,6 +99,22 @@ PT_D void frame_set(RayFrame& f, V3 o, V3 d) {
     f.rs = (f.idir.x >= 0.0f ? 1u : 0u) | (f.idir.y >= 0.0f ? 2u : 0u) | (f.idir.z >= 0.0f ? 4u : 0u);
 }
 
+// Producer side of K-trace's ray fetch: the world-space ray with everything the traversal derives
+// from it (box-test reciprocals + octant, watertight shear constants), 64 bytes per slot.  Computed
+// where rays are born (K-raygen / K-shade / k_ray_setup, all lanes busy) instead of in K-trace,
+// where refilled lanes would do it two at a time (profiles/r1a: 22 % of K-trace's issue slots).
+PT_D void store_ray(float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ ray_e, float4* __restrict__ ray_s,
+                    uint32_t slot, V3 o, V3 d, float tmin, float tmax) {
+    RayFrame f;
+    frame_set(f, o, d);
+    const RayPre rp = ray_precompute(d);
+    const uint32_t bits = f.rs | ((uint32_t)rp.kx << 3) | ((uint32_t)rp.ky << 5) | ((uint32_t)rp.kz << 7);
+    ray_o[slot] = make_float4(o.x, o.y, o.z, tmin);
+    ray_d[slot] = make_float4(d.x, d.y, d.z, tmax);
+    ray_e[slot] = make_float4(f.idir.x, f.idir.y, f.idir.z, __uint_as_float(bits));
+    ray_s[slot] = make_float4(rp.Sx, rp.Sy, rp.Sz, 0.0f);
+}
+
 // world -> object: o' = Ainv*(o - T), d' = Ainv*d (not renormalised: t is shared between spaces).
 // Same expression as the oracle.
 PT_D void to_object(const InstanceRec* __restrict__ inst, uint32_t i, V3 o, V3 d, V3& oo, V3& dd) {

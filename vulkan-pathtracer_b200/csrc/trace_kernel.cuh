@@ -20,12 +20,16 @@ namespace pt {
 // bias is folded into the plane offsets (c = b - 2^23*a, rounded away from the box), so
 // t = fma(2^23 + q, a, c) needs no subtraction; the directed rounding of c costs at most one grid
 // step of slack per plane.
-PT_D float q2f(uint32_t word, uint32_t j) {
-    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u | j));
+// `bias` holds 0x4B000000 in a register the compiler cannot fold (it comes from the kernel
+// parameters): PRMT then takes the selector as its immediate — with a literal bias ptxas puts the
+// literal in the immediate slot and re-materialises the selector with a MOV before every PRMT
+// (profiles/r1a: 48 extra MOV/IMAD.U32 per node test).
+PT_D float q2f(uint32_t word, uint32_t j, uint32_t bias) {
+    return __uint_as_float(__byte_perm(word, bias, 0x7650u | j));
 }
 
 PT_D uint32_t node_test_fast(const Bvh8Node* __restrict__ nodes, uint32_t idx, const RayFrame& f, float tmin, float tmax,
-                             uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
+                             uint32_t bias, uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
     const uint4* q = reinterpret_cast<const uint4*>(nodes + idx);
     const uint4 n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2), n3 = __ldg(q + 3), n4 = __ldg(q + 4);
     child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24;
@@ -65,8 +69,8 @@ PT_D uint32_t node_test_fast(const Bvh8Node* __restrict__ nodes, uint32_t idx, c
         const uint32_t cnt4 = (meta >> 5) & 0x07070707u;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float t0x = __fmaf_rn(q2f(nxw, j), anx, bnx), t0y = __fmaf_rn(q2f(nyw, j), any, bny), t0z = __fmaf_rn(q2f(nzw, j), anz, bnz);
-            const float t1x = __fmaf_rn(q2f(fxw, j), afx, bfx), t1y = __fmaf_rn(q2f(fyw, j), afy, bfy), t1z = __fmaf_rn(q2f(fzw, j), afz, bfz);
+            const float t0x = __fmaf_rn(q2f(nxw, j, bias), anx, bnx), t0y = __fmaf_rn(q2f(nyw, j, bias), any, bny), t0z = __fmaf_rn(q2f(nzw, j, bias), anz, bnz);
+            const float t1x = __fmaf_rn(q2f(fxw, j, bias), afx, bfx), t1y = __fmaf_rn(q2f(fyw, j, bias), afy, bfy), t1z = __fmaf_rn(q2f(fzw, j, bias), afz, bfz);
             const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             const uint32_t bits = ((cnt4 >> (8 * j)) & 0xffu) << ((idx4 >> (8 * j)) & 0xffu);
@@ -81,19 +85,34 @@ struct TraceIO {
     const uint32_t* count_ptr;  // number of entries (device), or nullptr -> count
     uint32_t count;
     uint32_t* cursor;           // dynamic-fetch cursor (zeroed before the launch)
-    const float4* ray_o;        // per slot: origin.xyz, tmin
-    const float4* ray_d;        // per slot: direction.xyz, tmax
+    // per slot, written by the producer of the ray (store_ray(): K-raygen, K-shade, k_ray_setup) at
+    // full SIMD width, so that a refilled lane only loads:
+    const float4* ray_o;        // origin.xyz, tmin
+    const float4* ray_d;        // direction.xyz, tmax
+    const float4* ray_e;        // 1/direction (box tests), bits: octant | kx<<3 | ky<<5 | kz<<7
+    const float4* ray_s;        // Sx, Sy, Sz (watertight shear constants), unused
     float4* hit_a;              // per slot: t, b1, b2, instance
     uint2* hit_b;               // per slot: primitive_index, triangle_index
-    uint32_t ray_stride;        // in float4: 1 = SoA path buffers, 2 = RayRec array (ray_d = ray_o + 1)
     uint32_t hit_a_stride;      // in float4: 1 = SoA, 2 = HitRec array
     uint32_t hit_b_stride;      // in uint2:  1 = SoA, 4 = HitRec array (hit_b = base + 2)
     uint32_t postpone_below;    // triangle tests are postponed while fewer lanes than this have one pending
+    uint32_t bias_word;         // 0x4B000000 (see q2f)
 };
 
 constexpr int kTraceBlock = 128;
 constexpr uint32_t kChunk = 128;   // rays per global atomic
 constexpr int kStackSize = 64;
+
+// world-space ray frame + shear constants of one slot (what store_ray() wrote)
+PT_D void load_ray(const TraceIO& io, uint32_t slot, RayFrame& f, RayPre& rp, float& tmin, float& tmax) {
+    const float4 ro = io.ray_o[slot], rd = io.ray_d[slot], re = io.ray_e[slot], rs = io.ray_s[slot];
+    f.o = v3(ro.x, ro.y, ro.z); f.d = v3(rd.x, rd.y, rd.z); f.idir = v3(re.x, re.y, re.z);
+    const uint32_t bits = __float_as_uint(re.w);
+    f.rs = bits & 7u;
+    rp.kx = (int)((bits >> 3) & 3u); rp.ky = (int)((bits >> 5) & 3u); rp.kz = (int)((bits >> 7) & 3u);
+    rp.Sx = rs.x; rp.Sy = rs.y; rp.Sz = rs.z;
+    tmin = ro.w; tmax = rd.w;
+}
 
 #ifdef PT_TRACE_MIN_BLOCKS
 #define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock, PT_TRACE_MIN_BLOCKS)
@@ -113,13 +132,15 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         }
         return;
     }
+    const uint32_t bias = io.bias_word;
     // warp-uniform chunk of the queue
     uint32_t w_next = 0, w_end = 0;
     bool exhausted = false;
-    // per-lane ray state
+    // per-lane ray state: ONE frame (world space at TLAS level, object space inside a transformed
+    // instance; the world frame is re-loaded from the slot when such an instance is left)
     bool active = false;
     uint32_t slot = 0;
-    RayFrame world, f;
+    RayFrame f;
     RayPre rp;
     float tmin = 0.0f, tmax = 0.0f;
     uint32_t cur_inst = kInvalidId;
@@ -128,9 +149,8 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     uint2 stack[kStackSize];
     int sp = 0;
     hit_init(best);
-    frame_set(world, v3s(0.0f), v3(0.0f, 0.0f, 1.0f));
-    f = world;
-    rp = ray_precompute(world.d);
+    f.o = v3s(0.0f); f.d = v3(0.0f, 0.0f, 1.0f); f.idir = v3s(1.0f); f.rs = 7u;
+    rp.kx = 0; rp.ky = 1; rp.kz = 2; rp.Sx = 0.0f; rp.Sy = 0.0f; rp.Sz = 1.0f;
 
     for (;;) {
         // ---- dynamic fetch: refill idle lanes from the warp's chunk
@@ -151,10 +171,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                     if (rank < avail) {
                         const uint32_t qi = w_next + rank;
                         slot = io.queue ? io.queue[qi] : qi;
-                        const float4 ro = io.ray_o[(size_t)slot * io.ray_stride], rd = io.ray_d[(size_t)slot * io.ray_stride];
-                        frame_set(world, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z));
-                        f = world;
-                        tmin = ro.w; tmax = rd.w;
+                        load_ray(io, slot, f, rp, tmin, tmax);
                         cur_inst = kInvalidId;
                         hit_init(best);
                         sp = 0;
@@ -187,13 +204,18 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
                 if (T.y && sp < kStackSize) stack[sp++] = T;
                 if ((G.y & 0xFF000000u) && sp < kStackSize) stack[sp++] = G;
-                if (sp < kStackSize) stack[sp++] = make_uint2(0xFFFFFFFFu, 0u);
                 cur_inst = __ldg(sc.tlas_leaf_instance + T.x + b);
-                V3 oo, dd;
-                to_object(sc.instances, cur_inst, world.o, world.d, oo, dd);
-                frame_set(f, oo, dd);
-                rp = ray_precompute(dd);
-                G = make_uint2(__ldg(&sc.instances[cur_inst].blas_root), 0x80000000u);
+                const uint4 ent = __ldg(reinterpret_cast<const uint4*>(&sc.instances[cur_inst].blas_root));   // blas_root, -, mesh | flags, -
+                const bool identity = (ent.z & kInstIdentity) != 0u;
+                // sentinel: y = 1 when the world frame must be re-loaded on the way out
+                if (sp < kStackSize) stack[sp++] = make_uint2(0xFFFFFFFFu, identity ? 0u : 1u);
+                if (!identity) {
+                    V3 oo, dd;
+                    to_object(sc.instances, cur_inst, f.o, f.d, oo, dd);
+                    frame_set(f, oo, dd);
+                    rp = ray_precompute(dd);
+                }
+                G = make_uint2(ent.x, 0x80000000u);
                 T = make_uint2(0u, 0u);
             }
         }
@@ -207,7 +229,11 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                     break;
                 }
                 const uint2 e = stack[--sp];
-                if (e.x == 0xFFFFFFFFu && e.y == 0u) { f = world; cur_inst = kInvalidId; continue; }
+                if (e.x == 0xFFFFFFFFu) {
+                    if (e.y) { float t0, t1; load_ray(io, slot, f, rp, t0, t1); }
+                    cur_inst = kInvalidId;
+                    continue;
+                }
                 if (e.y & 0xFF000000u) { G = e; } else { T = e; }
                 break;
             }
@@ -220,7 +246,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             const uint32_t node = G.x + __popc(G.y & 0xffu & ((1u << s) - 1u));
             if ((G.y & 0xFF000000u) && sp < kStackSize) stack[sp++] = G;
             uint32_t cb, tb, im;
-            const uint32_t hits = node_test_fast(sc.nodes, node, f, tmin, fminf(tmax, best.t), cb, tb, im);
+            const uint32_t hits = node_test_fast(sc.nodes, node, f, tmin, fminf(tmax, best.t), bias, cb, tb, im);
             G = make_uint2(cb, (hits & 0xFF000000u) | im);
             T = make_uint2(tb, hits & 0x00FFFFFFu);
         }
