@@ -76,7 +76,7 @@ int dev_alloc(T** p, size_t count) {
 
 void free_frame(PtRenderer* r) {
     PathBuffers& b = r->pb;
-    cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.ray_e); cudaFree(b.ray_s); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b);
+    cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.ray_e); cudaFree(b.ray_s); cudaFree(b.ray_m); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b);
     cudaFree(b.atten_sx); cudaFree(b.color_sy); cudaFree(b.final_sb); cudaFree(b.queue[0]); cudaFree(b.queue[1]);
     cudaFree(b.qcount); cudaFree(b.trace_next); cudaFree(b.trav_counters);
     b = PathBuffers{};
@@ -108,7 +108,7 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
     PathBuffers& b = r->pb;
     int rc;
 #define A(ptr, cnt) if ((rc = dev_alloc(&(ptr), (cnt))) != PT_OK) return rc
-    A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.hit_a, n); A(b.hit_b, n); A(b.prim_a, n); A(b.prim_b, n);
+    A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.ray_m, n); A(b.hit_a, n); A(b.hit_b, n); A(b.prim_a, n); A(b.prim_b, n);
     A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n);
     A(b.qcount, (size_t)r->max_iters + 2); A(b.trace_next, (size_t)r->max_iters + 2); A(b.trav_counters, 4);
     const size_t px = (size_t)pm.width * pm.height;
@@ -535,7 +535,7 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
     int rc;
     if ((rc = dev_alloc(&d_rays, n)) != PT_OK) return rc;
     if ((rc = dev_alloc(&d_hits, n)) != PT_OK) { cudaFree(d_rays); return rc; }
-    if ((rc = dev_alloc(&d_setup, 4 * n)) != PT_OK) { cudaFree(d_rays); cudaFree(d_hits); return rc; }
+    if ((rc = dev_alloc(&d_setup, 5 * n)) != PT_OK) { cudaFree(d_rays); cudaFree(d_hits); return rc; }
     static_assert(sizeof(PtRay) == sizeof(RayRec), "PtRay layout");
     cudaError_t e = cudaMemcpyAsync(d_rays, rays, n * sizeof(RayRec), cudaMemcpyHostToDevice, r->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(r->d_cursor, 0, 4, r->stream);

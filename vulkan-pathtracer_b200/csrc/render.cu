@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256) k_raygen(PixelMap pm, PathBuffers pb, Fra
         } else {
             const U2 seed = prng_seed(x, y, fp.cam.frame_count);            // :41
             const V3 d = primary_direction(fp.cam, x, y, pm.width, pm.height);
-            store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, slot, v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]), d,
+            store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]), d,
                       0.001f, 10000.0f);                                                                         // :38-39,47-48
             pb.atten_sx[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(seed.x));                          // :46
             pb.color_sy[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(seed.y));                          // :45
@@ -140,11 +140,11 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_rays(DeviceScene sc, co
 
 // standalone queries (pt_trace_rays): RayRec array -> the SoA ray records K-trace fetches
 __global__ void __launch_bounds__(256) k_ray_setup(const RayRec* __restrict__ rays, uint32_t n, float4* __restrict__ ro, float4* __restrict__ rd,
-                                                   float4* __restrict__ re, float4* __restrict__ rs) {
+                                                   float4* __restrict__ re, float4* __restrict__ rs, float4* __restrict__ rm) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const RayRec r = rays[i];
-    store_ray(ro, rd, re, rs, i, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax);
+    store_ray(ro, rd, re, rs, rm, i, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax);
 }
 
 // ------------------------------------------------------------------ K-shade
@@ -240,7 +240,7 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                 h.primitive_index = hb.x; h.triangle_index = hb.y;
             }
             if (emit) {
-                store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, slot, origin, direction, 0.001f, 10000.0f);
+                store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, origin, direction, 0.001f, 10000.0f);
                 pb.atten_sx[slot] = make_float4(atten.x, atten.y, atten.z, __uint_as_float(seed.x));
                 pb.color_sy[slot] = make_float4(color.x, color.y, color.z, __uint_as_float(seed.y));
                 pb.final_sb[slot] = make_float4(final_color.x, final_color.y, final_color.z, __uint_as_float(s | (j << 16)));
@@ -361,7 +361,7 @@ void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, T
     if (mode == TRACE_BVH8) {
         TraceIO io;
         io.queue = pb.queue[iter & 1u]; io.count_ptr = pb.qcount + iter; io.count = 0; io.cursor = pb.trace_next + iter;
-        io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.ray_e = pb.ray_e; io.ray_s = pb.ray_s; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
+        io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.ray_e = pb.ray_e; io.ray_s = pb.ray_s; io.ray_m = pb.ray_m; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
         io.hit_a_stride = 1; io.hit_b_stride = 1; io.postpone_below = trace_postpone_threshold(); io.bias_word = 0x4B000000u;
         k_trace_persistent<<<blocks[3], kTraceBlock, 0, st>>>(sc, io);
         return;
@@ -384,11 +384,11 @@ void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, Hi
     const int blocks = num_sms * 4;
     if (mode == TRACE_BVH8) {
         static_assert(sizeof(RayRec) == 32 && sizeof(HitRec) == 32, "AoS strides");
-        float4 *so = setup, *sd = setup + n, *se = setup + 2 * (size_t)n, *ss = setup + 3 * (size_t)n;
-        k_ray_setup<<<(n + 255) / 256, 256, 0, st>>>(rays, n, so, sd, se, ss);
+        float4 *so = setup, *sd = setup + n, *se = setup + 2 * (size_t)n, *ss = setup + 3 * (size_t)n, *sm = setup + 4 * (size_t)n;
+        k_ray_setup<<<(n + 255) / 256, 256, 0, st>>>(rays, n, so, sd, se, ss, sm);
         TraceIO io;
         io.queue = nullptr; io.count_ptr = nullptr; io.count = n; io.cursor = cursor;
-        io.ray_o = so; io.ray_d = sd; io.ray_e = se; io.ray_s = ss;
+        io.ray_o = so; io.ray_d = sd; io.ray_e = se; io.ray_s = ss; io.ray_m = sm;
         io.hit_a = reinterpret_cast<float4*>(hits); io.hit_a_stride = 2;
         io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4; io.postpone_below = trace_postpone_threshold();
         io.bias_word = 0x4B000000u;

@@ -18,7 +18,8 @@ struct PathBuffers {
     float4* ray_o;       // origin.xyz, tmin
     float4* ray_d;       // direction.xyz, tmax
     float4* ray_e;       // 1/direction, octant + shear axes (bits)     } derived by store_ray() where the ray is
-    float4* ray_s;       // shear constants Sx, Sy, Sz                  } produced; K-trace only loads them
+    float4* ray_s;       // shear row m0.xyz, Sz                        } produced; K-trace only loads them
+    float4* ray_m;       // shear row m1.xyz
     float4* hit_a;       // t, b1, b2, instance (bits)
     uint2* hit_b;        // primitive_index, triangle_index
     float4* prim_a;      // cached primary hit (reused for every sample, quirk Q1)
@@ -54,7 +55,7 @@ void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& 
                   int num_sms, cudaStream_t st);
 // standalone closest-hit queries (pt_trace_rays)
 void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
-                       uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, float4* setup /* 4*n */,
+                       uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, float4* setup /* 5*n */,
                        int num_sms, cudaStream_t st);
 // image post-processing
 void launch_to_bgra8(const float* rgba, uint8_t* bgra, uint32_t n_pixels, cudaStream_t st);

@@ -9,7 +9,13 @@ namespace pt {
 
 // ------------------------------------------------------------------ watertight ray/triangle test
 // Woop, Benthin, Wald 2013.  Same expression tree as the oracle (DESIGN.md "Closest-hit rule").
-struct RayPre { int kx, ky, kz; float Sx, Sy, Sz; };
+// The ray-space shear is carried as two matrix rows m0 = e_kx - Sx*e_kz, m1 = e_ky - Sy*e_kz, so
+// that the sheared coordinates are branch-free dot products: (m0x*A.x + m0y*A.y) + m0z*A.z has one
+// exact term (1*A[kx]), one rounded product (-(Sx*A[kz])), one zero and then one rounded sum — bit
+// for bit the oracle's A[kx] - Sx*A[kz] (no FMA contraction: --fmad=false) without the dynamic
+// component selects, which ptxas turned into seven divergent branch regions per test (profiles/r1a:
+// comp() alone was 8 % of K-trace's issue slots at 5.6 lanes).
+struct RayPre { float m0x, m0y, m0z, m1x, m1y, m1z, Sz; int kz; };
 
 PT_D RayPre ray_precompute(V3 d) {
     RayPre r;
@@ -18,23 +24,25 @@ PT_D RayPre ray_precompute(V3 d) {
     if (fabsf(d.z) > m) { kz = 2; }
     int kx = kz + 1; if (kx == 3) kx = 0;
     int ky = kx + 1; if (ky == 3) ky = 0;
-    if (comp(d, kz) < 0.0f) { int t = kx; kx = ky; ky = t; }
-    r.kx = kx; r.ky = ky; r.kz = kz;
+    const float dz = kz == 0 ? d.x : (kz == 1 ? d.y : d.z);
+    if (dz < 0.0f) { int t = kx; kx = ky; ky = t; }
+    const float dx = kx == 0 ? d.x : (kx == 1 ? d.y : d.z), dy = ky == 0 ? d.x : (ky == 1 ? d.y : d.z);
     // one correctly rounded division (same definition as the oracle): watertightness only needs the
     // same shear constants for every triangle the ray meets
-    r.Sz = 1.0f / comp(d, kz);
-    r.Sx = comp(d, kx) * r.Sz;
-    r.Sy = comp(d, ky) * r.Sz;
+    r.Sz = 1.0f / dz;
+    const float nSx = -(dx * r.Sz), nSy = -(dy * r.Sz);
+    r.kz = kz;
+    r.m0x = kx == 0 ? 1.0f : (kz == 0 ? nSx : 0.0f); r.m0y = kx == 1 ? 1.0f : (kz == 1 ? nSx : 0.0f); r.m0z = kx == 2 ? 1.0f : (kz == 2 ? nSx : 0.0f);
+    r.m1x = ky == 0 ? 1.0f : (kz == 0 ? nSy : 0.0f); r.m1y = ky == 1 ? 1.0f : (kz == 1 ? nSy : 0.0f); r.m1z = ky == 2 ? 1.0f : (kz == 2 ? nSy : 0.0f);
     return r;
 }
 
 PT_D bool intersect_tri(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2, float tmin, float tmax, float& t_out,
                         float& b1, float& b2) {
     const V3 A = v3(p0.x, p0.y, p0.z) - o, B = v3(p1.x, p1.y, p1.z) - o, C = v3(p2.x, p2.y, p2.z) - o;
-    const float Akz = comp(A, rp.kz), Bkz = comp(B, rp.kz), Ckz = comp(C, rp.kz);
-    const float Ax = comp(A, rp.kx) - rp.Sx * Akz, Ay = comp(A, rp.ky) - rp.Sy * Akz;
-    const float Bx = comp(B, rp.kx) - rp.Sx * Bkz, By = comp(B, rp.ky) - rp.Sy * Bkz;
-    const float Cx = comp(C, rp.kx) - rp.Sx * Ckz, Cy = comp(C, rp.ky) - rp.Sy * Ckz;
+    const float Ax = (rp.m0x * A.x + rp.m0y * A.y) + rp.m0z * A.z, Ay = (rp.m1x * A.x + rp.m1y * A.y) + rp.m1z * A.z;
+    const float Bx = (rp.m0x * B.x + rp.m0y * B.y) + rp.m0z * B.z, By = (rp.m1x * B.x + rp.m1y * B.y) + rp.m1z * B.z;
+    const float Cx = (rp.m0x * C.x + rp.m0y * C.y) + rp.m0z * C.z, Cy = (rp.m1x * C.x + rp.m1y * C.y) + rp.m1z * C.z;
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
@@ -47,6 +55,7 @@ PT_D bool intersect_tri(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2,
     if (U < 0.0f || V < 0.0f || W < 0.0f) return false;
     const float det = U + V + W;
     if (det == 0.0f) return false;
+    const float Akz = comp(A, rp.kz), Bkz = comp(B, rp.kz), Ckz = comp(C, rp.kz);
     const float Az = rp.Sz * Akz, Bz = rp.Sz * Bkz, Cz = rp.Sz * Ckz;
     const float T = U * Az + V * Bz + W * Cz;
     const float t = T / det;
@@ -81,7 +90,7 @@ PT_D void test_triangle(const Bvh8Tri* __restrict__ tris, uint32_t idx, V3 o, co
 
 // ------------------------------------------------------------------ ray frame for box tests
 struct RayFrame {
-    V3 o, d;         // origin / direction in the current space
+    V3 o;            // origin in the current space
     V3 idir;         // 1/d with |d| clamped away from 0
     uint32_t rs;     // octant: bit k set when d[k] >= 0
 };
@@ -94,25 +103,26 @@ PT_D float safe_rcp(float d) {
     return r;
 }
 PT_D void frame_set(RayFrame& f, V3 o, V3 d) {
-    f.o = o; f.d = d;
+    f.o = o;
     f.idir = v3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
     f.rs = (f.idir.x >= 0.0f ? 1u : 0u) | (f.idir.y >= 0.0f ? 2u : 0u) | (f.idir.z >= 0.0f ? 4u : 0u);
 }
 
 // Producer side of K-trace's ray fetch: the world-space ray with everything the traversal derives
-// from it (box-test reciprocals + octant, watertight shear constants), 64 bytes per slot.  Computed
+// from it (box-test reciprocals + octant, watertight shear rows), 80 bytes per slot.  Computed
 // where rays are born (K-raygen / K-shade / k_ray_setup, all lanes busy) instead of in K-trace,
 // where refilled lanes would do it two at a time (profiles/r1a: 22 % of K-trace's issue slots).
 PT_D void store_ray(float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ ray_e, float4* __restrict__ ray_s,
-                    uint32_t slot, V3 o, V3 d, float tmin, float tmax) {
+                    float4* __restrict__ ray_m, uint32_t slot, V3 o, V3 d, float tmin, float tmax) {
     RayFrame f;
     frame_set(f, o, d);
     const RayPre rp = ray_precompute(d);
-    const uint32_t bits = f.rs | ((uint32_t)rp.kx << 3) | ((uint32_t)rp.ky << 5) | ((uint32_t)rp.kz << 7);
+    const uint32_t bits = f.rs | ((uint32_t)rp.kz << 3);
     ray_o[slot] = make_float4(o.x, o.y, o.z, tmin);
     ray_d[slot] = make_float4(d.x, d.y, d.z, tmax);
     ray_e[slot] = make_float4(f.idir.x, f.idir.y, f.idir.z, __uint_as_float(bits));
-    ray_s[slot] = make_float4(rp.Sx, rp.Sy, rp.Sz, 0.0f);
+    ray_s[slot] = make_float4(rp.m0x, rp.m0y, rp.m0z, rp.Sz);
+    ray_m[slot] = make_float4(rp.m1x, rp.m1y, rp.m1z, 0.0f);
 }
 
 // world -> object: o' = Ainv*(o - T), d' = Ainv*d (not renormalised: t is shared between spaces).
@@ -235,7 +245,7 @@ PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, 
             PT_PUSH(kSentinel);
             cur_inst = __ldg(sc.tlas_leaf_instance + T.x + b);
             V3 oo, dd;
-            to_object(sc.instances, cur_inst, world.o, world.d, oo, dd);
+            to_object(sc.instances, cur_inst, o, d, oo, dd);
             frame_set(f, oo, dd);
             rp = ray_precompute(dd);
             G = make_uint2(__ldg(&sc.instances[cur_inst].blas_root), 0x80000000u);

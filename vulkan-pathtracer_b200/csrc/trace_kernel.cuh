@@ -89,8 +89,9 @@ struct TraceIO {
     // full SIMD width, so that a refilled lane only loads:
     const float4* ray_o;        // origin.xyz, tmin
     const float4* ray_d;        // direction.xyz, tmax
-    const float4* ray_e;        // 1/direction (box tests), bits: octant | kx<<3 | ky<<5 | kz<<7
-    const float4* ray_s;        // Sx, Sy, Sz (watertight shear constants), unused
+    const float4* ray_e;        // 1/direction (box tests), bits: octant | kz<<3
+    const float4* ray_s;        // shear row m0.xyz, Sz
+    const float4* ray_m;        // shear row m1.xyz, unused
     float4* hit_a;              // per slot: t, b1, b2, instance
     uint2* hit_b;               // per slot: primitive_index, triangle_index
     uint32_t hit_a_stride;      // in float4: 1 = SoA, 2 = HitRec array
@@ -105,12 +106,13 @@ constexpr int kStackSize = 64;
 
 // world-space ray frame + shear constants of one slot (what store_ray() wrote)
 PT_D void load_ray(const TraceIO& io, uint32_t slot, RayFrame& f, RayPre& rp, float& tmin, float& tmax) {
-    const float4 ro = io.ray_o[slot], rd = io.ray_d[slot], re = io.ray_e[slot], rs = io.ray_s[slot];
-    f.o = v3(ro.x, ro.y, ro.z); f.d = v3(rd.x, rd.y, rd.z); f.idir = v3(re.x, re.y, re.z);
+    const float4 ro = io.ray_o[slot], rd = io.ray_d[slot], re = io.ray_e[slot], rs = io.ray_s[slot], rm = io.ray_m[slot];
+    f.o = v3(ro.x, ro.y, ro.z); f.idir = v3(re.x, re.y, re.z);
     const uint32_t bits = __float_as_uint(re.w);
     f.rs = bits & 7u;
-    rp.kx = (int)((bits >> 3) & 3u); rp.ky = (int)((bits >> 5) & 3u); rp.kz = (int)((bits >> 7) & 3u);
-    rp.Sx = rs.x; rp.Sy = rs.y; rp.Sz = rs.z;
+    rp.kz = (int)((bits >> 3) & 3u);
+    rp.m0x = rs.x; rp.m0y = rs.y; rp.m0z = rs.z; rp.Sz = rs.w;
+    rp.m1x = rm.x; rp.m1y = rm.y; rp.m1z = rm.z;
     tmin = ro.w; tmax = rd.w;
 }
 
@@ -149,8 +151,8 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     uint2 stack[kStackSize];
     int sp = 0;
     hit_init(best);
-    f.o = v3s(0.0f); f.d = v3(0.0f, 0.0f, 1.0f); f.idir = v3s(1.0f); f.rs = 7u;
-    rp.kx = 0; rp.ky = 1; rp.kz = 2; rp.Sx = 0.0f; rp.Sy = 0.0f; rp.Sz = 1.0f;
+    f.o = v3s(0.0f); f.idir = v3s(1.0f); f.rs = 7u;
+    rp.m0x = 1.0f; rp.m0y = 0.0f; rp.m0z = 0.0f; rp.m1x = 0.0f; rp.m1y = 1.0f; rp.m1z = 0.0f; rp.Sz = 1.0f; rp.kz = 2;
 
     for (;;) {
         // ---- dynamic fetch: refill idle lanes from the warp's chunk
@@ -211,7 +213,8 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                 if (sp < kStackSize) stack[sp++] = make_uint2(0xFFFFFFFFu, identity ? 0u : 1u);
                 if (!identity) {
                     V3 oo, dd;
-                    to_object(sc.instances, cur_inst, f.o, f.d, oo, dd);
+                    const float4 wd = io.ray_d[slot];      // the world direction is not kept in registers
+                    to_object(sc.instances, cur_inst, f.o, v3(wd.x, wd.y, wd.z), oo, dd);
                     frame_set(f, oo, dd);
                     rp = ray_precompute(dd);
                 }
