@@ -131,7 +131,9 @@ enum {
     PT_FLAG_SORT_BY_MATERIAL = 1u << 0,   /* material-sorted shading queue */
     PT_FLAG_TRACE_BVH2 = 1u << 1,         /* use the simple BVH2 reference walker, not the BVH8 kernel */
     PT_FLAG_NO_PRIMARY_REUSE = 1u << 2,   /* re-trace the (identical) primary ray for every sample */
-    PT_FLAG_TRACE_WALKER = 1u << 3        /* simple one-ray-per-thread BVH8 walker instead of the persistent kernel */
+    PT_FLAG_TRACE_WALKER = 1u << 3,       /* simple one-ray-per-thread BVH8 walker instead of the persistent kernel */
+    PT_FLAG_BVH_PLOC = 1u << 4            /* build the binary hierarchy by locally-ordered clustering (PLOC) instead of
+                                             the Morton radix tree (LBVH): slower build, better trees for irregular meshes */
 };
 
 typedef struct PtRenderConfig {

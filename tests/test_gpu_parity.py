@@ -95,7 +95,8 @@ def test_unorm8_conversion_is_exact():
 
 
 # ------------------------------------------------------------------ traversal kernel vs brute force
-@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2])
+@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2, b200pt.PT_FLAG_BVH_PLOC,
+                                   b200pt.PT_FLAG_BVH_PLOC | b200pt.PT_FLAG_TRACE_BVH2])
 @pytest.mark.parametrize("seed,ntri,nmesh,ninst", [(3, 3000, 3, 7), (5, 3, 3, 4), (11, 20000, 2, 40), (12, 64, 5, 1)])
 def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
     ps = S.random_soup(seed, ntri, nmesh, ninst).pack()
@@ -108,6 +109,30 @@ def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
     ho = orc.OracleScene(ps, False).trace(rays, use_bvh=False)
     bad = hits_mismatch(hg, ho)
     assert not bad.any(), f"{int(bad.sum())} of {len(rays)} rays differ from brute force"
+    r.deinit()
+
+
+@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_BVH_PLOC])
+def test_duplicated_geometry_builds_and_keeps_the_tie_break(flags):
+    """6000 coincident triangles (two primitives, three instances at the same place): the builders must
+    terminate on runs of identical boxes, and the closest hit is the lexicographically smallest
+    (t, instance, primitive, triangle)."""
+    sb = S.SceneBuilder(); sb.add_material()
+    P = np.tile(np.array([[-1, -1, 2], [-1, 1, 2], [1, -1, 2]], np.float32), (1000, 1))
+    N = np.tile(np.array([[0, 0, -1]], np.float32), (3000, 1)); T = np.tile(np.array([[1, 0, 0, 1]], np.float32), (3000, 1))
+    UV = np.zeros((3000, 2), np.float32); I = np.arange(3000, dtype=np.uint32)
+    s0 = S.Soup(); s0.add(P, N, T, UV, I.reshape(-1, 3)); s1 = S.Soup(); s1.add(P, N, T, UV, I.reshape(-1, 3))
+    mesh = sb.add_mesh([s0.prim(0), s1.prim(0)])
+    for _ in range(3):
+        sb.add_node(mesh)
+    ps = sb.pack()
+    r = b200pt.Renderer(ps, 32, 32, 1, 1, flags=flags)
+    rays = np.zeros(64, b200pt.PtRay_dtype)
+    rays["origin"] = [-0.5, -0.25, 0]; rays["dir"] = [0, 0, 1]; rays["tmin"] = 1e-3; rays["tmax"] = 1e4
+    h = r.trace(rays)
+    ho = orc.OracleScene(ps, False).trace(rays, use_bvh=False)
+    assert not hits_mismatch(h, ho).any()
+    assert (h["instance"] == 0).all() and (h["primitive_index"] == 0).all() and (h["triangle_index"] == 0).all() and (h["t"] == 2.0).all()
     r.deinit()
 
 
@@ -158,6 +183,22 @@ def test_random_soup_with_scaled_rotated_instances():
 
 def test_instancing_scene_small():
     assert_matches_oracle(S.instanced(1234, 4, 64).pack(), 320, 180, 2, 4)
+
+
+def test_identity_and_transformed_instances_mix():
+    """Identity instances are entered without re-deriving the ray frame (kInstIdentity); leaving a
+    transformed instance must restore the world frame before the next identity instance is entered."""
+    sb = S.random_soup(21, 1500, 3, 0)
+    for k in range(3):
+        sb.add_node(k)                                            # identity
+        sb.add_node(k, translation=(0.3 * k - 0.2, 0.1, 0.4))     # pure translation: not identity
+        sb.add_node(k, rotation=(0.0, 0.38268343, 0.0, 0.92387953), scale=(1.0, 0.7, 1.2))
+    ps = sb.pack()
+    assert_matches_oracle(ps, 160, 90, 2, 4, use_bvh=False)
+    r = b200pt.Renderer(ps, 32, 32, 1, 1)
+    rays = random_rays(5, 100000, dtype=b200pt.PtRay_dtype)
+    assert not hits_mismatch(r.trace(rays), orc.OracleScene(ps, False).trace(rays, use_bvh=False)).any()
+    r.deinit()
 
 
 @pytest.fixture(scope="module")

@@ -10,5 +10,6 @@ for f in api render bvh_build; do $NV -c $f.cu -o $OBJ/$f.o -Xptxas -v 2> $OBJ/$
 wait
 g++ -O2 -std=c++17 -fPIC -ffp-contract=off -c host.cpp -o $OBJ/host.o
 g++ -O2 -std=c++17 -fPIC -ffp-contract=off -c scene_load.cpp -o $OBJ/scene_load.o
+g++ -O2 -std=c++17 -fPIC -ffp-contract=off -c image_decode.cpp -o $OBJ/image_decode.o
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libb200pt_$NAME.so $OBJ/*.o -lz
-grep -E "k_shade|k_trace_persistent" -A2 $OBJ/render.log | grep -E "Used|spill" | sed 's/ptxas info    ://'
+grep -E "k_shade|k_trace_persistent" -A3 $OBJ/render.log | grep -E "Used|spill" | sed "s/ptxas info    ://"

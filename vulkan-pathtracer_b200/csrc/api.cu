@@ -189,7 +189,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     if ((rc = dev_alloc(&r->d_instances_raw, inst.size())) != PT_OK) return rc;
     if (!inst.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances_raw, inst.data(), inst.size() * sizeof(PtInstance), cudaMemcpyHostToDevice));
     // acceleration structures (createBlases + Tlas.init)
-    if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, r->stream, &r->bvh)) != PT_OK) return rc;
+    if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, (r->cfg.flags & PT_FLAG_BVH_PLOC) != 0, r->stream, &r->bvh)) != PT_OK) return rc;
     // instance records: inverse of the 3x3 linear part (host, same formula as every other user)
     std::vector<InstanceRec> recs(inst.size());
     for (size_t i = 0; i < inst.size(); ++i) {

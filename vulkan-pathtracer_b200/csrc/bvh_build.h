@@ -15,7 +15,7 @@ struct SceneBvh {
     uint32_t* tlas_leaf_instance = nullptr;
     uint32_t tlas_root8 = kInvalidId;
     std::vector<uint32_t> blas_root8;   // per mesh, kInvalidId for empty meshes
-    // BVH2 (LBVH trees; input of the collapse, walked by the reference kernel)
+    // BVH2 (LBVH or PLOC trees; input of the collapse, walked by the reference kernel)
     Bvh2Node* nodes2 = nullptr;         // per mesh at tri_off[m]
     Bvh8Tri* tris2 = nullptr;           // Morton-ordered triangles per mesh at tri_off[m]
     Bvh2Node* tlas2 = nullptr;
@@ -32,6 +32,6 @@ struct SceneBvh {
 // d_* are device pointers, h_* their host copies.
 int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::vector<PrimRec>& h_prims,
                     const std::vector<PtMesh>& meshes, const PtInstance* d_instances,
-                    const std::vector<PtInstance>& h_instances, cudaStream_t stream, SceneBvh* out);
+                    const std::vector<PtInstance>& h_instances, bool use_ploc, cudaStream_t stream, SceneBvh* out);
 
 }  // namespace pt
