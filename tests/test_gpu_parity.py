@@ -185,6 +185,16 @@ def test_instancing_scene_small():
     assert_matches_oracle(S.instanced(1234, 4, 64).pack(), 320, 180, 2, 4)
 
 
+def test_material_sorted_shading_is_bit_identical():
+    """PT_FLAG_SORT_BY_MATERIAL reorders the shading queue only: same image, same ids, same ray count."""
+    ps = S.atrium(1234, 20000, 6, 64).pack()
+    a_img, a_ids, a_st = render(ps, 200, 120, 3, 4, 1)
+    b_img, b_ids, b_st = render(ps, 200, 120, 3, 4, 1, flags=b200pt.PT_FLAG_SORT_BY_MATERIAL)
+    assert bits_equal(a_img, b_img).all() and all((x == y).all() for x, y in zip(a_ids, b_ids))
+    assert a_st.rays_traced == b_st.rays_traced and b_st.kernel_launches > a_st.kernel_launches
+    assert_matches_oracle(ps, 200, 120, 3, 4, 1, flags=b200pt.PT_FLAG_SORT_BY_MATERIAL)
+
+
 def test_identity_and_transformed_instances_mix():
     """Identity instances are entered without re-deriving the ray frame (kInstIdentity); leaving a
     transformed instance must restore the world frame before the next identity instance is entered."""

@@ -77,7 +77,7 @@ int dev_alloc(T** p, size_t count) {
 void free_frame(PtRenderer* r) {
     PathBuffers& b = r->pb;
     cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.ray_e); cudaFree(b.ray_s); cudaFree(b.ray_m); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b);
-    cudaFree(b.atten_sx); cudaFree(b.color_sy); cudaFree(b.final_sb); cudaFree(b.queue[0]); cudaFree(b.queue[1]);
+    cudaFree(b.atten_sx); cudaFree(b.color_sy); cudaFree(b.final_sb); cudaFree(b.queue[0]); cudaFree(b.queue[1]); cudaFree(b.queue_sorted); cudaFree(b.sort_bins);
     cudaFree(b.qcount); cudaFree(b.trace_next); cudaFree(b.trav_counters);
     b = PathBuffers{};
     cudaFree(r->d_image); cudaFree(r->d_ids); cudaFree(r->d_bgra); cudaFree(r->d_upscaled); cudaFree(r->d_accum);
@@ -109,7 +109,7 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
     int rc;
 #define A(ptr, cnt) if ((rc = dev_alloc(&(ptr), (cnt))) != PT_OK) return rc
     A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.ray_m, n); A(b.hit_a, n); A(b.hit_b, n); A(b.prim_a, n); A(b.prim_b, n);
-    A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n);
+    A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n); A(b.queue_sorted, n); A(b.sort_bins, (size_t)r->scene.num_materials + 4);
     A(b.qcount, (size_t)r->max_iters + 2); A(b.trace_next, (size_t)r->max_iters + 2); A(b.trav_counters, 4);
     const size_t px = (size_t)pm.width * pm.height;
     A(r->d_image, px * 4); A(r->d_ids, px * 3);
@@ -347,6 +347,7 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     mark(2); launch_raygen(r->pm, pb, fp, st); mark_end(); ++launches;
     for (uint32_t it = 0; it < r->max_iters; ++it) {
         mark(0); launch_trace(r->scene, pb, it, mode, r->bvh.tlas2_count, r->bvh.tlas2_leaf_instance, r->num_sms, st); mark_end();
+        if (fp.flags & PT_FLAG_SORT_BY_MATERIAL) { mark(2); launch_material_sort(r->scene, pb, it, r->num_sms, st); mark_end(); launches += 3; }
         mark(1); launch_shade(r->scene, r->pm, pb, fp, it, r->num_sms, st); mark_end();
         launches += 2;
     }

@@ -147,6 +147,71 @@ __global__ void __launch_bounds__(256) k_ray_setup(const RayRec* __restrict__ ra
     store_ray(ro, rd, re, rs, rm, i, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax);
 }
 
+// ------------------------------------------------------------------ material sort (optional)
+// Counting sort of the live-path queue by material index (24 bit, triangle.glsl:107) so that the
+// lanes of a K-shade warp read the same MatRec and the same textures.  Three small kernels: count,
+// scan (one block), scatter.  Order inside a bin is arbitrary (atomics); results do not depend on it.
+PT_D uint32_t path_material(const DeviceScene& sc, const PathBuffers& pb, uint32_t slot) {
+    const float4 ha = pb.hit_a[slot];
+    if (ha.x == kMissT) return sc.num_materials;           // sky paths: last bin
+    const uint32_t prim = pb.hit_b[slot].x;
+    return min(__ldg(&sc.prims[prim].info) & PT_MATERIAL_INDEX_MASK, sc.num_materials);
+}
+
+__global__ void __launch_bounds__(256) k_matsort_count(DeviceScene sc, PathBuffers pb, uint32_t iter) {
+    const uint32_t n = pb.qcount[iter];
+    const uint32_t* __restrict__ q = pb.queue[iter & 1u];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t key = path_material(sc, pb, q[i]);
+        // warp-aggregated increment per distinct key
+        const uint32_t peers = __match_any_sync(__activemask(), key);
+        if ((threadIdx.x & 31u) == (uint32_t)(__ffs((int)peers) - 1)) atomicAdd(pb.sort_bins + key, (uint32_t)__popc(peers));
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_matsort_scan(PathBuffers pb, uint32_t bins) {
+    // exclusive scan of the bins in place (bins <= a few thousand: one block, chunked)
+    __shared__ uint32_t carry;
+    __shared__ uint32_t warp_sums[32];
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < bins; base += blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < bins ? pb.sort_bins[i] : 0u;
+        uint32_t x = v;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((int)(threadIdx.x & 31u) >= o) x += y; }
+        if ((threadIdx.x & 31u) == 31u) warp_sums[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_sums[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, w, o); if ((int)threadIdx.x >= o) w += y; }
+            warp_sums[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const uint32_t before = carry + (threadIdx.x >= 32 ? warp_sums[(threadIdx.x >> 5) - 1] : 0u) + x - v;
+        if (i < bins) pb.sort_bins[i] = before;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = before + v;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_matsort_scatter(DeviceScene sc, PathBuffers pb, uint32_t iter) {
+    const uint32_t n = pb.qcount[iter];
+    const uint32_t* __restrict__ q = pb.queue[iter & 1u];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = q[i];
+        const uint32_t key = path_material(sc, pb, slot);
+        const uint32_t peers = __match_any_sync(__activemask(), key);
+        const uint32_t lane = threadIdx.x & 31u;
+        const int leader = __ffs((int)peers) - 1;
+        uint32_t base = 0;
+        if ((int)lane == leader) base = atomicAdd(pb.sort_bins + key, (uint32_t)__popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        pb.queue_sorted[base + __popc(peers & ((1u << lane) - 1u))] = slot;
+    }
+}
+
 // ------------------------------------------------------------------ K-shade
 // One thread per live path.  Consumes the hit of segment (sample s, bounce j), runs the body of the
 // bounce loop (ray_gen.rgen:65-97), and either emits the next ray (appended to the next queue) or
@@ -159,7 +224,7 @@ __global__ void __launch_bounds__(256) k_ray_setup(const RayRec* __restrict__ ra
 #endif
 __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers pb, FrameParams fp, uint32_t iter) {
     const uint32_t n = pb.qcount[iter];
-    const uint32_t* __restrict__ qin = pb.queue[iter & 1u];
+    const uint32_t* __restrict__ qin = (fp.flags & PT_FLAG_SORT_BY_MATERIAL) ? pb.queue_sorted : pb.queue[iter & 1u];
     uint32_t* __restrict__ qout = pb.queue[(iter + 1u) & 1u];
     uint32_t* qout_count = pb.qcount + iter + 1u;
     const uint32_t S = fp.num_samples, B = fp.num_bounces;
@@ -369,6 +434,14 @@ void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, T
     if (mode == TRACE_BVH2) k_trace<TRACE_BVH2><<<blocks[1], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
     else if (mode == TRACE_BVH8_COUNT) k_trace<TRACE_BVH8_COUNT><<<blocks[2], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
     else k_trace<TRACE_BVH8><<<blocks[0], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
+}
+
+void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, int num_sms, cudaStream_t st) {
+    const uint32_t bins = sc.num_materials + 1u;
+    cudaMemsetAsync(pb.sort_bins, 0, sizeof(uint32_t) * (bins + 1u), st);
+    k_matsort_count<<<num_sms * 4, 256, 0, st>>>(sc, pb, iter);
+    k_matsort_scan<<<1, 1024, 0, st>>>(pb, bins);
+    k_matsort_scatter<<<num_sms * 4, 256, 0, st>>>(sc, pb, iter);
 }
 
 void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,

@@ -28,6 +28,8 @@ struct PathBuffers {
     float4* color_sy;    // color.rgb, seed.y (bits)
     float4* final_sb;    // final_color.rgb, sample | bounce << 16 (bits)
     uint32_t* queue[2];  // slot indices of live paths, double buffered
+    uint32_t* queue_sorted;   // PT_FLAG_SORT_BY_MATERIAL: the current queue reordered by material for K-shade
+    uint32_t* sort_bins;      // [num_materials + 2] counting-sort bins (zero between uses)
     uint32_t* qcount;    // [max_iters + 1] entries of queue k (zeroed per frame)
     uint32_t* trace_next;// [max_iters] dynamic-fetch cursors of the persistent trace kernel
     uint32_t* trav_counters;  // [2] nodes, tris (counting walker)
@@ -51,6 +53,8 @@ enum TraceMode { TRACE_BVH8 = 0, TRACE_BVH2 = 1, TRACE_BVH8_COUNT = 2, TRACE_BVH
 void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st);
 void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
                   const uint32_t* tlas2_leaf_instance, int num_sms, cudaStream_t st);
+// PT_FLAG_SORT_BY_MATERIAL: counting sort of queue `iter` by the material of each path's hit (misses last)
+void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, int num_sms, cudaStream_t st);
 void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
                   int num_sms, cudaStream_t st);
 // standalone closest-hit queries (pt_trace_rays)
