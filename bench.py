@@ -169,6 +169,11 @@ def main():
     if args.impl == "reference":
         return run_reference(args, rank, world)
 
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     import b200pt
@@ -308,7 +313,8 @@ def main():
                 "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(S.PtCamera), "d2h_bytes_per_step": W * H * 16,
                         "ms_per_step": 1e3 * e2e_s / args.steps, "spp_per_s": spp * args.steps * world / e2e_s},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     r.deinit()
     if world > 1:
         dist.destroy_process_group()

@@ -212,7 +212,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     if (!recs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances, recs.data(), recs.size() * sizeof(InstanceRec), cudaMemcpyHostToDevice));
     DeviceScene& sc = r->scene;
     sc.triangle_data = r->d_blob; sc.prims = r->d_prims; sc.materials = r->d_materials; sc.textures = r->d_textures;
-    sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
+    sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.node_bits = r->bvh.node_bits8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
     sc.nodes2 = r->bvh.nodes2; sc.tris2 = r->bvh.tris2; sc.tlas2 = r->bvh.tlas2; sc.tlas_root = r->bvh.tlas_root8;
     sc.num_instances = (uint32_t)inst.size(); sc.num_prims = (uint32_t)prims.size();
     sc.num_materials = (uint32_t)s->num_materials; sc.num_textures = (uint32_t)s->num_textures;

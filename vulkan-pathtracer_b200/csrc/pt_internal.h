@@ -92,6 +92,8 @@ struct DeviceScene {
     const TexRec* textures;
     const InstanceRec* instances;
     const Bvh8Node* nodes;       // all BLASes + TLAS
+    const uint4* node_bits;      // 2 x uint4 per node: per slot the hit-mask word of that child (inner: 1 << (24 + slot),
+                                 // leaf: unary triangle count << offset, empty: 0) — the meta bytes pre-expanded for K-trace
     const Bvh8Tri* tris;         // leaf triangles (BLAS) in collapse order
     const uint32_t* tlas_leaf_instance;  // TLAS leaf slots -> instance index
     const Bvh2Node* nodes2;      // LBVH trees (reference walker)
