@@ -159,6 +159,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--partition", default="frames", choices=["frames", "tiles", "tiles-peer"],
+                    help="N>1: frames = rank r renders frame_count r, r+N, ... (weak scaling, default); tiles = every rank renders "
+                         "its interleaved 32x8 tiles of the SAME frame + NCCL reduce (strong scaling); tiles-peer = same, but owned "
+                         "pixels are stored straight into rank 0's image over NVLink (CUDA IPC), one 4-byte NCCL all-reduce as fence")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-l2-flush", action="store_true")
     args = ap.parse_args()
@@ -188,8 +192,23 @@ def main():
     _, W, H, spp, seg = WORKLOADS[name]
     ps, t_gen = build_scene(name)
     t0 = time.time()
-    r = b200pt.Renderer(ps, W, H, spp, seg, device=local_rank, flags=args.flags)
+    tiles = world > 1 and args.partition != "frames"
+    peer = world > 1 and args.partition == "tiles-peer"
+    r = b200pt.Renderer(ps, W, H, spp, seg, device=local_rank, flags=args.flags, rank=rank if tiles else 0, world=world if tiles else 1,
+                        partition=b200pt.PT_PARTITION_TILES if tiles else b200pt.PT_PARTITION_NONE)
     t_create = time.time() - t0
+    if peer:
+        # rank 0 exports its image buffer; the others map it and their K-shade writes owned pixels into it
+        handle = torch.zeros(64, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            hb = (C.c_uint8 * 64)()
+            b200pt.check(b200pt.lib().pt_ipc_export_image(r.handle, hb))
+            handle.copy_(torch.tensor(list(hb), dtype=torch.uint8))
+        dist.broadcast(handle, src=0)
+        if rank != 0:
+            hb = (C.c_uint8 * 64)(*handle.cpu().tolist())
+            b200pt.check(b200pt.lib().pt_ipc_open_root_image(r.handle, hb))
+        fence = torch.zeros(1, dtype=torch.int32, device="cuda")
     st0 = r.stats()
     # a non-default torch stream: its handle is passed to pt_render so that torch.cuda.Event timing and
     # NCCL ordering see the renderer's kernels (the NULL handle would mean "the renderer's own stream")
@@ -207,12 +226,19 @@ def main():
         torch.cuda.synchronize()
 
     def frame_of(i):
-        return i * world + rank
+        return i if tiles else i * world + rank
+
+    def combine():
+        if world == 1:
+            return
+        if peer:
+            dist.all_reduce(fence)      # stream-ordered fence: every rank's kernels (and their peer stores) precede it
+        else:
+            dist.reduce(img_t, dst=0, op=dist.ReduceOp.SUM)
 
     def step(i):
         r.record(S.camera_default(W, H, frame_of(i)), sp)
-        if world > 1:
-            dist.reduce(img_t, dst=0, op=dist.ReduceOp.SUM)
+        combine()
 
     # ---------------- device-timed region: inputs resident, per-step CUDA events, L2 flushed between steps
     r.set_profiling(True)
@@ -248,7 +274,8 @@ def main():
         rays_total = float(rays_local)
     r.set_profiling(False)
     mrays = rays_total / (dev_ms * 1e-3) / 1e6
-    spp_s = spp * args.steps * world / (dev_ms * 1e-3)
+    frames_done = args.steps * (1 if tiles else world)
+    spp_s = spp * frames_done / (dev_ms * 1e-3)
 
     # ---------------- end-to-end: public API with host buffers (camera in, image out through pinned memory)
     host_img = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
@@ -258,10 +285,11 @@ def main():
     for k in range(args.steps):
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
         r.record(cam, sp)
-        if world > 1:
-            dist.reduce(img_t, dst=0, op=dist.ReduceOp.SUM)
+        combine()
         if rank == 0:
             b200pt.check(b200pt.lib().pt_read_rgba32f_async(r.handle, host_img.data_ptr(), sp))
+        if peer:
+            dist.all_reduce(fence)      # the next frame's peer stores must not overtake rank 0's read-back
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
@@ -303,15 +331,17 @@ def main():
                    "sample": f"{frames_cpu} frames x {rows} of {H} scanlines (every {row_step}th) at 1 spp, CPU oracle (C++ restatement, binned-SAH BVH2), {nt} threads, {dt:.2f} s"}
     if rank == 0:
         line = {"metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
-                "config": {"workload": WORKLOAD_DESC[name], "partition": "frames (rank r renders frame_count r, r+N, ...) + NCCL reduce(sum) to rank 0" if world > 1 else "none",
+                "config": {"workload": WORKLOAD_DESC[name], "partition": ("none" if world == 1 else "frames (rank r renders frame_count r, r+N, ...) + NCCL reduce(sum) to rank 0" if not tiles
+                                         else "interleaved 32x8 tiles of one frame, peer stores into rank 0 over NVLink + 4-byte NCCL fence" if peer
+                                         else "interleaved 32x8 tiles of one frame + NCCL reduce(sum) to rank 0"),
                            "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed; per-step path state (365 MB) exceeds L2",
                            "triangles": int(st0.num_triangles), "bvh8_nodes": int(st0.bvh_nodes), "bvh_build_ms": st0.ms_build,
                            "scene_gen_s": t_gen, "create_s": t_create},
-                "spp_per_s": spp_s, "rays_per_step": rays_total / args.steps / world,
+                "spp_per_s": spp_s, "rays_per_step": rays_total / args.steps / (1 if tiles else world),
                 "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(S.PtCamera), "d2h_bytes_per_step": W * H * 16,
-                        "ms_per_step": 1e3 * e2e_s / args.steps, "spp_per_s": spp * args.steps * world / e2e_s},
+                        "ms_per_step": 1e3 * e2e_s / args.steps, "spp_per_s": spp * frames_done / e2e_s},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())

@@ -59,6 +59,7 @@ struct PtRenderer {
     bool have_last_cam = false;
     // standalone trace buffers
     uint32_t* d_cursor = nullptr;
+    bool peer_root = false;   // pt_ipc_export_image was called: other ranks store their tiles into d_image
 };
 
 namespace {
@@ -330,7 +331,8 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     fp.id_inst = r->d_ids; fp.id_prim = r->d_ids + px; fp.id_tri = r->d_ids + 2 * px;
     PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
     PT_CUDA_CHECK(cudaMemsetAsync(pb.trace_next, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
-    if (r->pm.world > 1 && !r->d_remote_image) PT_CUDA_CHECK(cudaMemsetAsync(r->d_image, 0, px * 16, st));
+    // tile partition: non-owned pixels must read as 0 for the sum-reduce; not when peers store into this image
+    if (r->pm.world > 1 && !r->d_remote_image && !r->peer_root) PT_CUDA_CHECK(cudaMemsetAsync(r->d_image, 0, px * 16, st));
     size_t ev = 0;
     auto mark = [&](int kind) {
         if (!r->profiling) return;
@@ -659,6 +661,7 @@ int pt_ipc_export_image(PtRenderer* r, uint8_t handle[64]) {
     PT_CUDA_CHECK(cudaSetDevice(r->device));
     PT_CUDA_CHECK(cudaIpcGetMemHandle(&h, r->d_image));
     std::memcpy(handle, &h, 64);
+    r->peer_root = true;   // from now on the image is written by every rank: never cleared per frame
     return PT_OK;
 }
 
