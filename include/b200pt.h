@@ -132,6 +132,8 @@ enum {
     PT_FLAG_TRACE_BVH2 = 1u << 1,         /* use the simple BVH2 reference walker, not the BVH8 kernel */
     PT_FLAG_NO_PRIMARY_REUSE = 1u << 2,   /* re-trace the (identical) primary ray for every sample */
     PT_FLAG_TRACE_WALKER = 1u << 3,       /* simple one-ray-per-thread BVH8 walker instead of the persistent kernel */
+    PT_FLAG_NO_TEXTURE_INTERLEAVE = 1u << 5,   /* keep every texture separate (A/B switch): by default the maps of a
+                                             material that share one extent are interleaved per texel on the device */
     PT_FLAG_BVH_PLOC = 1u << 4            /* build the binary hierarchy by locally-ordered clustering (PLOC) instead of
                                              the Morton radix tree (LBVH): slower build, better trees for irregular meshes */
 };

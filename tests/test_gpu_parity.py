@@ -195,6 +195,21 @@ def test_material_sorted_shading_is_bit_identical():
     assert_matches_oracle(ps, 200, 120, 3, 4, 1, flags=b200pt.PT_FLAG_SORT_BY_MATERIAL)
 
 
+def test_interleaved_material_textures_are_bit_identical():
+    """Maps of one material that share an extent are interleaved per texel on the device (MatRec::atlas);
+    materials with differently sized maps, or a single map, keep separate textures.  Same image either way."""
+    sb = S.atrium(1234, 20000, 6, 64)
+    rng = np.random.default_rng(9)
+    small = sb.add_texture(rng.integers(0, 256, (16, 32, 4), dtype=np.uint8))      # 32x16: not the 64x64 of the others
+    sb.materials[1]["normal_tex"] = small                                          # mixed extents -> fallback path
+    sb.materials[2]["mr_tex"] = None; sb.materials[2]["normal_tex"] = None         # a single map -> fallback path
+    ps = sb.pack()
+    a_img, a_ids, _ = render(ps, 200, 120, 2, 4, 2)
+    b_img, b_ids, _ = render(ps, 200, 120, 2, 4, 2, flags=b200pt.PT_FLAG_NO_TEXTURE_INTERLEAVE)
+    assert bits_equal(a_img, b_img).all() and all((x == y).all() for x, y in zip(a_ids, b_ids))
+    assert_matches_oracle(ps, 200, 120, 2, 4, 2)
+
+
 def test_identity_and_transformed_instances_mix():
     """Identity instances are entered without re-deriving the ray frame (kInstIdentity); leaving a
     transformed instance must restore the world frame before the next identity instance is entered."""

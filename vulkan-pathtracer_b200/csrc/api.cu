@@ -5,6 +5,8 @@
 #include <cmath>
 #include <cstring>
 #include <string>
+#include <array>
+#include <map>
 #include <vector>
 
 #include "bvh_build.h"
@@ -31,6 +33,7 @@ struct PtRenderer {
     MatRec* d_materials = nullptr;
     TexRec* d_textures = nullptr;
     std::vector<uint32_t*> d_texels;
+    std::vector<uint4*> d_atlases;   // interleaved material textures (MatRec::atlas)
     PtInstance* d_instances_raw = nullptr;
     InstanceRec* d_instances = nullptr;
     SceneBvh bvh;
@@ -171,13 +174,36 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     if ((rc = dev_alloc(&r->d_textures, texs.size())) != PT_OK) return rc;
     if (!texs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_textures, texs.data(), texs.size() * sizeof(TexRec), cudaMemcpyHostToDevice));
     std::vector<MatRec> mats(s->num_materials);
+    std::map<std::array<uint32_t, 4>, uint4*> atlas_of;
     for (size_t i = 0; i < s->num_materials; ++i) {
         const PtMaterial& m = s->materials[i];
         MatRec& d = mats[i];
-        d.albedo_factor = m.albedo_factor; d.metal_roughness_factor = m.metal_roughness_factor; d.emissive_factor = m.emissive_factor; d._pad = 0;
+        d.albedo_factor = m.albedo_factor; d.metal_roughness_factor = m.metal_roughness_factor; d.emissive_factor = m.emissive_factor; d.present = 0;
         const uint32_t t[4] = {m.albedo_texture_index, m.metal_roughness_texture_index, m.emissive_texture_index, m.normal_texture_index};
         for (int k = 0; k < 4; ++k) d.tex[k] = (t[k] == PT_INVALID_TEXTURE) ? TexRec{nullptr, 0, 0} : texs[t[k]];
+        d.atlas = nullptr; d.atlas_width = 0; d.atlas_height = 0;
+        // interleave the material's maps when they can share one set of texel coordinates
+        uint32_t n_present = 0, w = 0, h = 0; bool same = true;
+        for (int k = 0; k < 4; ++k) {
+            if (!d.tex[k].texels) continue;
+            d.present |= 1u << k;
+            if (n_present++ == 0) { w = d.tex[k].width; h = d.tex[k].height; }
+            else same = same && d.tex[k].width == w && d.tex[k].height == h;
+        }
+        if (n_present >= 2 && same && !(r->cfg.flags & PT_FLAG_NO_TEXTURE_INTERLEAVE)) {
+            const std::array<uint32_t, 4> key = {t[0], t[1], t[2], t[3]};
+            auto it = atlas_of.find(key);
+            if (it == atlas_of.end()) {
+                uint4* a = nullptr;
+                if ((rc = dev_alloc(&a, (size_t)w * h)) != PT_OK) return rc;
+                r->d_atlases.push_back(a);
+                launch_interleave_textures(d.tex[0].texels, d.tex[1].texels, d.tex[2].texels, d.tex[3].texels, (size_t)w * h, a, r->stream);
+                it = atlas_of.emplace(key, a).first;
+            }
+            d.atlas = it->second; d.atlas_width = w; d.atlas_height = h;
+        }
     }
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
     if ((rc = dev_alloc(&r->d_materials, mats.size())) != PT_OK) return rc;
     if (!mats.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_materials, mats.data(), mats.size() * sizeof(MatRec), cudaMemcpyHostToDevice));
     // meshes / instances
@@ -227,6 +253,7 @@ void destroy_impl(PtRenderer* r) {
     free_frame(r);
     for (auto e : r->events) cudaEventDestroy(e);
     for (auto p : r->d_texels) cudaFree(p);
+    for (auto p : r->d_atlases) cudaFree(p);
     cudaFree(r->d_blob); cudaFree(r->d_prims); cudaFree(r->d_materials); cudaFree(r->d_textures);
     cudaFree(r->d_instances_raw); cudaFree(r->d_instances); cudaFree(r->d_cursor);
     if (r->d_remote_image) cudaIpcCloseMemHandle(r->d_remote_image);

@@ -26,6 +26,7 @@ struct SceneBvh {
     std::vector<uint32_t> tri_count;    // per mesh
     float* mesh_bounds = nullptr;       // device, 6 floats per mesh
     float ms_build = 0.0f;
+    uint32_t refit_repairs = 0;         // nodes corrected by the refit verification (expected 0)
 
     void release();
 };

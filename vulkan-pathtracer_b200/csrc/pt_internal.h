@@ -78,12 +78,17 @@ struct TexRec { const uint32_t* texels; uint32_t width, height; };  // RGBA8 pac
 
 // Device material: the reference's 28-byte Material (material.glsl:7-16) with the four texture
 // indices resolved to texel pointers + extents (texels == nullptr: no texture), so that shading
-// needs one dependent load less per texture.  80 bytes, 16-byte aligned.
+// needs one dependent load less per texture.  When at least two textures are present and all
+// present ones have the same extent, `atlas` holds them interleaved per texel as one uint4
+// (albedo, metal-roughness, emissive, normal RGBA8 words): the three or four bilinear taps that
+// material.glsl takes at the same uv then cost four 16-byte loads and about a third of the DRAM
+// sectors of separate textures.  `present` = bit k set when texture k exists.  96 bytes.
 struct __align__(16) MatRec {
-    uint32_t albedo_factor, metal_roughness_factor, emissive_factor, _pad;
+    uint32_t albedo_factor, metal_roughness_factor, emissive_factor, present;
     TexRec tex[4];   // albedo, metal-roughness, emissive, normal
+    const uint4* atlas; uint32_t atlas_width, atlas_height;
 };
-static_assert(sizeof(MatRec) == 80, "MatRec must be 80 bytes");
+static_assert(sizeof(MatRec) == 96, "MatRec must be 96 bytes");
 
 struct DeviceScene {
     const uint8_t* triangle_data;

@@ -315,6 +315,12 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
     }
 }
 
+__global__ void k_interleave_textures(const uint32_t* __restrict__ t0, const uint32_t* __restrict__ t1, const uint32_t* __restrict__ t2,
+                                      const uint32_t* __restrict__ t3, size_t n, uint4* __restrict__ out) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = make_uint4(t0 ? t0[i] : 0xFFFFFFFFu, t1 ? t1[i] : 0xFFFFFFFFu, t2 ? t2[i] : 0xFFFFFFFFu, t3 ? t3[i] : 0xFFFFFFFFu);
+}
+
 // ------------------------------------------------------------------ post-processing
 // fp32 RGBA -> b8g8r8a8_unorm as the reference's storage image does (Swapchain.zig:115-118):
 // NaN -> 0, clamp to [0,1], round to nearest.
@@ -483,6 +489,10 @@ void launch_debug_texture(TexRec tex, uint32_t n, const float* uv, float* out, c
     if (n) k_debug_texture<<<(n + 127) / 128, 128, 0, st>>>(tex, n, uv, out);
 }
 
+void launch_interleave_textures(const uint32_t* t0, const uint32_t* t1, const uint32_t* t2, const uint32_t* t3, size_t n, uint4* out,
+                                cudaStream_t st) {
+    if (n) k_interleave_textures<<<1184, 256, 0, st>>>(t0, t1, t2, t3, n, out);
+}
 void launch_to_bgra8(const float* rgba, uint8_t* bgra, uint32_t n_pixels, cudaStream_t st) {
     if (n_pixels) k_to_bgra8<<<(n_pixels + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(rgba), reinterpret_cast<uchar4*>(bgra), n_pixels);
 }

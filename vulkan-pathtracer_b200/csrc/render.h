@@ -61,6 +61,9 @@ void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& 
 void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
                        uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, float4* setup /* 5*n */,
                        int num_sms, cudaStream_t st);
+// material texture interleave (MatRec::atlas): out[i] = (t0[i], t1[i], t2[i], t3[i]); absent maps read as 0xFFFFFFFF
+void launch_interleave_textures(const uint32_t* t0, const uint32_t* t1, const uint32_t* t2, const uint32_t* t3, size_t n, uint4* out,
+                                cudaStream_t st);
 // image post-processing
 void launch_to_bgra8(const float* rgba, uint8_t* bgra, uint32_t n_pixels, cudaStream_t st);
 void launch_upscale(const float* src, uint32_t sw, uint32_t sh, float* dst, uint32_t dw, uint32_t dh, cudaStream_t st);

@@ -299,18 +299,40 @@ struct MaterialData { V4 albedo; V3 normal, emissive; float roughness, metallic;
 // material.glsl:31-69
 PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& td) {
     const MatRec* mp = sc.materials + td.material_index;
-    const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));     // factors
+    const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));     // factors + presence bits
+    const uint4 aw = __ldg(reinterpret_cast<const uint4*>(mp) + 5);  // interleaved texels, if any
+    const uint4* atlas = reinterpret_cast<const uint4*>(((uint64_t)aw.y << 32) | aw.x);
     TexRec tex[4];
     Taps taps[4];
+    if (atlas) {
+        // one set of texel coordinates, four 16-byte fetches: every present map's 2x2 footprint at once
+        TexRec at; at.texels = nullptr; at.width = aw.z; at.height = aw.w;
+        const float W = (float)at.width, H = (float)at.height;
+        const float u = td.uv.x * W - 0.5f, v = td.uv.y * H - 0.5f;
+        const float fu = floorf(u), fv = floorf(v);
+        const float a = u - fu, b = v - fv;
+        const uint32_t x0 = wrap_texel(fu, at.width), x1 = (x0 + 1 == at.width) ? 0u : x0 + 1;
+        const uint32_t y0 = wrap_texel(fv, at.height), y1 = (y0 + 1 == at.height) ? 0u : y0 + 1;
+        const uint4* r0 = atlas + (size_t)y0 * at.width;
+        const uint4* r1 = atlas + (size_t)y1 * at.width;
+        const uint4 q00 = __ldg(r0 + x0), q10 = __ldg(r0 + x1), q01 = __ldg(r1 + x0), q11 = __ldg(r1 + x1);
+        taps[0] = Taps{q00.x, q10.x, q01.x, q11.x, a, b};
+        taps[1] = Taps{q00.y, q10.y, q01.y, q11.y, a, b};
+        taps[2] = Taps{q00.z, q10.z, q01.z, q11.z, a, b};
+        taps[3] = Taps{q00.w, q10.w, q01.w, q11.w, a, b};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const uint4 w = __ldg(reinterpret_cast<const uint4*>(mp) + 1 + k);
-        tex[k].texels = reinterpret_cast<const uint32_t*>(((uint64_t)w.y << 32) | w.x);
-        tex[k].width = w.z; tex[k].height = w.w;
+        for (int k = 0; k < 4; ++k) tex[k].texels = ((fac.w >> k) & 1u) ? reinterpret_cast<const uint32_t*>(atlas) : nullptr;   // presence only
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint4 w = __ldg(reinterpret_cast<const uint4*>(mp) + 1 + k);
+            tex[k].texels = reinterpret_cast<const uint32_t*>(((uint64_t)w.y << 32) | w.x);
+            tex[k].width = w.z; tex[k].height = w.w;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (tex[k].texels) taps[k] = fetch_taps(tex[k], td.uv);
     }
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-        if (tex[k].texels) taps[k] = fetch_taps(tex[k], td.uv);
     MaterialData md;
     md.albedo = unpack_unorm4x8(fac.x);                                                  // :36
     if (tex[0].texels) {                                                                 // :37-39
