@@ -287,9 +287,13 @@ def main():
         r.record(cam, sp)
         combine()
         if rank == 0:
-            b200pt.check(b200pt.lib().pt_read_rgba32f_async(r.handle, host_img.data_ptr(), sp))
+            if peer:    # the fence below is ordered on `sp`, so the copy has to be too
+                b200pt.check(b200pt.lib().pt_read_rgba32f_async(r.handle, host_img.data_ptr(), sp))
+            else:       # copy of frame k overlaps ray generation + primary traversal of frame k+1
+                b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, host_img.data_ptr()))
         if peer:
             dist.all_reduce(fence)      # the next frame's peer stores must not overtake rank 0's read-back
+    r.sync()            # the last pipelined read-back
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")

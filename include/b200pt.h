@@ -242,6 +242,11 @@ int pt_read_bgra8(PtRenderer* r, uint8_t* host_dst);
  * memory supplied by the caller; complete after pt_sync or a sync of the stream. */
 int pt_read_rgba32f_async(PtRenderer* r, float* pinned_host_dst, void* cuda_stream);
 int pt_read_bgra8_async(PtRenderer* r, uint8_t* pinned_host_dst, void* cuda_stream);
+/* Pipelined variant for frame loops (the analogue of presenting image i while frame i+1 is recorded,
+ * main.zig:232-345): the copy is ordered after the last pt_render but runs on the renderer's own copy
+ * stream; the next pt_render only waits for it before its first write to the image, so the copy overlaps
+ * ray generation and primary traversal of the next frame.  Complete after pt_sync. */
+int pt_read_rgba32f_overlapped(PtRenderer* r, float* pinned_host_dst);
 /* Primary-hit id buffers of the last frame (parity: instance / primitive_index / triangle_index,
  * 0xFFFFFFFF on miss).  Any pointer may be NULL. */
 int pt_read_ids(PtRenderer* r, uint32_t* instance, uint32_t* primitive, uint32_t* triangle);

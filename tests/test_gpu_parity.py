@@ -336,6 +336,26 @@ def test_render_is_asynchronous_and_repeatable():
     r.deinit()
 
 
+def test_pipelined_readback_returns_every_frame_intact():
+    """pt_read_rgba32f_overlapped: the copy of frame k runs beside frame k+1; no frame may be torn."""
+    import torch
+    ps = S.atrium(1234, 20000, 6, 64).pack()
+    W, H = 640, 360
+    r = b200pt.Renderer(ps, W, H, 1, 3)
+    want = []
+    for f in range(4):
+        r.record(S.camera_default(W, H, f)); r.sync(); want.append(r.image().copy())
+    bufs = [torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True) for _ in range(4)]
+    for rep in range(3):
+        for f in range(4):
+            r.record(S.camera_default(W, H, f))
+            b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, bufs[f].data_ptr()))
+        r.sync()
+        for f in range(4):
+            assert bits_equal(bufs[f].numpy(), want[f]).all(), f"frame {f} torn in repetition {rep}"
+    r.deinit()
+
+
 def test_invalid_scene_is_rejected():
     import ctypes as C
     ps = S.cornell().pack()

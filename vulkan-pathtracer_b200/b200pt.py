@@ -84,6 +84,7 @@ def lib():
         L.pt_get_stats.argtypes = [C.c_void_p, C.POINTER(PtStats)]
         L.pt_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         L.pt_count_traversal.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.pt_read_rgba32f_overlapped.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_ipc_export_image.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_ipc_open_root_image.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_camera_new.argtypes = [C.c_float, C.c_float, C.POINTER(C.c_float * 3), C.c_float, C.c_float, C.c_uint32,

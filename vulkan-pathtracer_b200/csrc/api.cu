@@ -27,6 +27,11 @@ struct PtRenderer {
     int num_sms = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t last_stream = nullptr;   // stream of the most recent pt_render (caller's or our own)
+    // pipelined read-back (pt_read_*_overlapped): the copy runs on its own stream, the next frame only
+    // waits for it before its first image write (K-shade of iteration 0)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_frame_done = nullptr, ev_copy_done = nullptr;
+    bool copy_pending = false;
     // scene on the device
     uint8_t* d_blob = nullptr;
     PrimRec* d_prims = nullptr;
@@ -258,6 +263,9 @@ void destroy_impl(PtRenderer* r) {
     cudaFree(r->d_instances_raw); cudaFree(r->d_instances); cudaFree(r->d_cursor);
     if (r->d_remote_image) cudaIpcCloseMemHandle(r->d_remote_image);
     r->bvh.release();
+    if (r->copy_stream) { cudaStreamSynchronize(r->copy_stream); cudaStreamDestroy(r->copy_stream); }
+    if (r->ev_frame_done) cudaEventDestroy(r->ev_frame_done);
+    if (r->ev_copy_done) cudaEventDestroy(r->ev_copy_done);
     if (r->stream) cudaStreamDestroy(r->stream);
     delete r;
 }
@@ -358,6 +366,11 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     fp.id_inst = r->d_ids; fp.id_prim = r->d_ids + px; fp.id_tri = r->d_ids + 2 * px;
     PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
     PT_CUDA_CHECK(cudaMemsetAsync(pb.trace_next, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
+    bool waited_copy = !r->copy_pending;
+    auto wait_copy = [&]() {   // a pipelined read-back of the previous frame must finish before the image is written again
+        if (!waited_copy) { cudaStreamWaitEvent(st, r->ev_copy_done, 0); waited_copy = true; r->copy_pending = false; }
+    };
+    if (r->pm.world > 1 && !r->d_remote_image && !r->peer_root) wait_copy();
     // tile partition: non-owned pixels must read as 0 for the sum-reduce; not when peers store into this image
     if (r->pm.world > 1 && !r->d_remote_image && !r->peer_root) PT_CUDA_CHECK(cudaMemsetAsync(r->d_image, 0, px * 16, st));
     size_t ev = 0;
@@ -373,10 +386,12 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     };
     auto mark_end = [&]() { if (r->profiling) { cudaEventRecord(r->events[ev + 1], st); ev += 2; } };
     uint32_t launches = 0;
+    if (r->max_iters == 0) wait_copy();   // S == 0 or B == 0: K-raygen itself writes the (black) image
     mark(2); launch_raygen(r->pm, pb, fp, st); mark_end(); ++launches;
     for (uint32_t it = 0; it < r->max_iters; ++it) {
         mark(0); launch_trace(r->scene, pb, it, mode, r->bvh.tlas2_count, r->bvh.tlas2_leaf_instance, r->num_sms, st); mark_end();
         if (fp.flags & PT_FLAG_SORT_BY_MATERIAL) { mark(2); launch_material_sort(r->scene, pb, it, r->num_sms, st); mark_end(); launches += 3; }
+        wait_copy();
         mark(1); launch_shade(r->scene, r->pm, pb, fp, it, r->num_sms, st); mark_end();
         launches += 2;
     }
@@ -411,6 +426,7 @@ int pt_sync(PtRenderer* r) {
     PT_CUDA_CHECK(cudaSetDevice(r->device));
     if (r->last_stream && r->last_stream != r->stream) PT_CUDA_CHECK(cudaStreamSynchronize(r->last_stream));
     PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    if (r->copy_stream) PT_CUDA_CHECK(cudaStreamSynchronize(r->copy_stream));
     return PT_OK;
 }
 
@@ -441,6 +457,29 @@ int pt_read_rgba32f_async(PtRenderer* r, float* dst, void* cuda_stream) {
     cudaStream_t st = follow_stream(r, cuda_stream);
     PT_CUDA_CHECK(cudaMemcpyAsync(dst, r->d_image, (size_t)r->pm.width * r->pm.height * 16, cudaMemcpyDeviceToHost, st));
     return PT_OK;
+}
+
+// Pipelined read-back: the device->host copy of the current image is ordered after everything
+// enqueued so far on the render stream but runs on the renderer's copy stream, so it overlaps the
+// next frame's ray generation and primary traversal (which do not touch the image).
+static int overlapped_copy(PtRenderer* r, void* dst, const void* src, size_t bytes, cudaStream_t after) {
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    if (!r->copy_stream) {
+        PT_CUDA_CHECK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
+        PT_CUDA_CHECK(cudaEventCreateWithFlags(&r->ev_frame_done, cudaEventDisableTiming));
+        PT_CUDA_CHECK(cudaEventCreateWithFlags(&r->ev_copy_done, cudaEventDisableTiming));
+    }
+    PT_CUDA_CHECK(cudaEventRecord(r->ev_frame_done, after));
+    PT_CUDA_CHECK(cudaStreamWaitEvent(r->copy_stream, r->ev_frame_done, 0));
+    PT_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, r->copy_stream));
+    PT_CUDA_CHECK(cudaEventRecord(r->ev_copy_done, r->copy_stream));
+    r->copy_pending = true;
+    return PT_OK;
+}
+
+int pt_read_rgba32f_overlapped(PtRenderer* r, float* pinned_host_dst) {
+    PT_REQUIRE(r && pinned_host_dst, "pt_read_rgba32f_overlapped: null argument");
+    return overlapped_copy(r, pinned_host_dst, r->d_image, (size_t)r->pm.width * r->pm.height * 16, follow_stream(r, nullptr));
 }
 
 int pt_read_rgba32f(PtRenderer* r, float* host_dst) {
