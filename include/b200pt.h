@@ -285,7 +285,7 @@ int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t h
                      float* rgba4);
 
 /* Process-wide kernel tuning knobs (measurement only; results never depend on them).
- *   "postpone": K-trace postpones triangle tests while fewer than this many lanes have one pending. */
+ *   "postpone": retired (triangle postponing was measured flat and removed); accepted, no effect. */
 int pt_set_option(const char* key, int value);
 
 /* Multi-GPU (one process per GPU).  Peer stores: rank 0 exports its image buffer as a CUDA IPC

@@ -407,11 +407,10 @@ int persistent_blocks(K kernel, int threads, int num_sms) {
 
 }  // namespace
 
-// tuning knobs (defaults chosen from the sweeps in profiles/); see pt_set_option
-static int g_postpone = 8;
-static uint32_t trace_postpone_threshold() { return (uint32_t)g_postpone; }
+// tuning knobs; see pt_set_option
 int set_option(const char* key, int value) {
-    if (!strcmp(key, "postpone")) { g_postpone = value < 0 ? 0 : (value > 33 ? 33 : value); return 0; }
+    (void)value;
+    if (!strcmp(key, "postpone")) return 0;   // retired knob (triangle postponing was removed from K-trace); accepted, no effect
     return -1;
 }
 
@@ -433,7 +432,7 @@ void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, T
         TraceIO io;
         io.queue = pb.queue[iter & 1u]; io.count_ptr = pb.qcount + iter; io.count = 0; io.cursor = pb.trace_next + iter;
         io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.ray_e = pb.ray_e; io.ray_s = pb.ray_s; io.ray_m = pb.ray_m; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
-        io.hit_a_stride = 1; io.hit_b_stride = 1; io.postpone_below = trace_postpone_threshold(); io.bias_word = 0x4B000000u;
+        io.hit_a_stride = 1; io.hit_b_stride = 1; io.bias_word = 0x4B000000u;
         k_trace_persistent<<<blocks[3], kTraceBlock, 0, st>>>(sc, io);
         return;
     }
@@ -469,7 +468,7 @@ void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, Hi
         io.queue = nullptr; io.count_ptr = nullptr; io.count = n; io.cursor = cursor;
         io.ray_o = so; io.ray_d = sd; io.ray_e = se; io.ray_s = ss; io.ray_m = sm;
         io.hit_a = reinterpret_cast<float4*>(hits); io.hit_a_stride = 2;
-        io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4; io.postpone_below = trace_postpone_threshold();
+        io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4;
         io.bias_word = 0x4B000000u;
         k_trace_persistent<<<blocks, kTraceBlock, 0, st>>>(sc, io);
         return;

@@ -105,7 +105,6 @@ struct TraceIO {
     uint2* hit_b;               // per slot: primitive_index, triangle_index
     uint32_t hit_a_stride;      // in float4: 1 = SoA, 2 = HitRec array
     uint32_t hit_b_stride;      // in uint2:  1 = SoA, 4 = HitRec array (hit_b = base + 2)
-    uint32_t postpone_below;    // triangle tests are postponed while fewer lanes than this have one pending
     uint32_t bias_word;         // 0x4B000000 (see q2f)
 };
 
@@ -202,15 +201,11 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             if (exhausted) break;
             continue;
         }
-        // ---- phase 1: one leaf item.  Triangle tests run at low SIMD utilisation when only a few
-        // lanes have one pending: such lanes postpone the group (push it) and keep descending
-        // (Ylitie et al. 2017, "postponing"); a popped group is always tested (no node work left).
+        // ---- phase 1: one leaf item.  (Postponing triangle groups while few lanes hold one — Ylitie et
+        // al. 2017 — and repeating the phase while many do were both measured: neither pays here, and the
+        // warp votes they need cost 3-4 % each; profiles/r1_experiments.md.)
         const bool has_t = active && T.y != 0u;
-        const uint32_t n_t = __popc(__ballot_sync(0xffffffffu, has_t));
-        if (has_t && n_t < io.postpone_below && cur_inst != kInvalidId && (G.y & 0xFF000000u) != 0u && sp < kStackSize) {
-            stack[sp++] = T;
-            T.y = 0u;
-        } else if (has_t) {
+        if (has_t) {
             const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
             T.y &= T.y - 1u;
             if (cur_inst != kInvalidId) {
