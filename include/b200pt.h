@@ -215,6 +215,40 @@ void pt_scene_free(PtScene* scene);
 int pt_camera_new(float fov, float aspect_ratio, const float position[3], float yaw_deg,
                   float pitch_deg, uint32_t frame_count, PtCamera* out);
 
+/* ------------------------------------------------------------------ interactive camera  (src/Camera.zig:10-102)
+ * The whole Camera value, so that a recorded input/timer trace can be replayed headless.
+ * Angles in degrees, rotation as (w, x, y, z). */
+typedef struct PtCameraState {
+    float fov, aspect_ratio;
+    float position[3];
+    float rotation[4];
+    float pitch, yaw;
+    float forward[3], left[3], up[3];
+    float horizontal[3], vertical[3];
+} PtCameraState;
+
+enum PtKey {            /* the keys Camera.update reads (Camera.zig:65-78) */
+    PT_KEY_W = 1u << 0, PT_KEY_S = 1u << 1, PT_KEY_D = 1u << 2, PT_KEY_A = 1u << 3,
+    PT_KEY_SPACE = 1u << 4, PT_KEY_LEFT_CTRL = 1u << 5, PT_KEY_LEFT_SHIFT = 1u << 6
+};
+
+/* One frame of Input + Timer as Camera.update sees them (Input.zig:16-19, Timer.zig:6). */
+typedef struct PtInput {
+    uint32_t keys;                 /* PT_KEY_* currently held */
+    uint32_t mouse_left;           /* isMouseButtonPressed(.left) */
+    int32_t cursor_delta_x, cursor_delta_y;
+    float delta_time;              /* Timer.delta_time, seconds */
+} PtInput;
+
+/* Camera.new (Camera.zig:25-46) */
+int pt_camera_state_new(float fov, float aspect_ratio, const float position[3], PtCameraState* out);
+/* Camera.update (Camera.zig:48-79): mouse look while the left button is held, WASD / space / ctrl motion */
+int pt_camera_update(PtCameraState* camera, const PtInput* input);
+/* Camera.updateAspectRatio (Camera.zig:81-84), called after a resize (main.zig:346) */
+int pt_camera_update_aspect_ratio(PtCameraState* camera, float aspect_ratio);
+/* the push-constant block of one frame (RaytracingPass.zig:563-569) */
+int pt_camera_pack(const PtCameraState* camera, uint32_t frame_count, PtCamera* out);
+
 /* ------------------------------------------------------------------ RaytracingPass
  * init    src/RaytracingPass.zig:87-200  (scene upload, BLAS/TLAS build -> GPU BVH8 builder) */
 int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer** out);
@@ -283,6 +317,12 @@ int pt_debug_bsdf(int device, size_t n, const float* normal3, const float* view3
 int pt_debug_rng(int device, size_t n, const uint32_t* pixel_xy_frame3, uint32_t draws, uint32_t* state2, float* xi2);
 int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t height, size_t n, const float* uv2,
                      float* rgba4);
+
+/* Animated instances: replace all instance transforms (num_instances x 16 floats, the
+ * rows of M as in PtInstance.transform; mesh indices unchanged) and rebuild the top-level structure on the
+ * device -- Tlas.init (Tlas.zig:15-182) run again.  Synchronises with frames in flight; *ms_rebuild (may be
+ * NULL) receives the device time of the rebuild.  Resets the progressive accumulation. */
+int pt_set_instance_transforms(PtRenderer* r, const float* transforms, size_t num_instances, float* ms_rebuild);
 
 /* Process-wide kernel tuning knobs (measurement only; results never depend on them).
  *   "postpone": retired (triangle postponing was measured flat and removed); accepted, no effect. */

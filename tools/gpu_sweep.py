@@ -16,11 +16,11 @@ def measure(r, W, H, frames=8, warm=2):
     return tr / frames, sh / frames, ot / frames, rays / frames
 
 def main():
-    what = sys.argv[1] if len(sys.argv) > 1 else "postpone"
+    what = sys.argv[1] if len(sys.argv) > 1 else "one"
     name = sys.argv[2] if len(sys.argv) > 2 else "c2"
     builder, W, H, spp, seg = S.CONFIGS[name]
     ps = builder(1234).pack()
-    if what == "postpone":
+    if what == "postpone":   # retired knob (profiles/r1_experiments.md); the option is a no-op now
         r = b200pt.Renderer(ps, W, H, spp, seg)
         ref = None
         for v in (0, 2, 4, 6, 8, 12, 16, 20, 24, 33):

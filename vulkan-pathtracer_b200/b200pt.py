@@ -42,6 +42,24 @@ class PtStats(C.Structure):
                 ("ms_build", C.c_float)]
 
 
+class PtCameraState(C.Structure):
+    """Camera (Camera.zig:10-23): angles in degrees, rotation (w, x, y, z)."""
+    _fields_ = [("fov", C.c_float), ("aspect_ratio", C.c_float), ("position", C.c_float * 3), ("rotation", C.c_float * 4),
+                ("pitch", C.c_float), ("yaw", C.c_float), ("forward", C.c_float * 3), ("left", C.c_float * 3),
+                ("up", C.c_float * 3), ("horizontal", C.c_float * 3), ("vertical", C.c_float * 3)]
+
+
+class PtInput(C.Structure):
+    """One frame of Input + Timer as Camera.update reads them (Input.zig:16-19, Timer.zig:6)."""
+    _fields_ = [("keys", C.c_uint32), ("mouse_left", C.c_uint32), ("cursor_delta_x", C.c_int32),
+                ("cursor_delta_y", C.c_int32), ("delta_time", C.c_float)]
+
+
+PT_KEY_W, PT_KEY_S, PT_KEY_D, PT_KEY_A, PT_KEY_SPACE, PT_KEY_LEFT_CTRL, PT_KEY_LEFT_SHIFT = 1, 2, 4, 8, 16, 32, 64
+KEY_NAMES = {"w": PT_KEY_W, "s": PT_KEY_S, "d": PT_KEY_D, "a": PT_KEY_A, "space": PT_KEY_SPACE,
+             "left_ctrl": PT_KEY_LEFT_CTRL, "left_shift": PT_KEY_LEFT_SHIFT}
+
+
 class PtError(RuntimeError):
     def __init__(self, status, name, message):
         super().__init__(f"{name} ({status}): {message}")
@@ -89,6 +107,11 @@ def lib():
         L.pt_ipc_open_root_image.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_camera_new.argtypes = [C.c_float, C.c_float, C.POINTER(C.c_float * 3), C.c_float, C.c_float, C.c_uint32,
                                     C.POINTER(PtCamera)]
+        L.pt_camera_state_new.argtypes = [C.c_float, C.c_float, C.POINTER(C.c_float * 3), C.POINTER(PtCameraState)]
+        L.pt_camera_update.argtypes = [C.POINTER(PtCameraState), C.POINTER(PtInput)]
+        L.pt_camera_update_aspect_ratio.argtypes = [C.POINTER(PtCameraState), C.c_float]
+        L.pt_camera_pack.argtypes = [C.POINTER(PtCameraState), C.c_uint32, C.POINTER(PtCamera)]
+        L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
         L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_write_exr.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_scene_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
@@ -111,6 +134,32 @@ def camera_new(fov, aspect_ratio, position=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0, 
     pos = (C.c_float * 3)(*position)
     check(lib().pt_camera_new(fov, aspect_ratio, C.byref(pos), yaw, pitch, frame_count, C.byref(cam)))
     return cam
+
+
+class Camera:
+    """The reference's Camera value (Camera.zig) for replaying recorded input: new / update / updateAspectRatio."""
+
+    def __init__(self, fov, aspect_ratio, position=(0.0, 0.0, 0.0)):
+        self.state = PtCameraState()
+        pos = (C.c_float * 3)(*position)
+        check(lib().pt_camera_state_new(fov, aspect_ratio, C.byref(pos), C.byref(self.state)))
+
+    def update(self, keys=(), mouse_left=False, cursor_delta=(0, 0), delta_time=0.0):
+        """Camera.update(input, timer) (Camera.zig:48-79); `keys` are names from KEY_NAMES or a PT_KEY_* mask."""
+        mask = keys if isinstance(keys, int) else sum(KEY_NAMES[k] for k in set(keys))
+        inp = PtInput(mask, 1 if mouse_left else 0, int(cursor_delta[0]), int(cursor_delta[1]), delta_time)
+        check(lib().pt_camera_update(C.byref(self.state), C.byref(inp)))
+        return self
+
+    def update_aspect_ratio(self, aspect_ratio):
+        check(lib().pt_camera_update_aspect_ratio(C.byref(self.state), aspect_ratio))
+        return self
+
+    def pack(self, frame_count=0):
+        """The push constants of one frame (RaytracingPass.zig:563-569)."""
+        cam = PtCamera()
+        check(lib().pt_camera_pack(C.byref(self.state), frame_count, C.byref(cam)))
+        return cam
 
 
 class LoadedScene:
@@ -216,6 +265,13 @@ class Renderer:
         out = np.empty((self.height, self.width, 4), np.float32)
         check(lib().pt_read_accum_mean(self.handle, out.ctypes.data, total_frames))
         return out
+
+    def set_instance_transforms(self, transforms):
+        """Animated instances: new (n, 16) row-major matrices, top level rebuilt on the device; returns the ms."""
+        t = np.ascontiguousarray(transforms, np.float32).reshape(-1, 16)
+        ms = C.c_float(0.0)
+        check(lib().pt_set_instance_transforms(self.handle, t.ctypes.data, t.shape[0], C.byref(ms)))
+        return ms.value
 
     def set_profiling(self, on):
         check(lib().pt_set_profiling(self.handle, 1 if on else 0))

@@ -41,6 +41,7 @@ struct PtRenderer {
     std::vector<uint4*> d_atlases;   // interleaved material textures (MatRec::atlas)
     PtInstance* d_instances_raw = nullptr;
     InstanceRec* d_instances = nullptr;
+    std::vector<PtInstance> h_instances;   // host copy (animated instances: pt_set_instance_transforms)
     SceneBvh bvh;
     DeviceScene scene{};
     uint64_t num_triangles = 0;
@@ -127,6 +128,30 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
     PT_CUDA_CHECK(cudaMemset(r->d_ids, 0xff, std::max<size_t>(px, 1) * 12));
     PT_CUDA_CHECK(cudaMemset(b.trav_counters, 0, 16));
     r->accum_frames = 0;
+    return PT_OK;
+}
+
+// instance records from r->h_instances: inverse of the 3x3 linear part (host, same formula as every other user)
+static int upload_instance_records(PtRenderer* r) {
+    const std::vector<PtInstance>& inst = r->h_instances;
+    std::vector<InstanceRec> recs(inst.size());
+    for (size_t i = 0; i < inst.size(); ++i) {
+        const float* t = inst[i].transform;   // rows of M; first 12 = 3x4 (Tlas.zig:33-41)
+        M3 A;
+        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) A.m[rr][c] = t[4 * rr + c];
+        const M3 Ai = inverse(A);
+        InstanceRec& ir = recs[i];
+        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) ir.inv[3 * rr + c] = Ai.m[rr][c];
+        ir.inv[9] = t[3]; ir.inv[10] = t[7]; ir.inv[11] = t[11];
+        const uint32_t m = (uint32_t)inst[i].mesh_index;
+        bool identity = t[3] == 0.0f && t[7] == 0.0f && t[11] == 0.0f;
+        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) identity = identity && Ai.m[rr][c] == (rr == c ? 1.0f : 0.0f);
+        ir.mesh = m | (identity ? kInstIdentity : 0u);
+        ir.blas_root = r->bvh.blas_root8[m];
+        ir.bvh2_root = r->bvh.tri_off[m];
+        ir.bvh2_tri_base = r->bvh.tri_off[m];
+    }
+    if (!recs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances, recs.data(), recs.size() * sizeof(InstanceRec), cudaMemcpyHostToDevice));
     return PT_OK;
 }
 
@@ -222,26 +247,9 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     if (!inst.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances_raw, inst.data(), inst.size() * sizeof(PtInstance), cudaMemcpyHostToDevice));
     // acceleration structures (createBlases + Tlas.init)
     if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, (r->cfg.flags & PT_FLAG_BVH_PLOC) != 0, r->stream, &r->bvh)) != PT_OK) return rc;
-    // instance records: inverse of the 3x3 linear part (host, same formula as every other user)
-    std::vector<InstanceRec> recs(inst.size());
-    for (size_t i = 0; i < inst.size(); ++i) {
-        const float* t = inst[i].transform;   // rows of M; first 12 = 3x4 (Tlas.zig:33-41)
-        M3 A;
-        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) A.m[rr][c] = t[4 * rr + c];
-        const M3 Ai = inverse(A);
-        InstanceRec& ir = recs[i];
-        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) ir.inv[3 * rr + c] = Ai.m[rr][c];
-        ir.inv[9] = t[3]; ir.inv[10] = t[7]; ir.inv[11] = t[11];
-        const uint32_t m = (uint32_t)inst[i].mesh_index;
-        bool identity = t[3] == 0.0f && t[7] == 0.0f && t[11] == 0.0f;
-        for (int rr = 0; rr < 3; ++rr) for (int c = 0; c < 3; ++c) identity = identity && Ai.m[rr][c] == (rr == c ? 1.0f : 0.0f);
-        ir.mesh = m | (identity ? kInstIdentity : 0u);
-        ir.blas_root = r->bvh.blas_root8[m];
-        ir.bvh2_root = r->bvh.tri_off[m];
-        ir.bvh2_tri_base = r->bvh.tri_off[m];
-    }
-    if ((rc = dev_alloc(&r->d_instances, recs.size())) != PT_OK) return rc;
-    if (!recs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances, recs.data(), recs.size() * sizeof(InstanceRec), cudaMemcpyHostToDevice));
+    r->h_instances = inst;
+    if ((rc = dev_alloc(&r->d_instances, inst.size())) != PT_OK) return rc;
+    if ((rc = upload_instance_records(r)) != PT_OK) return rc;
     DeviceScene& sc = r->scene;
     sc.triangle_data = r->d_blob; sc.prims = r->d_prims; sc.materials = r->d_materials; sc.textures = r->d_textures;
     sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.node_bits = r->bvh.node_bits8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
@@ -643,6 +651,24 @@ int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t*
     if (nodes) *nodes = c[0];
     if (tris) *tris = c[1];
     if (rays) *rays = st.rays_traced;
+    return PT_OK;
+}
+
+// Animated instances.  The reference fixes the transforms at Tlas.init (Tlas.zig:32-52);
+// this is "Tlas.init again" with new matrices: instance records re-derived, top level rebuilt in place.
+int pt_set_instance_transforms(PtRenderer* r, const float* transforms, size_t num_instances, float* ms_rebuild) {
+    PT_REQUIRE(r && (transforms || num_instances == 0), "pt_set_instance_transforms: null argument");
+    PT_REQUIRE(num_instances == r->h_instances.size(), "pt_set_instance_transforms: instance count differs from the scene's");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    { int rc = pt_sync(r); if (rc != PT_OK) return rc; }       // frames in flight still read the old top level
+    for (size_t i = 0; i < num_instances; ++i) std::memcpy(r->h_instances[i].transform, transforms + 16 * i, sizeof(float) * 16);
+    if (num_instances) PT_CUDA_CHECK(cudaMemcpy(r->d_instances_raw, r->h_instances.data(), num_instances * sizeof(PtInstance), cudaMemcpyHostToDevice));
+    int rc = upload_instance_records(r);
+    if (rc != PT_OK) return rc;
+    rc = rebuild_tlas(&r->bvh, r->d_instances_raw, r->stream, ms_rebuild);
+    if (rc != PT_OK) return rc;
+    r->scene.tlas_root = r->bvh.tlas_root8;
+    r->accum_frames = 0;
     return PT_OK;
 }
 

@@ -573,6 +573,7 @@ struct Scratch {
     uint32_t *cid[2] = {nullptr, nullptr}, *nn = nullptr, *keep = nullptr, *pos = nullptr;
     float *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
     bool lbvh = false;
+    uint32_t capacity = 0;        // entries of wq2 / wq8
     uint32_t refit_repairs = 0;   // nodes the verification pass had to correct (expected 0)
     void release() {
         cudaFree(cid[0]); cudaFree(cid[1]); cudaFree(nn); cudaFree(keep); cudaFree(pos);
@@ -659,6 +660,82 @@ int collapse_tree(Scratch& s, CollapseArgs a, uint32_t n, uint32_t* root_out, cu
 
 }  // namespace
 
+namespace {
+
+#define PT_CU(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return PT_ERR_CUDA; } } while (0)
+
+// scratch for trees of up to L leaves (the caller releases it, also on failure)
+int alloc_scratch(Scratch& s, uint32_t L, size_t max_prims, bool use_ploc, cudaStream_t st) {
+    PT_CU(cudaMalloc(&s.tmp_tris, sizeof(Bvh8Tri) * L));
+    PT_CU(cudaMalloc(&s.leaf_lo, sizeof(float) * 3 * L)); PT_CU(cudaMalloc(&s.leaf_hi, sizeof(float) * 3 * L));
+    PT_CU(cudaMalloc(&s.bounds, sizeof(float) * 8));
+    PT_CU(cudaMalloc(&s.keys_in, 8 * (size_t)L)); PT_CU(cudaMalloc(&s.keys_out, 8 * (size_t)L));
+    PT_CU(cudaMalloc(&s.vals_in, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.vals_out, 4 * (size_t)L));
+    PT_CU(cudaMalloc(&s.parent, 4 * (size_t)(2 * L + 2))); PT_CU(cudaMalloc(&s.flags, 4 * (size_t)L));
+    PT_CU(cudaMalloc(&s.wq2, 4 * (size_t)(L + 8))); PT_CU(cudaMalloc(&s.wq8, 4 * (size_t)(L + 8)));
+    PT_CU(cudaMalloc(&s.counters, 4 * 16)); PT_CU(cudaMemsetAsync(s.counters, 0, 64, st));
+    PT_CU(cudaMalloc(&s.range, sizeof(uint2) * L));
+    PT_CU(cudaMalloc(&s.prim_prefix, 4 * (max_prims + 1)));
+    PT_CU(cub::DeviceRadixSort::SortPairs(nullptr, s.cub_bytes, s.keys_in, s.keys_out, s.vals_in, s.vals_out, (int)L, 0, 63, st));
+    {
+        size_t scan_bytes = 0;
+        PT_CU(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, s.keep, s.pos, (int)L, st));
+        s.cub_bytes = std::max(s.cub_bytes, scan_bytes);
+    }
+    PT_CU(cudaMalloc(&s.cub_temp, std::max<size_t>(s.cub_bytes, 16)));
+    {
+        const char* e = std::getenv("PT_BVH_PLOC");     // A/B switch for tools/; the API switch is PT_FLAG_BVH_PLOC
+        s.lbvh = !(use_ploc || (e && e[0] == '1'));
+    }
+    if (!s.lbvh) {
+        for (int k = 0; k < 2; ++k) {
+            PT_CU(cudaMalloc(&s.cid[k], 4 * (size_t)L)); PT_CU(cudaMalloc(&s.clo[k], 12 * (size_t)L)); PT_CU(cudaMalloc(&s.chi[k], 12 * (size_t)L));
+        }
+        PT_CU(cudaMalloc(&s.nn, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.keep, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.pos, 4 * (size_t)L));
+    }
+    return PT_OK;
+}
+
+// TLAS over the instances that reference a non-empty mesh (Tlas.init, Tlas.zig:15-182).  Its nodes are
+// appended at bvh->tlas_node_base, so a rebuild overwrites the previous TLAS in place.
+int build_tlas(Scratch& s, SceneBvh* out, const PtInstance* d_instances, cudaStream_t st) {
+    const uint32_t NI = (uint32_t)out->valid_inst.size();
+    if (NI == 0) return PT_OK;
+    uint32_t* node_counter = s.counters + 0;
+    uint32_t* tlas_leaf_counter = s.counters + 2;
+    const uint32_t zero = 0;
+    PT_CU(cudaMemcpyAsync(node_counter, &out->tlas_node_base, 4, cudaMemcpyHostToDevice, st));
+    PT_CU(cudaMemcpyAsync(tlas_leaf_counter, &zero, 4, cudaMemcpyHostToDevice, st));
+    PT_CU(cudaMemcpyAsync(s.counters + 5, &zero, 4, cudaMemcpyHostToDevice, st));
+    PT_CU(cudaMemcpyAsync(s.vals_in, out->valid_inst.data(), 4 * (size_t)NI, cudaMemcpyHostToDevice, st));
+    PT_CU(cudaStreamSynchronize(st));
+    uint32_t* ids_unsorted = nullptr;
+    PT_CU(cudaMalloc(&ids_unsorted, 4 * (size_t)NI));
+    int rc = PT_OK;
+    if (cudaMemcpyAsync(ids_unsorted, s.vals_in, 4 * (size_t)NI, cudaMemcpyDeviceToDevice, st) != cudaSuccess) rc = PT_ERR_CUDA;
+    if (rc == PT_OK) {
+        k_init_bounds<<<1, 32, 0, st>>>(s.bounds);
+        k_instance_boxes<<<blocks_for(NI), kThreads, 0, st>>>(d_instances, ids_unsorted, NI, out->mesh_bounds, s.leaf_lo, s.leaf_hi, s.bounds);
+        rc = build_tree(s, NI, out->tlas2, st);
+    }
+    if (rc == PT_OK) {
+        // sorted leaf j -> instance id
+        k_gather_u32<<<blocks_for(NI), kThreads, 0, st>>>(ids_unsorted, s.vals_out, NI, out->tlas2_leaf_instance);
+        CollapseArgs a{};
+        a.nodes2 = out->tlas2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
+        a.max_leaf = 1; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tlas_leaf_counter;
+        a.tris_sorted = nullptr; a.tris8 = nullptr; a.leaf_ids = ids_unsorted; a.leaf_out = out->tlas_leaf_instance;
+        a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = s.counters + 4; a.capacity = s.capacity; a.overflow = s.counters + 5;
+        rc = collapse_tree(s, a, NI, &out->tlas_root8, st);
+    }
+    cudaStreamSynchronize(st);
+    cudaFree(ids_unsorted);
+    return rc;
+}
+#undef PT_CU
+
+}  // namespace
+
 int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::vector<PrimRec>& h_prims,
                     const std::vector<PtMesh>& meshes, const PtInstance* d_instances,
                     const std::vector<PtInstance>& h_instances, bool use_ploc, cudaStream_t st, SceneBvh* out) {
@@ -690,33 +767,8 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
     auto fail = [&](int code) { s.release(); cudaEventDestroy(ev0); cudaEventDestroy(ev1); return code; };
 #define PT_TRY(expr) do { rc = (expr); if (rc != PT_OK) return fail(rc); } while (0)
 #define PT_CU(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return fail(PT_ERR_CUDA); } } while (0)
-    PT_CU(cudaMalloc(&s.tmp_tris, sizeof(Bvh8Tri) * L));
-    PT_CU(cudaMalloc(&s.leaf_lo, sizeof(float) * 3 * L)); PT_CU(cudaMalloc(&s.leaf_hi, sizeof(float) * 3 * L));
-    PT_CU(cudaMalloc(&s.bounds, sizeof(float) * 8));
-    PT_CU(cudaMalloc(&s.keys_in, 8 * (size_t)L)); PT_CU(cudaMalloc(&s.keys_out, 8 * (size_t)L));
-    PT_CU(cudaMalloc(&s.vals_in, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.vals_out, 4 * (size_t)L));
-    PT_CU(cudaMalloc(&s.parent, 4 * (size_t)(2 * L + 2))); PT_CU(cudaMalloc(&s.flags, 4 * (size_t)L));
-    PT_CU(cudaMalloc(&s.wq2, 4 * (size_t)(L + 8))); PT_CU(cudaMalloc(&s.wq8, 4 * (size_t)(L + 8)));
-    PT_CU(cudaMalloc(&s.counters, 4 * 16)); PT_CU(cudaMemsetAsync(s.counters, 0, 64, st));
-    PT_CU(cudaMalloc(&s.range, sizeof(uint2) * L));
-    PT_CU(cudaMalloc(&s.prim_prefix, 4 * (max_prims + 1)));
-    PT_CU(cub::DeviceRadixSort::SortPairs(nullptr, s.cub_bytes, s.keys_in, s.keys_out, s.vals_in, s.vals_out, (int)L, 0, 63, st));
-    {
-        size_t scan_bytes = 0;
-        PT_CU(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, s.keep, s.pos, (int)L, st));
-        s.cub_bytes = std::max(s.cub_bytes, scan_bytes);
-    }
-    PT_CU(cudaMalloc(&s.cub_temp, std::max<size_t>(s.cub_bytes, 16)));
-    {
-        const char* e = std::getenv("PT_BVH_PLOC");     // A/B switch for tools/; the API switch is PT_FLAG_BVH_PLOC
-        s.lbvh = !(use_ploc || (e && e[0] == '1'));
-    }
-    if (!s.lbvh) {
-        for (int k = 0; k < 2; ++k) {
-            PT_CU(cudaMalloc(&s.cid[k], 4 * (size_t)L)); PT_CU(cudaMalloc(&s.clo[k], 12 * (size_t)L)); PT_CU(cudaMalloc(&s.chi[k], 12 * (size_t)L));
-        }
-        PT_CU(cudaMalloc(&s.nn, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.keep, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.pos, 4 * (size_t)L));
-    }
+    PT_TRY(alloc_scratch(s, L, max_prims, use_ploc, st));
+    s.capacity = L + 8;
 
     const size_t cap_nodes = (size_t)total + M + NI + 8;
     PT_CU(cudaMalloc(&out->nodes8, sizeof(Bvh8Node) * cap_nodes));
@@ -731,7 +783,6 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
 
     uint32_t* node_counter = s.counters + 0;
     uint32_t* tri_counter = s.counters + 1;
-    uint32_t* tlas_leaf_counter = s.counters + 2;
     uint32_t* tail = s.counters + 4;      // [4] tail, [5] overflow (read together)
     uint32_t* overflow = s.counters + 5;
 
@@ -758,31 +809,12 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
         a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = tail; a.capacity = L + 8; a.overflow = overflow;
         PT_TRY(collapse_tree(s, a, n, &out->blas_root8[m], st));
     }
-    // ---- TLAS over the instances that reference a non-empty mesh
-    if (NI > 0) {
-        PT_CU(cudaMemcpyAsync(s.vals_in, valid_inst.data(), 4 * (size_t)NI, cudaMemcpyHostToDevice, st));
-        PT_CU(cudaStreamSynchronize(st));
-        // leaf ids live in flags' neighbour: reuse wq buffers is unsafe, keep a dedicated copy in tlas2_leaf_instance (unsorted for now)
-        uint32_t* ids_unsorted = nullptr;
-        PT_CU(cudaMalloc(&ids_unsorted, 4 * (size_t)NI));
-        PT_CU(cudaMemcpyAsync(ids_unsorted, s.vals_in, 4 * (size_t)NI, cudaMemcpyDeviceToDevice, st));
-        k_init_bounds<<<1, 32, 0, st>>>(s.bounds);
-        k_instance_boxes<<<blocks_for(NI), kThreads, 0, st>>>(d_instances, ids_unsorted, NI, out->mesh_bounds, s.leaf_lo, s.leaf_hi, s.bounds);
-        rc = build_tree(s, NI, out->tlas2, st);
-        if (rc == PT_OK) {
-            // sorted leaf j -> instance id
-            k_gather_u32<<<blocks_for(NI), kThreads, 0, st>>>(ids_unsorted, s.vals_out, NI, out->tlas2_leaf_instance);
-            CollapseArgs a{};
-            a.nodes2 = out->tlas2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
-            a.max_leaf = 1; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tlas_leaf_counter;
-            a.tris_sorted = nullptr; a.tris8 = nullptr; a.leaf_ids = ids_unsorted; a.leaf_out = out->tlas_leaf_instance;
-            a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = tail; a.capacity = L + 8; a.overflow = overflow;
-            rc = collapse_tree(s, a, NI, &out->tlas_root8, st);
-        }
-        cudaStreamSynchronize(st);
-        cudaFree(ids_unsorted);
-        if (rc != PT_OK) return fail(rc);
-    }
+    // ---- TLAS
+    PT_CU(cudaMemcpyAsync(&out->tlas_node_base, node_counter, 4, cudaMemcpyDeviceToHost, st));
+    PT_CU(cudaStreamSynchronize(st));
+    out->valid_inst = valid_inst;
+    out->use_ploc = !s.lbvh;
+    PT_TRY(build_tlas(s, out, d_instances, st));
     PT_CU(cudaMemcpyAsync(&out->num_nodes8, node_counter, 4, cudaMemcpyDeviceToHost, st));
     PT_CU(cudaEventRecord(ev1, st));
     PT_CU(cudaStreamSynchronize(st));
@@ -794,6 +826,31 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
 #undef PT_TRY
 #undef PT_CU
     return PT_OK;
+}
+
+// Animated instances: the instance transforms changed (d_instances holds the new ones); mesh indices and the
+// BLASes are unchanged.  The reference has no TLAS update path (Tlas.init is its only builder), so this is
+// a full rebuild of the top level, which costs well under a millisecond for 1 000 instances.
+int rebuild_tlas(SceneBvh* bvh, const PtInstance* d_instances, cudaStream_t st, float* ms_out) {
+    const uint32_t NI = (uint32_t)bvh->valid_inst.size();
+    if (ms_out) *ms_out = 0.0f;
+    if (NI == 0) return PT_OK;
+    cudaEvent_t ev0, ev1;
+    PT_CUDA_CHECK(cudaEventCreate(&ev0)); PT_CUDA_CHECK(cudaEventCreate(&ev1));
+    Scratch s;
+    int rc = alloc_scratch(s, NI, 1, bvh->use_ploc, st);
+    s.capacity = NI + 8;
+    if (rc == PT_OK) {
+        cudaEventRecord(ev0, st);
+        rc = build_tlas(s, bvh, d_instances, st);
+        cudaEventRecord(ev1, st);
+        cudaStreamSynchronize(st);
+        if (rc == PT_OK && ms_out) cudaEventElapsedTime(ms_out, ev0, ev1);
+    }
+    bvh->refit_repairs += s.refit_repairs;
+    s.release();
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    return rc;
 }
 
 }  // namespace pt

@@ -25,6 +25,10 @@ struct SceneBvh {
     std::vector<uint32_t> tri_off;      // per mesh
     std::vector<uint32_t> tri_count;    // per mesh
     float* mesh_bounds = nullptr;       // device, 6 floats per mesh
+    // TLAS rebuild state (animated instances)
+    uint32_t tlas_node_base = 0;        // first BVH8 node of the TLAS (everything below belongs to BLASes)
+    std::vector<uint32_t> valid_inst;   // instances that reference a non-empty mesh
+    bool use_ploc = false;
     float ms_build = 0.0f;
     uint32_t refit_repairs = 0;         // nodes corrected by the refit verification (expected 0)
 
@@ -35,5 +39,8 @@ struct SceneBvh {
 int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::vector<PrimRec>& h_prims,
                     const std::vector<PtMesh>& meshes, const PtInstance* d_instances,
                     const std::vector<PtInstance>& h_instances, bool use_ploc, cudaStream_t stream, SceneBvh* out);
+
+// Rebuilds the top level in place after the transforms in d_instances changed (mesh indices unchanged).
+int rebuild_tlas(SceneBvh* bvh, const PtInstance* d_instances, cudaStream_t stream, float* ms_out);
 
 }  // namespace pt

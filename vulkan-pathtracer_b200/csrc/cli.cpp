@@ -24,6 +24,7 @@ struct Args {
     std::string scene_path;
     // additive (headless) options
     std::string output = "out.pfm";
+    std::string camera_path;
     uint32_t frames = 1;
     bool accumulate = false, quiet = false;
     float position[3] = {0.0f, 0.0f, 0.0f};
@@ -46,6 +47,9 @@ void usage(FILE* f) {
         "  -f, --frames <u32>                      frames to render, frame_count = 0..N-1 (default 1)\n"
         "      --accumulate                        write the mean over all frames instead of the last frame\n"
         "      --camera-position <x,y,z>  --yaw <deg>  --pitch <deg>   (defaults 0,0,0 / 0 / 0)\n"
+        "      --camera-path <file>                replay recorded input through Camera.update, one line per frame:\n"
+        "                                          <delta_time_s> <keys|-> <mouse_left 0|1> <cursor_dx> <cursor_dy>\n"
+        "                                          keys joined by '+': w s a d space left_ctrl left_shift\n"
         "      --device <ordinal>  --quiet\n",
         f);
 }
@@ -104,6 +108,7 @@ int parse(int argc, char** argv, Args& a) {
         else if (is("--scene-path", "-s")) a.scene_path = val;
         else if (is("--output", "-o")) a.output = val;
         else if (is("--frames", "-f")) ok = parse_u32(val, a.frames);
+        else if (is("--camera-path", nullptr)) a.camera_path = val;
         else if (is("--yaw", nullptr)) ok = parse_f32(val, a.yaw);
         else if (is("--pitch", nullptr)) ok = parse_f32(val, a.pitch);
         else if (is("--device", nullptr)) { uint32_t d = 0; ok = parse_u32(val, d); a.device = (int)d; }
@@ -112,6 +117,41 @@ int parse(int argc, char** argv, Args& a) {
         if (!ok) { std::fprintf(stderr, "b200pt: invalid value '%s' for %s\n", val, key.c_str()); return 2; }
     }
     return 0;
+}
+
+// recorded Input + Timer values for Camera.update (Camera.zig:48-79), one PtInput per frame
+bool read_camera_path(const std::string& path, std::vector<PtInput>& out) {
+    FILE* f = std::fopen(path.c_str(), "r");
+    if (!f) { std::fprintf(stderr, "b200pt: cannot open camera path %s\n", path.c_str()); return false; }
+    char line[512];
+    int lineno = 0;
+    while (std::fgets(line, sizeof(line), f)) {
+        ++lineno;
+        char* p = line;
+        while (*p == ' ' || *p == '\t') ++p;
+        if (*p == '#' || *p == '\n' || *p == '\r' || !*p) continue;
+        char keys[256];
+        PtInput in;
+        std::memset(&in, 0, sizeof(in));
+        unsigned mouse = 0;
+        if (std::sscanf(p, "%f %255s %u %d %d", &in.delta_time, keys, &mouse, &in.cursor_delta_x, &in.cursor_delta_y) != 5) {
+            std::fprintf(stderr, "b200pt: %s:%d: expected <dt> <keys|-> <mouse 0|1> <dx> <dy>\n", path.c_str(), lineno);
+            std::fclose(f); return false;
+        }
+        in.mouse_left = mouse ? 1u : 0u;
+        for (char* tok = std::strtok(keys, "+"); tok; tok = std::strtok(nullptr, "+")) {
+            static const struct { const char* name; uint32_t bit; } names[] = {
+                {"w", PT_KEY_W}, {"s", PT_KEY_S}, {"d", PT_KEY_D}, {"a", PT_KEY_A}, {"space", PT_KEY_SPACE},
+                {"left_ctrl", PT_KEY_LEFT_CTRL}, {"left_shift", PT_KEY_LEFT_SHIFT}};
+            if (!std::strcmp(tok, "-")) continue;
+            bool known = false;
+            for (const auto& n : names) if (!std::strcmp(tok, n.name)) { in.keys |= n.bit; known = true; }
+            if (!known) { std::fprintf(stderr, "b200pt: %s:%d: unknown key '%s'\n", path.c_str(), lineno, tok); std::fclose(f); return false; }
+        }
+        out.push_back(in);
+    }
+    std::fclose(f);
+    return true;
 }
 
 bool ends_with(const std::string& s, const char* suffix) {
@@ -139,6 +179,8 @@ int main(int argc, char** argv) {
         std::fputs("b200pt: resolution, divider and frames must be non-zero\n", stderr);
         return 2;
     }
+    std::vector<PtInput> path;
+    if (!a.camera_path.empty() && !read_camera_path(a.camera_path, path)) return 2;
     using clock = std::chrono::steady_clock;
     const auto t_load = clock::now();
     PtScene* scene = nullptr;
@@ -162,12 +204,21 @@ int main(int argc, char** argv) {
     if (a.accumulate) pt_set_accumulate(r, 1);
 
     const float aspect = (float)a.resolution_x / (float)a.resolution_y;           // main.zig:222
+    PtCameraState camera;
+    st = pt_camera_state_new(3.14159265358979323846f * 0.25f, aspect, a.position, &camera);   // main.zig:220-224
+    if (st != PT_OK) return die("Camera.new", st);
     uint64_t rays = 0;
     const auto t0 = clock::now();
     for (uint32_t frame = 0; frame < a.frames; ++frame) {                         // the present loop, main.zig:232-345
         PtCamera cam;
-        st = pt_camera_new(3.14159265358979323846f * 0.25f, aspect, a.position, a.yaw, a.pitch, frame, &cam);   // main.zig:220-224
-        if (st != PT_OK) return die("Camera.new", st);
+        if (!path.empty()) {
+            // camera.update(input, timer) at the top of the loop body (main.zig:242); the trace holds its last line
+            st = pt_camera_update(&camera, &path[frame < path.size() ? frame : path.size() - 1]);
+            if (st == PT_OK) st = pt_camera_pack(&camera, frame, &cam);
+        } else {
+            st = pt_camera_new(3.14159265358979323846f * 0.25f, aspect, a.position, a.yaw, a.pitch, frame, &cam);
+        }
+        if (st != PT_OK) return die("Camera.update", st);
         st = pt_render(r, &cam, nullptr);                                         // RaytracingPass.record, main.zig:263-270
         if (st != PT_OK) return die("RaytracingPass.record", st);
         if (!a.quiet) {

@@ -62,6 +62,95 @@ int pt_camera_new(float fov, float aspect_ratio, const float position[3], float 
     return PT_OK;
 }
 
+}  // extern "C"
+
+namespace {
+V v3(const float* p) { return V{p[0], p[1], p[2]}; }
+void put3(float* p, V v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
+
+// Camera.updateOrientation, Camera.zig:86-94
+void update_orientation(PtCameraState& c) {
+    const Q rotation = qmul(from_axis(c.yaw, V{0.0f, 1.0f, 0.0f}), from_axis(c.pitch, V{1.0f, 0.0f, 0.0f}));
+    c.rotation[0] = rotation.w; c.rotation[1] = rotation.x; c.rotation[2] = rotation.y; c.rotation[3] = rotation.z;
+    const V forward = rotate(rotation, V{0.0f, 0.0f, 1.0f}), left = rotate(rotation, V{-1.0f, 0.0f, 0.0f});
+    put3(c.forward, forward); put3(c.left, left); put3(c.up, cross(left, forward));
+}
+// Camera.updateVectors, Camera.zig:96-102
+void update_vectors(PtCameraState& c) {
+    const float viewport_height = 2.0f * std::tan(c.fov * 0.5f);
+    const float viewport_width = viewport_height * c.aspect_ratio;
+    put3(c.horizontal, scale(v3(c.left), viewport_width));
+    put3(c.vertical, scale(v3(c.up), viewport_height));
+}
+// zalgebra Vec3.norm (pinned 4a85a71, un-vendored): the zero vector is returned unchanged
+V norm(V v) {
+    const float l = std::sqrt(dot(v, v));
+    return l == 0.0f ? v : V{v.x / l, v.y / l, v.z / l};
+}
+}  // namespace
+
+extern "C" {
+
+int pt_camera_state_new(float fov, float aspect_ratio, const float position[3], PtCameraState* out) {
+    if (!position || !out) { pt::set_error("pt_camera_state_new: null argument"); return PT_ERR_INVALID_ARGUMENT; }
+    std::memset(out, 0, sizeof(*out));
+    out->fov = fov; out->aspect_ratio = aspect_ratio;
+    out->position[0] = position[0]; out->position[1] = position[1]; out->position[2] = position[2];
+    out->pitch = 0.0f; out->yaw = 0.0f;                    // Camera.zig:32-34
+    update_orientation(*out); update_vectors(*out);        // :42-43
+    return PT_OK;
+}
+
+int pt_camera_update(PtCameraState* c, const PtInput* in) {
+    if (!c || !in) { pt::set_error("pt_camera_update: null argument"); return PT_ERR_INVALID_ARGUMENT; }
+    if (in->mouse_left) {                                                          // Camera.zig:49
+        const float rotate_speed = 0.25f;
+        if (in->cursor_delta_x != 0 || in->cursor_delta_y != 0) {                  // :51
+            c->yaw -= (float)in->cursor_delta_x * rotate_speed;                   // :54
+            c->pitch += (float)in->cursor_delta_y * rotate_speed;                 // :55
+            if (c->yaw < 0.0f) c->yaw += 360.0f;                                   // :57
+            if (c->yaw >= 360.0f) c->yaw -= 360.0f;                                // :58
+            c->pitch = std::fmin(std::fmax(c->pitch, -90.0f), 90.0f);              // :60
+            update_orientation(*c); update_vectors(*c);                            // :62-63
+        }
+    }
+    const float move_speed = (in->keys & PT_KEY_LEFT_SHIFT) ? 10.0f : 5.0f;        // :67
+    V dir{0.0f, 0.0f, 0.0f};
+    const V fwd = v3(c->forward), left = v3(c->left);
+    if (in->keys & PT_KEY_W) dir = add(dir, fwd);                                   // :69
+    if (in->keys & PT_KEY_S) dir = add(dir, scale(fwd, -1.0f));                     // :70  (sub)
+    if (in->keys & PT_KEY_D) dir = add(dir, left);                                  // :71
+    if (in->keys & PT_KEY_A) dir = add(dir, scale(left, -1.0f));                    // :72
+    const float step = move_speed * in->delta_time;
+    const V velocity = scale(norm(dir), step);                                      // :74
+    c->position[0] += velocity.x; c->position[1] += velocity.y; c->position[2] += velocity.z;   // :75
+    if (in->keys & PT_KEY_SPACE) c->position[1] += step;                            // :77
+    if (in->keys & PT_KEY_LEFT_CTRL) c->position[1] -= step;                        // :78
+    return PT_OK;
+}
+
+int pt_camera_update_aspect_ratio(PtCameraState* c, float aspect_ratio) {
+    if (!c) { pt::set_error("pt_camera_update_aspect_ratio: null argument"); return PT_ERR_INVALID_ARGUMENT; }
+    c->aspect_ratio = aspect_ratio;
+    update_vectors(*c);
+    return PT_OK;
+}
+
+int pt_camera_pack(const PtCameraState* c, uint32_t frame_count, PtCamera* out) {
+    if (!c || !out) { pt::set_error("pt_camera_pack: null argument"); return PT_ERR_INVALID_ARGUMENT; }
+    for (int k = 0; k < 3; ++k) {
+        out->position[k] = c->position[k]; out->horizontal[k] = c->horizontal[k];
+        out->vertical[k] = c->vertical[k]; out->forward[k] = c->forward[k];
+    }
+    out->position[3] = 1.0f; out->horizontal[3] = 0.0f; out->vertical[3] = 0.0f; out->forward[3] = 0.0f;
+    out->frame_count = frame_count;
+    return PT_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
 // PFM (Portable FloatMap): "PF", bottom row first, little endian; RGB only.
 int pt_write_pfm(const char* path, const float* rgba, uint32_t width, uint32_t height) {
     if (!path || !rgba) { pt::set_error("pt_write_pfm: null argument"); return PT_ERR_INVALID_ARGUMENT; }
