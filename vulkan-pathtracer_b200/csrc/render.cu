@@ -69,13 +69,11 @@ __global__ void __launch_bounds__(256) k_raygen(PixelMap pm, PathBuffers pb, Fra
             fp.id_inst[pi] = kInvalidId; fp.id_prim[pi] = kInvalidId; fp.id_tri[pi] = kInvalidId;
             live = false;
         } else {
-            const U2 seed = prng_seed(x, y, fp.cam.frame_count);            // :41
+            // the path state (seed :41, final :43, color :45, attenuation :46) is initialised by K-shade of
+            // iteration 0, which saves 48 B written here and 48 B read there per pixel
             const V3 d = primary_direction(fp.cam, x, y, pm.width, pm.height);
             store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]), d,
                       0.001f, 10000.0f);                                                                         // :38-39,47-48
-            pb.atten_sx[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(seed.x));                          // :46
-            pb.color_sy[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(seed.y));                          // :45
-            pb.final_sb[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0u));                              // :43
         }
     }
     queue_push(pb.queue[0], pb.qcount + 0, live, slot);
@@ -238,10 +236,17 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
             slot = qin[idx];
             uint32_t x, y;
             slot_to_pixel(pm, slot, x, y);
-            const float4 a4 = pb.atten_sx[slot], c4 = pb.color_sy[slot], f4 = pb.final_sb[slot];
-            V3 atten = v3(a4.x, a4.y, a4.z), color = v3(c4.x, c4.y, c4.z), final_color = v3(f4.x, f4.y, f4.z);
-            U2 seed; seed.x = __float_as_uint(a4.w); seed.y = __float_as_uint(c4.w);
-            uint32_t s = __float_as_uint(f4.w) & 0xffffu, j = __float_as_uint(f4.w) >> 16;
+            V3 atten = v3s(1.0f), color = v3s(0.0f), final_color = v3s(0.0f);            // :46, :45, :43
+            U2 seed;
+            uint32_t s = 0u, j = 0u;
+            if (iter == 0u) {
+                seed = prng_seed(x, y, fp.cam.frame_count);                                  // :41
+            } else {
+                const float4 a4 = pb.atten_sx[slot], c4 = pb.color_sy[slot], f4 = pb.final_sb[slot];
+                atten = v3(a4.x, a4.y, a4.z); color = v3(c4.x, c4.y, c4.z); final_color = v3(f4.x, f4.y, f4.z);
+                seed.x = __float_as_uint(a4.w); seed.y = __float_as_uint(c4.w);
+                s = __float_as_uint(f4.w) & 0xffffu; j = __float_as_uint(f4.w) >> 16;
+            }
             const float4 ro = pb.ray_o[slot], rd = pb.ray_d[slot];
             V3 origin = v3(ro.x, ro.y, ro.z), direction = v3(rd.x, rd.y, rd.z);
             HitRec h;
@@ -252,8 +257,10 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
             }
             if (s == 0u && j == 0u) {
                 // first segment of the pixel: this is the primary hit
-                pb.prim_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.instance));
-                pb.prim_b[slot] = make_uint2(h.primitive_index, h.triangle_index);
+                if (S > 1u) {   // cached for the later samples of this pixel (quirk Q1)
+                    pb.prim_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.instance));
+                    pb.prim_b[slot] = make_uint2(h.primitive_index, h.triangle_index);
+                }
                 const size_t pi = (size_t)y * pm.width + x;
                 fp.id_inst[pi] = h.instance; fp.id_prim[pi] = h.primitive_index; fp.id_tri[pi] = h.triangle_index;
             }
@@ -263,32 +270,32 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                     const float t = 0.5f * (direction.y + 1.0f);
                     color = color + atten * mix(v3(1.0f, 1.0f, 1.0f), v3(0.5f, 0.7f, 1.0f), t);
                     end_sample = true;
+                } else if (j + 1u >= B) {
+                    // last segment: loop bound reached (:49,:77); only the emission of this hit is consumed (:75)
+                    color = color + get_emissive(sc, h) * 10.0f * atten;
+                    end_sample = true;
                 } else {
                     const TriangleData td = get_triangle_data(sc, h);                       // :72
                     const MaterialData md = get_material_data(sc, td);                      // :73
                     color = color + md.emissive * 10.0f * atten;                            // :75
-                    if (j + 1u < B) {                                                       // :77
-                        ShadingInfo si;
-                        si.out_dir = -direction;                                            // :79
-                        si.normal = md.normal;                                              // :80
-                        si.lambert_out = dot(si.normal, si.out_dir);                        // :81
-                        const V3 alb = v3(md.albedo.x, md.albedo.y, md.albedo.z);
-                        si.fresnel_0 = mix(v3s(0.02f), alb, md.metallic);                   // :82
-                        si.diffuse_albedo = alb - md.metallic * alb;                        // :83
-                        si.roughness = gmax(0.006f, md.roughness);                          // :84
-                        origin = origin + h.t * direction + td.geometry_normal * 0.00001f;  // :86
-                        direction = sample_brdf(si, pcg2d(seed));                           // :87
-                        const float density = get_brdf_density(si, direction);              // :89
-                        const float lambert_in = dot(si.normal, direction);                 // :90
-                        if (lambert_in <= 0.0f) {                                           // :91-93
-                            end_sample = true;
-                        } else {
-                            atten = atten * (brdf(si, direction) * lambert_in / density);   // :95
-                            ++j;
-                            emit = true;
-                        }
+                    ShadingInfo si;
+                    si.out_dir = -direction;                                                // :79
+                    si.normal = md.normal;                                                  // :80
+                    si.lambert_out = dot(si.normal, si.out_dir);                            // :81
+                    const V3 alb = v3(md.albedo.x, md.albedo.y, md.albedo.z);
+                    si.fresnel_0 = mix(v3s(0.02f), alb, md.metallic);                       // :82
+                    si.diffuse_albedo = alb - md.metallic * alb;                            // :83
+                    si.roughness = gmax(0.006f, md.roughness);                              // :84
+                    origin = origin + h.t * direction + td.geometry_normal * 0.00001f;      // :86
+                    direction = sample_brdf(si, pcg2d(seed));                               // :87
+                    const float density = get_brdf_density(si, direction);                  // :89
+                    const float lambert_in = dot(si.normal, direction);                     // :90
+                    if (lambert_in <= 0.0f) {                                               // :91-93
+                        end_sample = true;
                     } else {
-                        end_sample = true;   // last segment: loop bound reached (:49)
+                        atten = atten * (brdf(si, direction) * lambert_in / density);       // :95
+                        ++j;
+                        emit = true;
                     }
                 }
                 if (!end_sample) break;      // next segment must be traced

@@ -363,4 +363,35 @@ PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& t
     return md;
 }
 
+// The last segment of a sample (ray_gen.rgen:75-77 with b == NUM_BOUNCES - 1) only adds the hit's emission:
+// of getTriangleData / getMaterialData nothing but `emissive` is consumed, so only the emissive factor and --
+// when the material has an emissive map -- the interpolated uv and that map's four texels are fetched.
+// Same expressions as above for everything that is computed, hence the same bits.
+PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h) {
+    const PrimRec p = sc.prims[h.primitive_index];
+    const MatRec* mp = sc.materials + (p.info & PT_MATERIAL_INDEX_MASK);
+    const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));
+    const V4 e = unpack_unorm4x8(fac.z);                                                 // material.glsl:50
+    V3 emissive = v3(e.x, e.y, e.z);
+    if ((fac.w >> 2) & 1u) {                                                             // :51-53
+        const V3 c = v3(1.0f - h.b1 - h.b2, h.b1, h.b2);
+        uint32_t id[3];
+        tri_indices(sc, p, h.triangle_index, id);
+        const uint8_t* base = sc.triangle_data;
+        const float u0 = ldf(base, p.uvs_offset + 8u * id[0]), v0 = ldf(base, p.uvs_offset + 8u * id[0] + 4);
+        const float u1 = ldf(base, p.uvs_offset + 8u * id[1]), v1 = ldf(base, p.uvs_offset + 8u * id[1] + 4);
+        const float u2 = ldf(base, p.uvs_offset + 8u * id[2]), v2 = ldf(base, p.uvs_offset + 8u * id[2] + 4);
+        V2 uv;
+        uv.x = u0 * c.x + u1 * c.y + u2 * c.z;
+        uv.y = v0 * c.x + v1 * c.y + v2 * c.z;
+        const uint4 w = __ldg(reinterpret_cast<const uint4*>(mp) + 3);                   // TexRec of the emissive map
+        TexRec tex;
+        tex.texels = reinterpret_cast<const uint32_t*>(((uint64_t)w.y << 32) | w.x);
+        tex.width = w.z; tex.height = w.w;
+        const V4 t = sample_texture(tex, uv);
+        emissive = emissive * v3(t.x, t.y, t.z);
+    }
+    return emissive;
+}
+
 }  // namespace pt
