@@ -318,6 +318,10 @@ int pt_debug_rng(int device, size_t n, const uint32_t* pixel_xy_frame3, uint32_t
 int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t height, size_t n, const float* uv2,
                      float* rgba4);
 
+/* Digest of the device acceleration structures (determinism probes): [0] Morton-ordered triangles, [1] binary
+ * topology, [2] binary boxes, [3] BVH8 node count, [4] order-independent hash of the BVH8 nodes, [5] BLAS roots. */
+int pt_debug_bvh_digest(PtRenderer* r, uint64_t digest[6]);
+
 /* Animated instances: replace all instance transforms (num_instances x 16 floats, the
  * rows of M as in PtInstance.transform; mesh indices unchanged) and rebuild the top-level structure on the
  * device -- Tlas.init (Tlas.zig:15-182) run again.  Synchronises with frames in flight; *ms_rebuild (may be

@@ -463,3 +463,32 @@ def test_cli_replays_a_camera_path(tmp_path):
     assert bits_equal(got, want).all()
     assert cam.state.position[2] > 0.7 and cam.state.yaw != 0.0   # the path did move the camera
     ren.deinit()
+
+
+def test_single_instance_scene_skips_the_top_level_only_when_identity():
+    """One identity instance starts traversal at its BLAS root (DeviceScene::start_root); a moved one does not."""
+    import copy
+    import ctypes as C
+    ps = S.random_soup(33, 2500, 1, 1).pack()                    # one instance, translated: general path
+    W, H, spp, seg = 160, 90, 2, 3
+    cam = S.camera_default(W, H, 1, position=(0.0, 0.0, -6.0))
+    eye = np.eye(4, dtype=np.float32).reshape(1, 16)
+    ps_id = copy.copy(ps)
+    ps_id.instances = (S.PtInstance * 1)()
+    ps_id.instances[0].mesh_index = ps.instances[0].mesh_index
+    ps_id.instances[0].transform = (C.c_float * 16)(*eye[0].tolist())
+    T0 = np.array([list(ps.instances[0].transform)], np.float32)
+    rays = random_rays(3, 100_000, 6.0, b200pt.PtRay_dtype)
+    r = b200pt.Renderer(ps, W, H, spp, seg)
+    for scene, T in ((ps, None), (ps_id, eye), (ps, T0)):
+        if T is not None:
+            r.set_instance_transforms(T)
+        osc = orc.OracleScene(scene, True)
+        r.record(cam); r.sync()
+        oimg, oids, _ = osc.render(S.render_config(W, H, spp, seg), cam, True)
+        assert bits_equal(r.image(), oimg).all() and all((a == b).all() for a, b in zip(r.ids(), oids))
+        assert not hits_mismatch(r.trace(rays), osc.trace(rays)).any()
+    r.deinit()
+    fresh_img, fresh_ids, _ = render(ps_id, W, H, spp, seg, 1)   # created as identity from the start (camera at 0)
+    oimg, oids, _ = orc.OracleScene(ps_id, True).render(S.render_config(W, H, spp, seg), S.camera_default(W, H, 1), True)
+    assert bits_equal(fresh_img, oimg).all() and all((a == b).all() for a, b in zip(fresh_ids, oids))

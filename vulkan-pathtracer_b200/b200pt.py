@@ -111,6 +111,7 @@ def lib():
         L.pt_camera_update.argtypes = [C.POINTER(PtCameraState), C.POINTER(PtInput)]
         L.pt_camera_update_aspect_ratio.argtypes = [C.POINTER(PtCameraState), C.c_float]
         L.pt_camera_pack.argtypes = [C.POINTER(PtCameraState), C.c_uint32, C.POINTER(PtCamera)]
+        L.pt_debug_bvh_digest.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 6)]
         L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
         L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_write_exr.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
@@ -272,6 +273,11 @@ class Renderer:
         ms = C.c_float(0.0)
         check(lib().pt_set_instance_transforms(self.handle, t.ctypes.data, t.shape[0], C.byref(ms)))
         return ms.value
+
+    def bvh_digest(self):
+        d = (C.c_uint64 * 6)()
+        check(lib().pt_debug_bvh_digest(self.handle, C.byref(d)))
+        return tuple(d)
 
     def set_profiling(self, on):
         check(lib().pt_set_profiling(self.handle, 1 if on else 0))

@@ -124,9 +124,11 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
     const size_t px = (size_t)pm.width * pm.height;
     A(r->d_image, px * 4); A(r->d_ids, px * 3);
 #undef A
-    PT_CUDA_CHECK(cudaMemset(r->d_image, 0, std::max<size_t>(px, 1) * 16));
-    PT_CUDA_CHECK(cudaMemset(r->d_ids, 0xff, std::max<size_t>(px, 1) * 12));
-    PT_CUDA_CHECK(cudaMemset(b.trav_counters, 0, 16));
+    // on the renderer's stream: it is non-blocking, so work on the legacy default stream is not ordered with it
+    PT_CUDA_CHECK(cudaMemsetAsync(r->d_image, 0, std::max<size_t>(px, 1) * 16, r->stream));
+    PT_CUDA_CHECK(cudaMemsetAsync(r->d_ids, 0xff, std::max<size_t>(px, 1) * 12, r->stream));
+    PT_CUDA_CHECK(cudaMemsetAsync(b.trav_counters, 0, 16, r->stream));
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
     r->accum_frames = 0;
     return PT_OK;
 }
@@ -151,7 +153,18 @@ static int upload_instance_records(PtRenderer* r) {
         ir.bvh2_root = r->bvh.tri_off[m];
         ir.bvh2_tri_base = r->bvh.tri_off[m];
     }
-    if (!recs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances, recs.data(), recs.size() * sizeof(InstanceRec), cudaMemcpyHostToDevice));
+    // Uploads go through the renderer's stream.  A plain cudaMemcpy from pageable memory returns once the data
+    // is staged, while the DMA itself runs on the legacy default stream -- which a non-blocking stream does
+    // not wait for, so a kernel on r->stream could read the buffer before the copy has landed (seen twice in
+    // this round as a BVH built from partly stale triangle data; profiles/r1_experiments.md).
+    if (!recs.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_instances, recs.data(), recs.size() * sizeof(InstanceRec), cudaMemcpyHostToDevice, r->stream));
+    PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    // traversal start (DeviceScene::start_root): skip the top level for a single identity instance
+    r->scene.start_root = r->bvh.tlas_root8; r->scene.start_inst = kInvalidId;
+    if (r->bvh.valid_inst.size() == 1) {
+        const uint32_t i = r->bvh.valid_inst[0];
+        if (recs[i].mesh & kInstIdentity) { r->scene.start_root = recs[i].blas_root; r->scene.start_inst = i; }
+    }
     return PT_OK;
 }
 
@@ -159,7 +172,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     int rc;
     if (s->triangle_data_len > 0xFFFFFFF0ull) { set_error("triangle_data larger than 4 GiB is not supported"); return PT_ERR_INVALID_ARGUMENT; }
     if ((rc = dev_alloc(&r->d_blob, s->triangle_data_len + 16)) != PT_OK) return rc;
-    if (s->triangle_data_len) PT_CUDA_CHECK(cudaMemcpy(r->d_blob, s->triangle_data, s->triangle_data_len, cudaMemcpyHostToDevice));
+    if (s->triangle_data_len) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_blob, s->triangle_data, s->triangle_data_len, cudaMemcpyHostToDevice, r->stream));
     // primitives: validate every offset against the blob (the reference trusts the file; we must not fault)
     std::vector<PrimRec> prims(s->num_primitives);
     for (size_t i = 0; i < s->num_primitives; ++i) {
@@ -183,7 +196,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
         r->num_triangles += p.triangle_count;
     }
     if ((rc = dev_alloc(&r->d_prims, prims.size())) != PT_OK) return rc;
-    if (!prims.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_prims, prims.data(), prims.size() * sizeof(PrimRec), cudaMemcpyHostToDevice));
+    if (!prims.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_prims, prims.data(), prims.size() * sizeof(PrimRec), cudaMemcpyHostToDevice, r->stream));
     // materials + textures (r8g8b8a8_unorm, single mip; RaytracingPass.zig:490-518)
     for (size_t i = 0; i < s->num_materials; ++i) {
         const uint32_t t[4] = {s->materials[i].albedo_texture_index, s->materials[i].metal_roughness_texture_index,
@@ -198,11 +211,11 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
         if (t.width == 0 || t.height == 0 || !t.rgba) { set_error("texture " + std::to_string(i) + ": empty"); return PT_ERR_INVALID_ARGUMENT; }
         const size_t n = (size_t)t.width * t.height;
         if ((rc = dev_alloc(&r->d_texels[i], n)) != PT_OK) return rc;
-        PT_CUDA_CHECK(cudaMemcpy(r->d_texels[i], t.rgba, n * 4, cudaMemcpyHostToDevice));
+        PT_CUDA_CHECK(cudaMemcpyAsync(r->d_texels[i], t.rgba, n * 4, cudaMemcpyHostToDevice, r->stream));
         texs[i] = TexRec{r->d_texels[i], t.width, t.height};
     }
     if ((rc = dev_alloc(&r->d_textures, texs.size())) != PT_OK) return rc;
-    if (!texs.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_textures, texs.data(), texs.size() * sizeof(TexRec), cudaMemcpyHostToDevice));
+    if (!texs.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_textures, texs.data(), texs.size() * sizeof(TexRec), cudaMemcpyHostToDevice, r->stream));
     std::vector<MatRec> mats(s->num_materials);
     std::map<std::array<uint32_t, 4>, uint4*> atlas_of;
     for (size_t i = 0; i < s->num_materials; ++i) {
@@ -235,7 +248,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     }
     PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
     if ((rc = dev_alloc(&r->d_materials, mats.size())) != PT_OK) return rc;
-    if (!mats.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_materials, mats.data(), mats.size() * sizeof(MatRec), cudaMemcpyHostToDevice));
+    if (!mats.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_materials, mats.data(), mats.size() * sizeof(MatRec), cudaMemcpyHostToDevice, r->stream));
     // meshes / instances
     std::vector<PtMesh> meshes(s->meshes, s->meshes + s->num_meshes);
     for (size_t m = 0; m < meshes.size(); ++m)
@@ -244,7 +257,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     for (size_t i = 0; i < inst.size(); ++i)
         if (inst[i].mesh_index >= meshes.size()) { set_error("instance " + std::to_string(i) + ": mesh index out of range"); return PT_ERR_INVALID_ARGUMENT; }
     if ((rc = dev_alloc(&r->d_instances_raw, inst.size())) != PT_OK) return rc;
-    if (!inst.empty()) PT_CUDA_CHECK(cudaMemcpy(r->d_instances_raw, inst.data(), inst.size() * sizeof(PtInstance), cudaMemcpyHostToDevice));
+    if (!inst.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_instances_raw, inst.data(), inst.size() * sizeof(PtInstance), cudaMemcpyHostToDevice, r->stream));
     // acceleration structures (createBlases + Tlas.init)
     if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, (r->cfg.flags & PT_FLAG_BVH_PLOC) != 0, r->stream, &r->bvh)) != PT_OK) return rc;
     r->h_instances = inst;
@@ -654,6 +667,53 @@ int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t*
     return PT_OK;
 }
 
+// Digest of the acceleration structures, for determinism probes (tools/gpu_determinism.py):
+//   [0] Morton-ordered triangles of every mesh   [1] BVH2 topology (left/right)   [2] BVH2 boxes
+//   [3] number of BVH8 nodes   [4] BVH8 nodes as an order-independent sum of per-node hashes of the geometry
+//   fields (frame, exponents, quantised planes, metas' top bits)   [5] per-mesh BVH8 roots
+int pt_debug_bvh_digest(PtRenderer* r, uint64_t digest[6]) {
+    PT_REQUIRE(r && digest, "pt_debug_bvh_digest: null argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
+    { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
+    auto fnv = [](uint64_t h, const void* p, size_t n) { const uint8_t* b = static_cast<const uint8_t*>(p); for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; } return h; };
+    const uint64_t seed = 1469598103934665603ull;
+    for (int k = 0; k < 6; ++k) digest[k] = seed;
+    const SceneBvh& b = r->bvh;
+    std::vector<Bvh8Tri> tris(std::max<uint32_t>(b.num_tris, 1));
+    std::vector<Bvh2Node> n2(std::max<uint32_t>(b.num_tris, 1));
+    if (b.num_tris) {
+        PT_CUDA_CHECK(cudaMemcpy(tris.data(), b.tris2, sizeof(Bvh8Tri) * b.num_tris, cudaMemcpyDeviceToHost));
+        PT_CUDA_CHECK(cudaMemcpy(n2.data(), b.nodes2, sizeof(Bvh2Node) * b.num_tris, cudaMemcpyDeviceToHost));
+    }
+    for (size_t m = 0; m < b.tri_count.size(); ++m) {
+        const uint32_t n = b.tri_count[m], off = b.tri_off[m];
+        for (uint32_t i = 0; i < n; ++i) {
+            digest[0] = fnv(digest[0], &tris[off + i].v0, 12); digest[0] = fnv(digest[0], &tris[off + i].v1, 12); digest[0] = fnv(digest[0], &tris[off + i].v2, 12);
+            digest[0] = fnv(digest[0], &tris[off + i].v0.w, 4); digest[0] = fnv(digest[0], &tris[off + i].v1.w, 4);
+        }
+        for (uint32_t i = 0; i + 1 < std::max(n, 2u) && n > 0; ++i) {
+            const Bvh2Node& q = n2[off + i];
+            digest[1] = fnv(digest[1], &q.left, 4); digest[1] = fnv(digest[1], &q.right, 4);
+            digest[2] = fnv(digest[2], q.lo, 12); digest[2] = fnv(digest[2], q.hi, 12);
+        }
+    }
+    digest[3] = b.num_nodes8;
+    std::vector<Bvh8Node> n8(std::max<uint32_t>(b.num_nodes8, 1));
+    if (b.num_nodes8) PT_CUDA_CHECK(cudaMemcpy(n8.data(), b.nodes8, sizeof(Bvh8Node) * b.num_nodes8, cudaMemcpyDeviceToHost));
+    uint64_t sum = 0;
+    for (uint32_t i = 0; i < b.num_nodes8; ++i) {
+        uint64_t h = fnv(seed, &n8[i], 16);                 // frame + exponents + imask
+        uint8_t kinds[8];
+        for (int k = 0; k < 8; ++k) kinds[k] = n8[i].meta[k] >> 5;
+        h = fnv(h, kinds, 8);
+        h = fnv(h, n8[i].qlo_x, 48);
+        sum += h;
+    }
+    digest[4] = sum;
+    digest[5] = fnv(seed, b.blas_root8.data(), b.blas_root8.size() * 4);
+    return PT_OK;
+}
+
 // Animated instances.  The reference fixes the transforms at Tlas.init (Tlas.zig:32-52);
 // this is "Tlas.init again" with new matrices: instance records re-derived, top level rebuilt in place.
 int pt_set_instance_transforms(PtRenderer* r, const float* transforms, size_t num_instances, float* ms_rebuild) {
@@ -662,12 +722,11 @@ int pt_set_instance_transforms(PtRenderer* r, const float* transforms, size_t nu
     PT_CUDA_CHECK(cudaSetDevice(r->device));
     { int rc = pt_sync(r); if (rc != PT_OK) return rc; }       // frames in flight still read the old top level
     for (size_t i = 0; i < num_instances; ++i) std::memcpy(r->h_instances[i].transform, transforms + 16 * i, sizeof(float) * 16);
-    if (num_instances) PT_CUDA_CHECK(cudaMemcpy(r->d_instances_raw, r->h_instances.data(), num_instances * sizeof(PtInstance), cudaMemcpyHostToDevice));
-    int rc = upload_instance_records(r);
-    if (rc != PT_OK) return rc;
-    rc = rebuild_tlas(&r->bvh, r->d_instances_raw, r->stream, ms_rebuild);
+    if (num_instances) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_instances_raw, r->h_instances.data(), num_instances * sizeof(PtInstance), cudaMemcpyHostToDevice, r->stream));
+    int rc = rebuild_tlas(&r->bvh, r->d_instances_raw, r->stream, ms_rebuild);
     if (rc != PT_OK) return rc;
     r->scene.tlas_root = r->bvh.tlas_root8;
+    if ((rc = upload_instance_records(r)) != PT_OK) return rc;
     r->accum_frames = 0;
     return PT_OK;
 }

@@ -105,6 +105,10 @@ struct DeviceScene {
     const Bvh8Tri* tris2;        // triangles in Morton order per mesh (BVH2 leaves)
     const Bvh2Node* tlas2;       // BVH2 over instances
     uint32_t tlas_root;          // BVH8 node index of the TLAS root
+    // where a ray starts: (tlas_root, kInvalidId) in general; when the scene is one instance whose transform
+    // is exactly the identity the top level would be one node test with one child for every ray, so traversal
+    // starts at that instance's BLAS root with the instance already entered
+    uint32_t start_root, start_inst;
     uint32_t num_instances, num_prims, num_materials, num_textures;
 };
 

@@ -203,13 +203,13 @@ PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, 
     frame_set(world, o, d);
     f = world;
     RayPre rp = ray_precompute(d);   // only used inside a BLAS; recomputed on entry
-    uint32_t cur_inst = kInvalidId;
+    uint32_t cur_inst = sc.start_inst;
     constexpr int kStack = 64;
     uint2 stack[kStack];
     int sp = 0;
 #define PT_PUSH(v) do { if (sp < kStack) stack[sp++] = (v); } while (0)
     const uint2 kSentinel = make_uint2(0xFFFFFFFFu, 0u);
-    uint2 G = make_uint2(sc.tlas_root, 0x80000000u);   // node group: (base, hits<<24 | imask)
+    uint2 G = make_uint2(sc.start_root, 0x80000000u);  // node group: (base, hits<<24 | imask)
     uint2 T = make_uint2(0u, 0u);                      // leaf group: (base, item mask)
     for (;;) {
         if (G.y & 0xFF000000u) {

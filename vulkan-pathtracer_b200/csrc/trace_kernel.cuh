@@ -186,10 +186,10 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                         const uint32_t qi = w_next + rank;
                         slot = io.queue ? io.queue[qi] : qi;
                         load_ray(io, slot, f, rp, tmin, tmax);
-                        cur_inst = kInvalidId;
+                        cur_inst = sc.start_inst;
                         hit_init(best);
                         sp = 0;
-                        G = make_uint2(sc.tlas_root, 0x80000000u);
+                        G = make_uint2(sc.start_root, 0x80000000u);
                         T = make_uint2(0u, 0u);
                         active = true;
                     }
