@@ -34,7 +34,10 @@ def main():
     elif what == "one":
         r = b200pt.Renderer(ps, W, H, spp, seg)
         tr, sh, ot, rays = measure(r, W, H)
-        print(f"trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays")
+        st = r.stats()
+        nn, nt, nr = r.count_traversal()
+        print(f"trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays   "
+              f"bvh8 nodes {st.bvh_nodes}  per ray: {nn/max(nr,1):.2f} nodes {nt/max(nr,1):.2f} tris  build {st.ms_build:.2f} ms")
         r.deinit()
     elif what == "modes":
         for flags, label in ((0, "persistent"), (8, "walker"), (2, "bvh2")):

@@ -367,6 +367,8 @@ struct CollapseArgs {
     const float* leaf_lo;       // source leaf boxes
     const float* leaf_hi;
     uint32_t max_leaf;          // 3 for a BLAS (triangles per leaf slot), 1 for the TLAS
+    uint32_t pack_below;        // subtrees with at most this many leaves become ONE leaf-only node (0 = off; needs
+                                // contiguous leaf ranges, i.e. the Morton radix tree)
     // outputs
     Bvh8Node* nodes8;           // global node array
     uint4* node_bits8;          // 2 per node
@@ -384,11 +386,12 @@ struct CollapseArgs {
     uint32_t* overflow;
 };
 
-struct CChild { uint32_t ref, count; float lo[3], hi[3]; };
+struct CChild { uint32_t ref, count; float lo[3], hi[3]; uint32_t first; };   // first: sorted index of a packed run, else ~0
 
 __device__ __forceinline__ CChild load_child(const CollapseArgs& a, uint32_t ref) {
     CChild c;
     c.ref = ref;
+    c.first = 0xFFFFFFFFu;
     if (ref & 0x80000000u) {
         uint32_t j = ref & 0x7fffffffu;
         size_t src = a.order[j];
@@ -432,6 +435,29 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
         const uint32_t l = n.left, r = n.right;
         ch[best] = load_child(a, l);
         ch[cnt++] = load_child(a, r);
+    }
+    // Bottom of the tree: when the greedy expansion ran out of slots although the whole subtree would fit into
+    // one node (<= 8 slots of <= max_leaf leaves), the leftover inner children would become tiny nodes with two
+    // or three slots each -- a full node test per ray for very little culling.  Pack the subtree instead: its
+    // leaves are a contiguous run of the Morton order, cut into consecutive groups of max_leaf.
+    if (a.pack_below) {
+        bool leftover = false;
+        for (int c = 0; c < cnt; ++c) leftover = leftover || (!(ch[c].ref & 0x80000000u) && ch[c].count > a.max_leaf);
+        const uint2 rg = a.range[b2];
+        const uint32_t total = rg.y - rg.x + 1u;
+        if (leftover && total <= a.pack_below) {
+            cnt = 0;
+            for (uint32_t j0 = rg.x; j0 <= rg.y; j0 += a.max_leaf) {
+                CChild c;
+                c.first = j0; c.count = min(a.max_leaf, rg.y - j0 + 1u); c.ref = 0x80000000u | j0;
+                for (int k = 0; k < 3; ++k) { c.lo[k] = 3.0e38f; c.hi[k] = -3.0e38f; }
+                for (uint32_t t = 0; t < c.count; ++t) {
+                    const size_t src = a.order[j0 + t];
+                    for (int k = 0; k < 3; ++k) { c.lo[k] = fminf(c.lo[k], a.leaf_lo[3 * src + k]); c.hi[k] = fmaxf(c.hi[k], a.leaf_hi[3 * src + k]); }
+                }
+                ch[cnt++] = c;
+            }
+        }
     }
     // node frame
     float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
@@ -524,7 +550,13 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
             cbits[s] = unary << leaf_off;
             // the (at most max_leaf) leaves under this child, left to right; any binary topology
             uint32_t st[4]; int sp = 0; uint32_t t = 0;
-            st[sp++] = ch[c].ref;
+            if (ch[c].first != 0xFFFFFFFFu) {
+                for (; t < k; ++t) {      // packed run of the Morton order
+                    const uint32_t j = ch[c].first + t;
+                    if (a.tris8) a.tris8[tri_base + leaf_off + t] = a.tris_sorted[j];
+                    else a.leaf_out[tri_base + leaf_off + t] = a.leaf_ids[a.order[j]];
+                }
+            } else st[sp++] = ch[c].ref;
             while (sp) {
                 const uint32_t ref = st[--sp];
                 if (ref & 0x80000000u) {
@@ -574,6 +606,9 @@ struct Scratch {
     float *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
     bool lbvh = false;
     uint32_t capacity = 0;        // entries of wq2 / wq8
+    uint32_t pack_below = 0;      // CollapseArgs::pack_below for BLASes (measured slower on C2 / C4: off)
+    uint32_t max_leaf = 2;        // triangles per BLAS leaf slot (format limit 3; measured 1 / 2 / 3 on C2: 1.438 / 1.406 /
+                                  // 1.429 ms, on C4: 19.4 / 19.5 / 20.3 ms -- a triangle test costs ~0.7 node tests here)
     uint32_t refit_repairs = 0;   // nodes the verification pass had to correct (expected 0)
     void release() {
         cudaFree(cid[0]); cudaFree(cid[1]); cudaFree(nn); cudaFree(keep); cudaFree(pos);
@@ -686,6 +721,10 @@ int alloc_scratch(Scratch& s, uint32_t L, size_t max_prims, bool use_ploc, cudaS
     {
         const char* e = std::getenv("PT_BVH_PLOC");     // A/B switch for tools/; the API switch is PT_FLAG_BVH_PLOC
         s.lbvh = !(use_ploc || (e && e[0] == '1'));
+        const char* pk = std::getenv("PT_BVH_PACK");    // A/B switch for tools/
+        if (pk) s.pack_below = (uint32_t)std::atoi(pk);
+        const char* ml = std::getenv("PT_BVH_MAXLEAF");
+        if (ml) s.max_leaf = (uint32_t)std::max(1, std::min(3, std::atoi(ml)));
     }
     if (!s.lbvh) {
         for (int k = 0; k < 2; ++k) {
@@ -804,7 +843,7 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
         k_reorder_tris<<<blocks_for(n), kThreads, 0, st>>>(s.tmp_tris, s.vals_out, n, out->tris2 + out->tri_off[m]);
         CollapseArgs a{};
         a.nodes2 = n2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
-        a.max_leaf = 3; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tri_counter;
+        a.max_leaf = s.max_leaf; a.pack_below = s.lbvh ? s.pack_below : 0u; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tri_counter;
         a.tris_sorted = out->tris2 + out->tri_off[m]; a.tris8 = out->tris8; a.leaf_ids = nullptr; a.leaf_out = nullptr;
         a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = tail; a.capacity = L + 8; a.overflow = overflow;
         PT_TRY(collapse_tree(s, a, n, &out->blas_root8[m], st));
