@@ -122,6 +122,63 @@ __global__ void k_instance_boxes(const PtInstance* __restrict__ inst, const uint
     }
 }
 
+// Exact world boxes: every vertex of the instance's mesh through the transform.  The box of a rotated box is up
+// to sqrt(3) larger per axis than the box of the rotated mesh, and every false top-level hit costs a ray an
+// instance entry (ray transform, new frame, BLAS root test), so for rotated instances this is where
+// traversal time goes (C4: DESIGN.md).  grid = (chunks, instances); leaf_lo/hi pre-set to +-3e38.
+__global__ void k_instance_boxes_init(uint32_t n, float* __restrict__ leaf_lo, float* __restrict__ leaf_hi) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 3 * n) { leaf_lo[i] = 3.0e38f; leaf_hi[i] = -3.0e38f; }
+}
+__global__ void __launch_bounds__(256) k_instance_boxes_exact(const PtInstance* __restrict__ inst, const uint32_t* __restrict__ ids,
+                                                               const Bvh8Tri* __restrict__ tris, const uint2* __restrict__ mesh_range,
+                                                               float* __restrict__ leaf_lo, float* __restrict__ leaf_hi) {
+    const uint32_t i = blockIdx.y;
+    const PtInstance& in = inst[ids[i]];
+    const uint2 rg = mesh_range[in.mesh_index];          // (first triangle, count)
+    float m[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) m[k] = in.transform[k];
+    float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < rg.y; t += gridDim.x * blockDim.x) {
+        const float4* q = reinterpret_cast<const float4*>(tris + rg.x + t);
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+            const float4 p = __ldg(q + v);
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                const float w = m[4 * r] * p.x + m[4 * r + 1] * p.y + m[4 * r + 2] * p.z + m[4 * r + 3];
+                lo[r] = fminf(lo[r], w); hi[r] = fmaxf(hi[r], w);
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[r] = fminf(lo[r], __shfl_xor_sync(0xffffffffu, lo[r], o));
+            hi[r] = fmaxf(hi[r], __shfl_xor_sync(0xffffffffu, hi[r], o));
+        }
+    }
+    if ((threadIdx.x & 31u) == 0u && lo[0] <= hi[0]) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r) { atomic_min_f(leaf_lo + 3 * (size_t)i + r, lo[r]); atomic_max_f(leaf_hi + 3 * (size_t)i + r, hi[r]); }
+    }
+}
+// pad (fp32 transform here, fp32 inverse transform in traversal: a few ulp apart; 1e-5 relative is ~100x that)
+__global__ void k_instance_boxes_finish(uint32_t n, float* __restrict__ leaf_lo, float* __restrict__ leaf_hi, float* __restrict__ bounds) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int a = 0; a < 3; ++a) {
+        float lo = leaf_lo[3 * (size_t)i + a], hi = leaf_hi[3 * (size_t)i + a];
+        const float pad = 1e-5f * fmaxf(fmaxf(fabsf(lo), fabsf(hi)), hi - lo) + 1e-30f;
+        lo -= pad; hi += pad;
+        leaf_lo[3 * (size_t)i + a] = lo; leaf_hi[3 * (size_t)i + a] = hi;
+        atomic_min_f(bounds + a, lo);
+        atomic_max_f(bounds + 3 + a, hi);
+    }
+}
+
 // ------------------------------------------------------------------ Morton codes
 __device__ __forceinline__ uint64_t expand21(uint32_t v) {
     uint64_t x = v & 0x1fffffu;
@@ -584,7 +641,7 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
 // ------------------------------------------------------------------ host orchestration
 void SceneBvh::release() {
     cudaFree(nodes8); cudaFree(node_bits8); cudaFree(tris8); cudaFree(tlas_leaf_instance); cudaFree(nodes2); cudaFree(tris2);
-    cudaFree(tlas2); cudaFree(tlas2_leaf_instance); cudaFree(mesh_bounds);
+    cudaFree(tlas2); cudaFree(tlas2_leaf_instance); cudaFree(mesh_bounds); cudaFree(mesh_tri_range); mesh_tri_range = nullptr;
     nodes8 = nullptr; node_bits8 = nullptr; tris8 = nullptr; tlas_leaf_instance = nullptr; nodes2 = nullptr; tris2 = nullptr;
     tlas2 = nullptr; tlas2_leaf_instance = nullptr; mesh_bounds = nullptr;
 }
@@ -754,7 +811,14 @@ int build_tlas(Scratch& s, SceneBvh* out, const PtInstance* d_instances, cudaStr
     if (cudaMemcpyAsync(ids_unsorted, s.vals_in, 4 * (size_t)NI, cudaMemcpyDeviceToDevice, st) != cudaSuccess) rc = PT_ERR_CUDA;
     if (rc == PT_OK) {
         k_init_bounds<<<1, 32, 0, st>>>(s.bounds);
-        k_instance_boxes<<<blocks_for(NI), kThreads, 0, st>>>(d_instances, ids_unsorted, NI, out->mesh_bounds, s.leaf_lo, s.leaf_hi, s.bounds);
+        if (out->exact_instance_boxes) {
+            k_instance_boxes_init<<<blocks_for(3 * NI), kThreads, 0, st>>>(NI, s.leaf_lo, s.leaf_hi);
+            const uint32_t chunks = std::max(1u, std::min(64u, (out->max_mesh_tris + 2047u) / 2048u));
+            k_instance_boxes_exact<<<dim3(chunks, NI), 256, 0, st>>>(d_instances, ids_unsorted, out->tris2, out->mesh_tri_range, s.leaf_lo, s.leaf_hi);
+            k_instance_boxes_finish<<<blocks_for(NI), kThreads, 0, st>>>(NI, s.leaf_lo, s.leaf_hi, s.bounds);
+        } else {
+            k_instance_boxes<<<blocks_for(NI), kThreads, 0, st>>>(d_instances, ids_unsorted, NI, out->mesh_bounds, s.leaf_lo, s.leaf_hi, s.bounds);
+        }
         rc = build_tree(s, NI, out->tlas2, st);
     }
     if (rc == PT_OK) {
@@ -849,6 +913,18 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
         PT_TRY(collapse_tree(s, a, n, &out->blas_root8[m], st));
     }
     // ---- TLAS
+    {
+        std::vector<uint2> rg(std::max<size_t>(M, 1), make_uint2(0u, 0u));
+        uint64_t instanced = 0;
+        for (size_t m = 0; m < M; ++m) { rg[m] = make_uint2(out->tri_off[m], out->tri_count[m]); out->max_mesh_tris = std::max(out->max_mesh_tris, out->tri_count[m]); }
+        for (uint32_t i : valid_inst) instanced += out->tri_count[h_instances[i].mesh_index];
+        PT_CU(cudaMalloc(&out->mesh_tri_range, sizeof(uint2) * rg.size()));
+        PT_CU(cudaMemcpyAsync(out->mesh_tri_range, rg.data(), sizeof(uint2) * rg.size(), cudaMemcpyHostToDevice, st));
+        PT_CU(cudaStreamSynchronize(st));
+        const char* e = std::getenv("PT_TLAS_CORNER_BOXES");   // A/B switch for tools/
+        // exact boxes touch every instanced triangle once per (re)build: bounded so that it stays well under a millisecond
+        out->exact_instance_boxes = !(e && e[0] == '1') && instanced <= (64ull << 20);
+    }
     PT_CU(cudaMemcpyAsync(&out->tlas_node_base, node_counter, 4, cudaMemcpyDeviceToHost, st));
     PT_CU(cudaStreamSynchronize(st));
     out->valid_inst = valid_inst;

@@ -25,6 +25,9 @@ struct SceneBvh {
     std::vector<uint32_t> tri_off;      // per mesh
     std::vector<uint32_t> tri_count;    // per mesh
     float* mesh_bounds = nullptr;       // device, 6 floats per mesh
+    uint2* mesh_tri_range = nullptr;    // device, per mesh: (first triangle in tris2, count)
+    uint32_t max_mesh_tris = 0;
+    bool exact_instance_boxes = false;  // TLAS leaves from transformed vertices instead of transformed mesh-box corners
     // TLAS rebuild state (animated instances)
     uint32_t tlas_node_base = 0;        // first BVH8 node of the TLAS (everything below belongs to BLASes)
     std::vector<uint32_t> valid_inst;   // instances that reference a non-empty mesh
