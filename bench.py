@@ -14,6 +14,7 @@ Prints ONE JSON line on rank 0.
 import argparse
 import ctypes as C
 import json
+import math
 import os
 import subprocess
 import sys
@@ -310,9 +311,23 @@ def main():
         bytes_per_ray = (80.0 * nodes + 48.0 * tris) / max(1, crays)
         n_trace_launches = args.steps * seg if spp == 1 else None
         achieved = bytes_per_ray * rays_local / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else 0.0
+        # DRAM bytes per K-trace launch from the committed `ncu --set full` capture of this workload (None if absent)
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                tj = json.load(f)
+            if tj.get("workload") == args.workload:
+                traffic = tj["k_trace_persistent"]["dram_bytes_per_launch"]
+        except (OSError, KeyError, ValueError):
+            pass
+        # bloat guard: one root-to-leaf descent of a perfect 8-ary tree with 3 triangles per leaf
+        per_mesh = [sum(ps.primitives[p].triangle_count for p in range(m.start, m.end)) for m in ps.meshes]
+        t_blas, n_inst = max(per_mesh + [1]), max(1, len(ps.instances))
+        ceil_log8 = lambda v: 0 if v <= 1 else int(math.ceil(math.log(v, 8) - 1e-9))
+        a_floor = 80.0 * (ceil_log8(t_blas / 3.0) + ceil_log8(n_inst)) + 48.0 * 3
         roof = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                "traffic": None, "kernel": "k_trace<BVH8>", "peak_source": pk_src,
-                "algorithmic_bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),
+                "traffic": traffic, "kernel": "k_trace_persistent", "peak_source": pk_src,
+                "algorithmic_bytes_per_ray": bytes_per_ray, "a_floor_bytes_per_ray": a_floor, "a_trav_over_floor": bytes_per_ray / a_floor, "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),
                 "trace_ms_per_step": trace_ms / args.steps, "shade_ms_per_step": shade_ms / args.steps, "other_ms_per_step": other_ms / args.steps,
                 "trace_mrays_per_s": rays_local / (trace_ms * 1e-3) / 1e6 if trace_ms > 0 else 0.0,
                 "note": "BVH (nodes+triangles) is L2-resident on B200; the HBM peak is the contract's denominator, see DESIGN.md"}
