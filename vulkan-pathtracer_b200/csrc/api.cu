@@ -86,7 +86,7 @@ int dev_alloc(T** p, size_t count) {
 
 void free_frame(PtRenderer* r) {
     PathBuffers& b = r->pb;
-    cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.ray_e); cudaFree(b.ray_s); cudaFree(b.ray_m); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b);
+    cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.ray_e); cudaFree(b.ray_s); cudaFree(b.ray_m); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b); cudaFree(b.prim_c); cudaFree(b.prim_d);
     cudaFree(b.atten_sx); cudaFree(b.color_sy); cudaFree(b.final_sb); cudaFree(b.queue[0]); cudaFree(b.queue[1]); cudaFree(b.queue_sorted); cudaFree(b.sort_bins);
     cudaFree(b.qcount); cudaFree(b.trace_next); cudaFree(b.trav_counters);
     b = PathBuffers{};
@@ -118,7 +118,7 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
     PathBuffers& b = r->pb;
     int rc;
 #define A(ptr, cnt) if ((rc = dev_alloc(&(ptr), (cnt))) != PT_OK) return rc
-    A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.ray_m, n); A(b.hit_a, n); A(b.hit_b, n); A(b.prim_a, n); A(b.prim_b, n);
+    A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.ray_m, n); A(b.hit_a, n); A(b.hit_b, n); { const size_t np = r->cfg.num_samples > 1 ? n : 1; A(b.prim_a, np); A(b.prim_b, np); A(b.prim_c, np); A(b.prim_d, np); }
     A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n); A(b.queue_sorted, n); A(b.sort_bins, (size_t)r->scene.num_materials + 4);
     A(b.qcount, (size_t)r->max_iters + 2); A(b.trace_next, (size_t)r->max_iters + 2); A(b.trav_counters, 4);
     const size_t px = (size_t)pm.width * pm.height;

@@ -215,11 +215,16 @@ __global__ void __launch_bounds__(256) k_matsort_scatter(DeviceScene sc, PathBuf
 // bounce loop (ray_gen.rgen:65-97), and either emits the next ray (appended to the next queue) or
 // ends the sample; a finished sample restarts from the cached primary hit (every sample of a pixel
 // shoots the same primary ray, quirk Q1) until NUM_SAMPLES are done, then the pixel is stored.
+// Two instantiations.  kMulti = false (one sample per pixel, C2): no primary-surface cache, no restart-from-cache
+// path; 80 registers / 6 CTAs per SM measured best (C2 shade 4 / 5 / 6 / 8 blocks: 0.362 / 0.363 / 0.339 / 0.346 ms).
+// kMulti = true (S > 1): restarts read the cached primary surface; here spills are what hurts (C3 shade at
+// 4 / 5 / 6 blocks: 656 / 798 / 846 ms), so 128 registers / 4 CTAs per SM.
 #ifdef PT_SHADE_MIN_BLOCKS
 #define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, PT_SHADE_MIN_BLOCKS)
 #else
-#define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, 4)   // 128 regs, no spills: with all texel loads in flight ILP beats occupancy (profiles/)
+#define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, kMulti ? 4 : 6)
 #endif
+template <bool kMulti>
 __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers pb, FrameParams fp, uint32_t iter) {
     const uint32_t n = pb.qcount[iter];
     const uint32_t* __restrict__ qin = (fp.flags & PT_FLAG_SORT_BY_MATERIAL) ? pb.queue_sorted : pb.queue[iter & 1u];
@@ -255,61 +260,93 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                 h.t = ha.x; h.b1 = ha.y; h.b2 = ha.z; h.instance = __float_as_uint(ha.w);
                 h.primitive_index = hb.x; h.triangle_index = hb.y;
             }
-            if (s == 0u && j == 0u) {
-                // first segment of the pixel: this is the primary hit
-                if (S > 1u) {   // cached for the later samples of this pixel (quirk Q1)
-                    pb.prim_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.instance));
-                    pb.prim_b[slot] = make_uint2(h.primitive_index, h.triangle_index);
-                }
+            // Every sample of a pixel shoots the same primary ray (quirk Q1), so the primary hit is traced once.
+            // With S > 1 its *shading inputs* (64 B: normal, roughness, albedo, metallic, emission, hit distance,
+            // geometric normal) are cached at iteration 0 and a restarted sample reads them back instead of
+            // re-fetching vertices, material and texels: same values, hence the same bits, without the chain of
+            // dependent loads (K-shade is latency-bound on multi-sample workloads).
+            const bool keep_primary = kMulti && iter == 0u && !(fp.flags & PT_FLAG_NO_PRIMARY_REUSE);
+            if (iter == 0u) {
                 const size_t pi = (size_t)y * pm.width + x;
                 fp.id_inst[pi] = h.instance; fp.id_prim[pi] = h.primitive_index; fp.id_tri[pi] = h.triangle_index;
             }
+            bool from_cache = false;
             for (;;) {
                 bool end_sample = false;
-                if (h.t == kMissT) {                                                        // :65-70
+                float t_hit;
+                V3 sf_normal = v3s(0.0f), sf_albedo = v3s(0.0f), sf_emissive = v3s(0.0f), sf_gn = v3s(0.0f);
+                float sf_roughness = 0.0f, sf_metallic = 0.0f;
+                if (kMulti && from_cache) {
+                    const float4 c2 = pb.prim_c[slot];
+                    t_hit = c2.w; sf_emissive = v3(c2.x, c2.y, c2.z);
+                    if (t_hit != kMissT && j + 1u < B) {
+                        const float4 c0 = pb.prim_a[slot], c1 = pb.prim_b[slot], c3 = pb.prim_d[slot];
+                        sf_normal = v3(c0.x, c0.y, c0.z); sf_roughness = c0.w;
+                        sf_albedo = v3(c1.x, c1.y, c1.z); sf_metallic = c1.w;
+                        sf_gn = v3(c3.x, c3.y, c3.z);
+                    }
+                } else {
+                    t_hit = h.t;
+                    if (t_hit != kMissT) {
+                        if (j + 1u >= B && !keep_primary) {
+                            // last segment: loop bound reached (:49,:77); only the emission of this hit is consumed (:75)
+                            sf_emissive = get_emissive(sc, h);
+                        } else {
+                            const TriangleData td = get_triangle_data(sc, h);                   // :72
+                            const MaterialData md = get_material_data(sc, td);                  // :73
+                            sf_normal = md.normal; sf_roughness = md.roughness;
+                            sf_albedo = v3(md.albedo.x, md.albedo.y, md.albedo.z); sf_metallic = md.metallic;
+                            sf_emissive = md.emissive; sf_gn = td.geometry_normal;
+                        }
+                    }
+                    if (keep_primary) {
+                        pb.prim_c[slot] = make_float4(sf_emissive.x, sf_emissive.y, sf_emissive.z, t_hit);
+                        if (t_hit != kMissT) {
+                            pb.prim_a[slot] = make_float4(sf_normal.x, sf_normal.y, sf_normal.z, sf_roughness);
+                            pb.prim_b[slot] = make_float4(sf_albedo.x, sf_albedo.y, sf_albedo.z, sf_metallic);
+                            pb.prim_d[slot] = make_float4(sf_gn.x, sf_gn.y, sf_gn.z, 0.0f);
+                        }
+                    }
+                }
+                if (t_hit == kMissT) {                                                      // :65-70
                     const float t = 0.5f * (direction.y + 1.0f);
                     color = color + atten * mix(v3(1.0f, 1.0f, 1.0f), v3(0.5f, 0.7f, 1.0f), t);
                     end_sample = true;
-                } else if (j + 1u >= B) {
-                    // last segment: loop bound reached (:49,:77); only the emission of this hit is consumed (:75)
-                    color = color + get_emissive(sc, h) * 10.0f * atten;
-                    end_sample = true;
                 } else {
-                    const TriangleData td = get_triangle_data(sc, h);                       // :72
-                    const MaterialData md = get_material_data(sc, td);                      // :73
-                    color = color + md.emissive * 10.0f * atten;                            // :75
-                    ShadingInfo si;
-                    si.out_dir = -direction;                                                // :79
-                    si.normal = md.normal;                                                  // :80
-                    si.lambert_out = dot(si.normal, si.out_dir);                            // :81
-                    const V3 alb = v3(md.albedo.x, md.albedo.y, md.albedo.z);
-                    si.fresnel_0 = mix(v3s(0.02f), alb, md.metallic);                       // :82
-                    si.diffuse_albedo = alb - md.metallic * alb;                            // :83
-                    si.roughness = gmax(0.006f, md.roughness);                              // :84
-                    origin = origin + h.t * direction + td.geometry_normal * 0.00001f;      // :86
-                    direction = sample_brdf(si, pcg2d(seed));                               // :87
-                    const float density = get_brdf_density(si, direction);                  // :89
-                    const float lambert_in = dot(si.normal, direction);                     // :90
-                    if (lambert_in <= 0.0f) {                                               // :91-93
-                        end_sample = true;
+                    color = color + sf_emissive * 10.0f * atten;                            // :75
+                    if (j + 1u < B) {                                                       // :77
+                        ShadingInfo si;
+                        si.out_dir = -direction;                                            // :79
+                        si.normal = sf_normal;                                              // :80
+                        si.lambert_out = dot(si.normal, si.out_dir);                        // :81
+                        si.fresnel_0 = mix(v3s(0.02f), sf_albedo, sf_metallic);             // :82
+                        si.diffuse_albedo = sf_albedo - sf_metallic * sf_albedo;            // :83
+                        si.roughness = gmax(0.006f, sf_roughness);                          // :84
+                        origin = origin + t_hit * direction + sf_gn * 0.00001f;             // :86
+                        direction = sample_brdf(si, pcg2d(seed));                           // :87
+                        const float density = get_brdf_density(si, direction);              // :89
+                        const float lambert_in = dot(si.normal, direction);                 // :90
+                        if (lambert_in <= 0.0f) {                                           // :91-93
+                            end_sample = true;
+                        } else {
+                            atten = atten * (brdf(si, direction) * lambert_in / density);   // :95
+                            ++j;
+                            emit = true;
+                        }
                     } else {
-                        atten = atten * (brdf(si, direction) * lambert_in / density);       // :95
-                        ++j;
-                        emit = true;
+                        end_sample = true;   // last segment: loop bound reached (:49)
                     }
                 }
                 if (!end_sample) break;      // next segment must be traced
                 final_color = final_color + color;                                          // :99
                 ++s;
-                if (s == S) { write_pixel(fp, pm.width, x, y, final_color); break; }        // :102-104
+                if (!kMulti || s == S) { write_pixel(fp, pm.width, x, y, final_color); break; }   // :102-104 (kMulti = false: S == 1)
                 // next sample (:44-48)
                 color = v3s(0.0f); atten = v3s(1.0f); j = 0u;
                 origin = v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]);
                 direction = primary_direction(fp.cam, x, y, pm.width, pm.height);
                 if (fp.flags & PT_FLAG_NO_PRIMARY_REUSE) { emit = true; break; }
-                const float4 ha = pb.prim_a[slot]; const uint2 hb = pb.prim_b[slot];
-                h.t = ha.x; h.b1 = ha.y; h.b2 = ha.z; h.instance = __float_as_uint(ha.w);
-                h.primitive_index = hb.x; h.triangle_index = hb.y;
+                from_cache = true;
             }
             if (emit) {
                 store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, origin, direction, 0.001f, 10000.0f);
@@ -458,9 +495,10 @@ void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t
 
 void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
                   int num_sms, cudaStream_t st) {
-    static int blocks = 0;
-    if (!blocks) blocks = persistent_blocks(k_shade, kShadeThreads, num_sms);
-    k_shade<<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+    static int blocks[2] = {0, 0};
+    if (!blocks[0]) { blocks[0] = persistent_blocks(k_shade<false>, kShadeThreads, num_sms); blocks[1] = persistent_blocks(k_shade<true>, kShadeThreads, num_sms); }
+    if (fp.num_samples > 1u) k_shade<true><<<blocks[1], kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+    else k_shade<false><<<blocks[0], kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
 }
 
 void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,

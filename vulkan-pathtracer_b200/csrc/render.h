@@ -22,8 +22,9 @@ struct PathBuffers {
     float4* ray_m;       // shear row m1.xyz
     float4* hit_a;       // t, b1, b2, instance (bits)
     uint2* hit_b;        // primitive_index, triangle_index
-    float4* prim_a;      // cached primary hit (reused for every sample, quirk Q1)
-    uint2* prim_b;
+    // cached shading inputs of the primary hit (S > 1; reused for every sample, quirk Q1):
+    // a = normal, roughness | b = albedo, metallic | c = emission, hit distance (1e32 = miss) | d = geometric normal
+    float4 *prim_a, *prim_b, *prim_c, *prim_d;
     float4* atten_sx;    // atten.rgb, seed.x (bits)
     float4* color_sy;    // color.rgb, seed.y (bits)
     float4* final_sb;    // final_color.rgb, sample | bounce << 16 (bits)
