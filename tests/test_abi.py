@@ -106,3 +106,18 @@ def test_pfm_and_exr_writers(tmp_path):
         back = None
     if back is not None and back.ndim == 3:
         assert np.allclose(back[..., :3][..., ::-1], img[..., :3])
+
+
+def test_new_round_one_entry_points_reject_null_arguments():
+    """Every entry point added for SURVEY 8(f) returns a status (no crash) on null arguments."""
+    L = b200pt.lib()
+    cam = b200pt.PtCameraState()
+    assert L.pt_camera_state_new(0.5, 1.0, None, C.byref(cam)) == -1
+    assert L.pt_camera_update(None, None) == -1
+    assert L.pt_camera_update(C.byref(cam), None) == -1
+    assert L.pt_camera_update_aspect_ratio(None, 1.0) == -1
+    assert L.pt_camera_pack(None, 0, None) == -1
+    assert L.pt_set_instance_transforms(None, None, 0, None) == -1
+    assert L.pt_debug_bvh_digest(None, None) == -1
+    assert L.pt_read_rgba32f_overlapped(None, None) == -1
+    assert C.sizeof(b200pt.PtCameraState) == 26 * 4 and C.sizeof(b200pt.PtInput) == 20

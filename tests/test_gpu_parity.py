@@ -492,3 +492,17 @@ def test_single_instance_scene_skips_the_top_level_only_when_identity():
     fresh_img, fresh_ids, _ = render(ps_id, W, H, spp, seg, 1)   # created as identity from the start (camera at 0)
     oimg, oids, _ = orc.OracleScene(ps_id, True).render(S.render_config(W, H, spp, seg), S.camera_default(W, H, 1), True)
     assert bits_equal(fresh_img, oimg).all() and all((a == b).all() for a, b in zip(fresh_ids, oids))
+
+
+def test_builder_is_deterministic_across_builds():
+    """Same scene, repeated builds with other work in between: identical digests of every builder stage."""
+    ps = S.random_soup(3, 3000, 3, 7).pack()
+    pc = S.cornell().pack()
+    seen = set()
+    for k in range(12):
+        if k % 3 == 0:
+            rc = b200pt.Renderer(pc, 96, 64, 1 + k % 2, 2); rc.record(S.camera_default(96, 64, k)); rc.sync(); rc.deinit()
+        r = b200pt.Renderer(ps, 100, 60, 1, 2, flags=(0, b200pt.PT_FLAG_TRACE_BVH2)[k & 1])
+        seen.add(r.bvh_digest())
+        r.deinit()
+    assert len(seen) == 1, f"{len(seen)} different acceleration structures from the same input"
