@@ -329,6 +329,7 @@ int pt_debug_bvh_digest(PtRenderer* r, uint64_t digest[6]);
 int pt_set_instance_transforms(PtRenderer* r, const float* transforms, size_t num_instances, float* ms_rebuild);
 
 /* Process-wide kernel tuning knobs (measurement only; results never depend on them).
+ *   "chunk": rays a K-trace warp takes from the queue per global atomic (default 32).
  *   "postpone": retired (triangle postponing was measured flat and removed); accepted, no effect. */
 int pt_set_option(const char* key, int value);
 

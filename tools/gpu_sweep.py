@@ -6,7 +6,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "vulkan-pathtrac
 import b200pt
 from tools import scene as S
 
-def measure(r, W, H, frames=8, warm=2):
+def measure(r, W, H, frames=int(os.environ.get("SWEEP_FRAMES", "8")), warm=2):
     r.set_profiling(True)
     tr = sh = ot = 0.0; rays = 0
     for f in range(warm + frames):
@@ -30,6 +30,14 @@ def main():
             if ref is None: ref = img
             same = np.array_equal(ref.view(np.uint32), img.view(np.uint32))
             print(f"postpone<{v:2d}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays  {rays/(tr*1e3):.0f} Mrays/s(trace)  same_image={same}")
+        r.deinit()
+    elif what == "chunk":
+        r = b200pt.Renderer(ps, W, H, spp, seg)
+        for v in (8, 16, 32, 64, 128):
+            b200pt.set_option("chunk", v)
+            tr, sh, ot, rays = measure(r, W, H)
+            print(f"chunk {v:4d}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}")
+        b200pt.set_option("chunk", 32)
         r.deinit()
     elif what == "one":
         r = b200pt.Renderer(ps, W, H, spp, seg)

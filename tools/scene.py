@@ -843,4 +843,6 @@ CONFIGS = {
     "c3": (sponza_scale, 3840, 2160, 64, 8),
     "c4": (instanced, 1920, 1080, 4, 4),
     "c5": (heavy_material, 1920, 1080, 16, 6),
+    # one rank's share of C3 on 8 GPUs (an eighth of the pixels): small wavefronts, same iteration count
+    "c3_8th": (sponza_scale, 1360, 760, 64, 8),
 }

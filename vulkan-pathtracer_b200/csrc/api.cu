@@ -88,7 +88,7 @@ void free_frame(PtRenderer* r) {
     PathBuffers& b = r->pb;
     cudaFree(b.ray_o); cudaFree(b.ray_d); cudaFree(b.ray_e); cudaFree(b.ray_s); cudaFree(b.ray_m); cudaFree(b.hit_a); cudaFree(b.hit_b); cudaFree(b.prim_a); cudaFree(b.prim_b); cudaFree(b.prim_c); cudaFree(b.prim_d);
     cudaFree(b.atten_sx); cudaFree(b.color_sy); cudaFree(b.final_sb); cudaFree(b.queue[0]); cudaFree(b.queue[1]); cudaFree(b.queue_sorted); cudaFree(b.sort_bins);
-    cudaFree(b.qcount); cudaFree(b.trace_next); cudaFree(b.trav_counters);
+    cudaFree(b.qcount); cudaFree(b.trav_counters);   // trace_next / shade_next live inside qcount's allocation
     b = PathBuffers{};
     cudaFree(r->d_image); cudaFree(r->d_ids); cudaFree(r->d_bgra); cudaFree(r->d_upscaled); cudaFree(r->d_accum);
     r->d_image = nullptr; r->d_ids = nullptr; r->d_bgra = nullptr; r->d_upscaled = nullptr; r->d_accum = nullptr;
@@ -120,7 +120,8 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
 #define A(ptr, cnt) if ((rc = dev_alloc(&(ptr), (cnt))) != PT_OK) return rc
     A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.ray_m, n); A(b.hit_a, n); A(b.hit_b, n); { const size_t np = r->cfg.num_samples > 1 ? n : 1; A(b.prim_a, np); A(b.prim_b, np); A(b.prim_c, np); A(b.prim_d, np); }
     A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n); A(b.queue_sorted, n); A(b.sort_bins, (size_t)r->scene.num_materials + 4);
-    A(b.qcount, (size_t)r->max_iters + 2); A(b.trace_next, (size_t)r->max_iters + 2); A(b.trav_counters, 4);
+    A(b.qcount, 3 * ((size_t)r->max_iters + 2)); A(b.trav_counters, 4);
+    b.trace_next = b.qcount + ((size_t)r->max_iters + 2); b.shade_next = b.trace_next + ((size_t)r->max_iters + 2);
     const size_t px = (size_t)pm.width * pm.height;
     A(r->d_image, px * 4); A(r->d_ids, px * 3);
 #undef A
@@ -385,8 +386,7 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     fp.image = r->d_remote_image ? r->d_remote_image : r->d_image;
     const size_t px = (size_t)r->pm.width * r->pm.height;
     fp.id_inst = r->d_ids; fp.id_prim = r->d_ids + px; fp.id_tri = r->d_ids + 2 * px;
-    PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
-    PT_CUDA_CHECK(cudaMemsetAsync(pb.trace_next, 0, sizeof(uint32_t) * ((size_t)r->max_iters + 2), st));
+    PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * 3 * ((size_t)r->max_iters + 2), st));   // counts + both cursor arrays
     bool waited_copy = !r->copy_pending;
     auto wait_copy = [&]() {   // a pipelined read-back of the previous frame must finish before the image is written again
         if (!waited_copy) { cudaStreamWaitEvent(st, r->ev_copy_done, 0); waited_copy = true; r->copy_pending = false; }

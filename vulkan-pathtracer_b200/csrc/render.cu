@@ -231,9 +231,15 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
     uint32_t* __restrict__ qout = pb.queue[(iter + 1u) & 1u];
     uint32_t* qout_count = pb.qcount + iter + 1u;
     const uint32_t S = fp.num_samples, B = fp.num_bounces;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    // whole warps iterate together (queue_push is warp-collective over the active mask)
-    for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += stride) {
+    // whole warps iterate together (queue_push is warp-collective over the active mask); 32 entries per atomic, taken
+    // dynamically: the cost of an entry varies from a sky lookup to full material + BSDF, so a static split leaves
+    // warps idle at the end of small wavefronts
+    uint32_t* cursor = pb.shade_next + iter;
+    for (;;) {
+        uint32_t base = 0;
+        if ((threadIdx.x & 31u) == 0u) base = atomicAdd(cursor, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
         const uint32_t idx = base + (threadIdx.x & 31u);
         bool emit = false;
         uint32_t slot = 0;
@@ -452,8 +458,9 @@ int persistent_blocks(K kernel, int threads, int num_sms) {
 }  // namespace
 
 // tuning knobs; see pt_set_option
+static uint32_t g_chunk = 32;
 int set_option(const char* key, int value) {
-    (void)value;
+    if (!strcmp(key, "chunk")) { g_chunk = (uint32_t)(value < 1 ? 1 : value); return 0; }   // K-trace: rays per queue atomic
     if (!strcmp(key, "postpone")) return 0;   // retired knob (triangle postponing was removed from K-trace); accepted, no effect
     return -1;
 }
@@ -476,7 +483,7 @@ void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, T
         TraceIO io;
         io.queue = pb.queue[iter & 1u]; io.count_ptr = pb.qcount + iter; io.count = 0; io.cursor = pb.trace_next + iter;
         io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.ray_e = pb.ray_e; io.ray_s = pb.ray_s; io.ray_m = pb.ray_m; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
-        io.hit_a_stride = 1; io.hit_b_stride = 1; io.bias_word = 0x4B000000u;
+        io.hit_a_stride = 1; io.hit_b_stride = 1; io.bias_word = 0x4B000000u; io.chunk = g_chunk;
         k_trace_persistent<<<blocks[3], kTraceBlock, 0, st>>>(sc, io);
         return;
     }
@@ -514,7 +521,7 @@ void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, Hi
         io.ray_o = so; io.ray_d = sd; io.ray_e = se; io.ray_s = ss; io.ray_m = sm;
         io.hit_a = reinterpret_cast<float4*>(hits); io.hit_a_stride = 2;
         io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4;
-        io.bias_word = 0x4B000000u;
+        io.bias_word = 0x4B000000u; io.chunk = g_chunk;
         k_trace_persistent<<<blocks, kTraceBlock, 0, st>>>(sc, io);
         return;
     }

@@ -33,6 +33,7 @@ struct PathBuffers {
     uint32_t* sort_bins;      // [num_materials + 2] counting-sort bins (zero between uses)
     uint32_t* qcount;    // [max_iters + 1] entries of queue k (zeroed per frame)
     uint32_t* trace_next;// [max_iters] dynamic-fetch cursors of the persistent trace kernel
+    uint32_t* shade_next;// [max_iters] the same for K-shade (qcount, trace_next and shade_next are one allocation)
     uint32_t* trav_counters;  // [2] nodes, tris (counting walker)
 };
 
