@@ -166,6 +166,7 @@ def main():
                          "pixels are stored straight into rank 0's image over NVLink (CUDA IPC), one 4-byte NCCL all-reduce as fence")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-l2-flush", action="store_true")
+    ap.add_argument("--single-frame-in-flight", action="store_true", help="e2e leg without the sibling frame context")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
@@ -280,10 +281,28 @@ def main():
 
     # ---------------- end-to-end: public API with host buffers (camera in, image out through pinned memory)
     host_img = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+    # One GPU: two frames in flight, like the reference's one command buffer + fence per swapchain image
+    # (main.zig:209-217,255-259): a sibling context shares the device scene and has its own stream, path state,
+    # image and pinned destination, so the tail of frame k overlaps ray generation + primary traversal of frame k+1.
+    in_flight = 2 if (world == 1 and not args.single_frame_in_flight) else 1
+    if in_flight == 2:
+        ctx = [r, r.sibling()]
+        hosts = [host_img, torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)]
+        for k in range(2):      # untimed: the sibling creates its copy stream and events on first use
+            ctx[1].record(S.camera_default(W, H, k))
+            b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(ctx[1].handle, hosts[1].data_ptr()))
+        ctx[1].sync()
     barrier()
     t0 = time.perf_counter()
     e2e_rays = 0
-    for k in range(args.steps):
+    for k in range(args.steps if in_flight == 2 else 0):
+        cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
+        c = ctx[k & 1]
+        c.record(cam)
+        b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(c.handle, hosts[k & 1].data_ptr()))
+    if in_flight == 2:
+        ctx[0].sync(); ctx[1].sync()
+    for k in range(args.steps if in_flight == 1 else 0):
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
         r.record(cam, sp)
         combine()
@@ -360,10 +379,12 @@ def main():
                            "scene_gen_s": t_gen, "create_s": t_create},
                 "spp_per_s": spp_s, "rays_per_step": rays_total / args.steps / (1 if tiles else world),
                 "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(S.PtCamera), "d2h_bytes_per_step": W * H * 16,
-                        "ms_per_step": 1e3 * e2e_s / args.steps, "spp_per_s": spp * frames_done / e2e_s},
+                        "ms_per_step": 1e3 * e2e_s / args.steps, "spp_per_s": spp * frames_done / e2e_s, "frames_in_flight": in_flight},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
+    if in_flight == 2:
+        ctx[1].deinit()     # the sibling goes first: the scene belongs to r
     r.deinit()
     if world > 1:
         dist.destroy_process_group()

@@ -252,6 +252,11 @@ int pt_camera_pack(const PtCameraState* camera, uint32_t frame_count, PtCamera* 
 /* ------------------------------------------------------------------ RaytracingPass
  * init    src/RaytracingPass.zig:87-200  (scene upload, BLAS/TLAS build -> GPU BVH8 builder) */
 int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer** out);
+/* frames in flight (the reference: one command buffer + fence per swapchain image, src/main.zig:209-217,255-259): a second
+ * frame context over the SAME device scene and acceleration structures -- own stream, path state, image and
+ * read-back pipeline.  `parent` must outlive it and owns the scene (pt_set_instance_transforms goes to the parent,
+ * with no frame in flight on either).  Alternate pt_render between the two to overlap consecutive frames. */
+int pt_create_sibling(PtRenderer* parent, PtRenderer** out);
 /* deinit  src/RaytracingPass.zig:202-222 */
 void pt_destroy(PtRenderer* r);
 /* record  src/RaytracingPass.zig:520-675: enqueue one frame on `cuda_stream` (a cudaStream_t, or

@@ -506,3 +506,24 @@ def test_builder_is_deterministic_across_builds():
         seen.add(r.bvh_digest())
         r.deinit()
     assert len(seen) == 1, f"{len(seen)} different acceleration structures from the same input"
+
+
+def test_sibling_context_shares_the_scene_and_keeps_two_frames_in_flight():
+    """pt_create_sibling: same device scene, own stream / path state / image; frames alternate between the two."""
+    ps = S.atrium(1234, 20000, 6, 64).pack()
+    W, H, spp, seg = 320, 180, 2, 3
+    a = b200pt.Renderer(ps, W, H, spp, seg)
+    b = a.sibling()
+    want = []
+    for f in range(4):
+        a.record(S.camera_default(W, H, f)); a.sync(); want.append(a.image().copy())
+    # two frames in flight: submit on a and b back to back, read each after its own fence
+    for f in (0, 2):
+        a.record(S.camera_default(W, H, f)); b.record(S.camera_default(W, H, f + 1))
+        a.sync(); b.sync()
+        assert bits_equal(a.image(), want[f]).all() and bits_equal(b.image(), want[f + 1]).all()
+    rays = random_rays(9, 20000, 10.0, b200pt.PtRay_dtype)
+    assert not hits_mismatch(a.trace(rays), b.trace(rays)).any()
+    with pytest.raises(b200pt.PtError):
+        b.set_instance_transforms(np.eye(4, dtype=np.float32).reshape(1, 16))     # the scene belongs to the parent
+    b.deinit(); a.deinit()

@@ -111,6 +111,7 @@ def lib():
         L.pt_camera_update.argtypes = [C.POINTER(PtCameraState), C.POINTER(PtInput)]
         L.pt_camera_update_aspect_ratio.argtypes = [C.POINTER(PtCameraState), C.c_float]
         L.pt_camera_pack.argtypes = [C.POINTER(PtCameraState), C.c_uint32, C.POINTER(PtCamera)]
+        L.pt_create_sibling.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.pt_debug_bvh_digest.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 6)]
         L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
         L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
@@ -200,6 +201,16 @@ class Renderer:
         w, h = C.c_uint32(), C.c_uint32()
         check(lib().pt_render_extent(self.handle, C.byref(w), C.byref(h)))
         self.width, self.height = w.value, h.value
+
+    def sibling(self):
+        """A second frame context over the same device scene (frames in flight, main.zig:209-217,255-259): own stream,
+        path state and image.  Deinit it before this renderer."""
+        other = Renderer.__new__(Renderer)
+        other.handle = C.c_void_p()
+        other.cfg = self.cfg
+        check(lib().pt_create_sibling(self.handle, C.byref(other.handle)))
+        other.width, other.height = self.width, self.height
+        return other
 
     # -- RaytracingPass.record / fence / resize / deinit
     def record(self, camera, stream=None):

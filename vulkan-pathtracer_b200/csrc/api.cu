@@ -69,6 +69,7 @@ struct PtRenderer {
     // standalone trace buffers
     uint32_t* d_cursor = nullptr;
     bool peer_root = false;   // pt_ipc_export_image was called: other ranks store their tiles into d_image
+    bool owns_scene = true;   // false for a sibling (pt_create_sibling): scene + BVH belong to the parent
 };
 
 namespace {
@@ -279,12 +280,15 @@ void destroy_impl(PtRenderer* r) {
     if (r->stream) cudaStreamSynchronize(r->stream);
     free_frame(r);
     for (auto e : r->events) cudaEventDestroy(e);
-    for (auto p : r->d_texels) cudaFree(p);
-    for (auto p : r->d_atlases) cudaFree(p);
-    cudaFree(r->d_blob); cudaFree(r->d_prims); cudaFree(r->d_materials); cudaFree(r->d_textures);
-    cudaFree(r->d_instances_raw); cudaFree(r->d_instances); cudaFree(r->d_cursor);
+    if (r->owns_scene) {
+        for (auto p : r->d_texels) cudaFree(p);
+        for (auto p : r->d_atlases) cudaFree(p);
+        cudaFree(r->d_blob); cudaFree(r->d_prims); cudaFree(r->d_materials); cudaFree(r->d_textures);
+        cudaFree(r->d_instances_raw); cudaFree(r->d_instances);
+        r->bvh.release();
+    }
+    cudaFree(r->d_cursor);
     if (r->d_remote_image) cudaIpcCloseMemHandle(r->d_remote_image);
-    r->bvh.release();
     if (r->copy_stream) { cudaStreamSynchronize(r->copy_stream); cudaStreamDestroy(r->copy_stream); }
     if (r->ev_frame_done) cudaEventDestroy(r->ev_frame_done);
     if (r->ev_copy_done) cudaEventDestroy(r->ev_copy_done);
@@ -370,6 +374,32 @@ int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer
         if ((rc = dev_alloc(&r->d_cursor, 4)) != PT_OK) break;
         if (r->cfg.flags & PT_FLAG_TRACE_BVH2) r->trace_mode = TRACE_BVH2;
         else if (r->cfg.flags & PT_FLAG_TRACE_WALKER) r->trace_mode = TRACE_BVH8_WALKER;
+    } while (0);
+    if (rc != PT_OK) { std::string keep = g_last_error; destroy_impl(r); g_last_error = keep; return rc; }
+    *out = r;
+    return PT_OK;
+}
+
+// A second frame context over the same device scene: its own stream, path state, image and read-back pipeline,
+// sharing scene data and acceleration structures with `parent` (which must outlive it).  Alternating pt_render
+// between a renderer and its sibling keeps two frames in flight -- the reference does the same with one command
+// buffer and fence per swapchain image (main.zig:209-217,255-259) -- so the tail of one frame's last wavefront
+// overlaps the next frame's ray generation and primary traversal.
+int pt_create_sibling(PtRenderer* parent, PtRenderer** out) {
+    PT_REQUIRE(parent && out, "pt_create_sibling: null argument");
+    *out = nullptr;
+    PT_REQUIRE(parent->owns_scene, "pt_create_sibling: the parent must be a renderer made by pt_create");
+    PT_CUDA_CHECK(cudaSetDevice(parent->device));
+    PtRenderer* r = new PtRenderer();
+    r->cfg = parent->cfg; r->device = parent->device; r->num_sms = parent->num_sms; r->owns_scene = false;
+    r->d_blob = parent->d_blob; r->d_prims = parent->d_prims; r->d_materials = parent->d_materials; r->d_textures = parent->d_textures;
+    r->d_instances_raw = parent->d_instances_raw; r->d_instances = parent->d_instances;
+    r->bvh = parent->bvh; r->scene = parent->scene; r->num_triangles = parent->num_triangles; r->trace_mode = parent->trace_mode;
+    int rc = PT_OK;
+    do {
+        if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); rc = PT_ERR_CUDA; break; }
+        if ((rc = alloc_frame(r, parent->full_w, parent->full_h, r->cfg.divider)) != PT_OK) break;
+        if ((rc = dev_alloc(&r->d_cursor, 4)) != PT_OK) break;
     } while (0);
     if (rc != PT_OK) { std::string keep = g_last_error; destroy_impl(r); g_last_error = keep; return rc; }
     *out = r;
@@ -718,6 +748,7 @@ int pt_debug_bvh_digest(PtRenderer* r, uint64_t digest[6]) {
 // this is "Tlas.init again" with new matrices: instance records re-derived, top level rebuilt in place.
 int pt_set_instance_transforms(PtRenderer* r, const float* transforms, size_t num_instances, float* ms_rebuild) {
     PT_REQUIRE(r && (transforms || num_instances == 0), "pt_set_instance_transforms: null argument");
+    PT_REQUIRE(r->owns_scene, "pt_set_instance_transforms: call it on the renderer that owns the scene (not a sibling)");
     PT_REQUIRE(num_instances == r->h_instances.size(), "pt_set_instance_transforms: instance count differs from the scene's");
     PT_CUDA_CHECK(cudaSetDevice(r->device));
     { int rc = pt_sync(r); if (rc != PT_OK) return rc; }       // frames in flight still read the old top level
