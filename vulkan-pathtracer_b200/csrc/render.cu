@@ -234,6 +234,10 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
     // whole warps iterate together (queue_push is warp-collective over the active mask); 32 entries per atomic, taken
     // dynamically: the cost of an entry varies from a sky lookup to full material + BSDF, so a static split leaves
     // warps idle at the end of small wavefronts
+    // unorm8 -> float table for the texel and factor conversions (48 per fully textured hit): x / 255.0f, IEEE
+    __shared__ float s_unorm[256];
+    for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) s_unorm[i] = (float)i / 255.0f;
+    __syncthreads();
     uint32_t* cursor = pb.shade_next + iter;
     for (;;) {
         uint32_t base = 0;
@@ -296,10 +300,10 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                     if (t_hit != kMissT) {
                         if (j + 1u >= B && !keep_primary) {
                             // last segment: loop bound reached (:49,:77); only the emission of this hit is consumed (:75)
-                            sf_emissive = get_emissive(sc, h);
+                            sf_emissive = get_emissive(sc, h, s_unorm);
                         } else {
                             const TriangleData td = get_triangle_data(sc, h);                   // :72
-                            const MaterialData md = get_material_data(sc, td);                  // :73
+                            const MaterialData md = get_material_data(sc, td, s_unorm);         // :73
                             sf_normal = md.normal; sf_roughness = md.roughness;
                             sf_albedo = v3(md.albedo.x, md.albedo.y, md.albedo.z); sf_metallic = md.metallic;
                             sf_emissive = md.emissive; sf_gn = td.geometry_normal;

@@ -247,10 +247,16 @@ PT_D float unorm8(uint32_t x) {
     const float rem = __fmaf_rn(-q, 255.0f, xf);
     return __fmaf_rn(rem, r, q);
 }
-PT_D V4 unpack_unorm4x8(uint32_t p) {
+// `lut` (optional): 256 floats, lut[x] = (float)x / 255.0f, in shared memory (K-shade builds it per CTA): one LDS
+// per channel instead of the five-instruction sequence above; the same values by construction.
+PT_D V4 unpack_unorm4x8(uint32_t p, const float* lut = nullptr) {
     V4 r;
-    r.x = unorm8(p & 0xff); r.y = unorm8((p >> 8) & 0xff);
-    r.z = unorm8((p >> 16) & 0xff); r.w = unorm8(p >> 24);
+    if (lut) {
+        r.x = lut[p & 0xff]; r.y = lut[(p >> 8) & 0xff]; r.z = lut[(p >> 16) & 0xff]; r.w = lut[p >> 24];
+    } else {
+        r.x = unorm8(p & 0xff); r.y = unorm8((p >> 8) & 0xff);
+        r.z = unorm8((p >> 16) & 0xff); r.w = unorm8(p >> 24);
+    }
     return r;
 }
 
@@ -281,8 +287,8 @@ PT_D Taps fetch_taps(const TexRec& tex, V2 uv) {
     t.t00 = __ldg(r0 + x0); t.t10 = __ldg(r0 + x1); t.t01 = __ldg(r1 + x0); t.t11 = __ldg(r1 + x1);
     return t;
 }
-PT_D V4 filter_taps(const Taps& t) {
-    const V4 t00 = unpack_unorm4x8(t.t00), t10 = unpack_unorm4x8(t.t10), t01 = unpack_unorm4x8(t.t01), t11 = unpack_unorm4x8(t.t11);
+PT_D V4 filter_taps(const Taps& t, const float* lut = nullptr) {
+    const V4 t00 = unpack_unorm4x8(t.t00, lut), t10 = unpack_unorm4x8(t.t10, lut), t01 = unpack_unorm4x8(t.t01, lut), t11 = unpack_unorm4x8(t.t11, lut);
     const float a = t.a, b = t.b;
     const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
     V4 r;
@@ -292,12 +298,12 @@ PT_D V4 filter_taps(const Taps& t) {
     r.w = t00.w * w00 + t10.w * w10 + t01.w * w01 + t11.w * w11;
     return r;
 }
-PT_D V4 sample_texture(const TexRec& tex, V2 uv) { return filter_taps(fetch_taps(tex, uv)); }
+PT_D V4 sample_texture(const TexRec& tex, V2 uv, const float* lut = nullptr) { return filter_taps(fetch_taps(tex, uv), lut); }
 
 struct MaterialData { V4 albedo; V3 normal, emissive; float roughness, metallic; };
 
 // material.glsl:31-69
-PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& td) {
+PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& td, const float* lut = nullptr) {
     const MatRec* mp = sc.materials + td.material_index;
     const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));     // factors + presence bits
     const uint4 aw = __ldg(reinterpret_cast<const uint4*>(mp) + 5);  // interleaved texels, if any
@@ -334,26 +340,26 @@ PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& t
             if (tex[k].texels) taps[k] = fetch_taps(tex[k], td.uv);
     }
     MaterialData md;
-    md.albedo = unpack_unorm4x8(fac.x);                                                  // :36
+    md.albedo = unpack_unorm4x8(fac.x, lut);                                                // :36
     if (tex[0].texels) {                                                                 // :37-39
-        const V4 t = filter_taps(taps[0]);
+        const V4 t = filter_taps(taps[0], lut);
         md.albedo.x *= t.x; md.albedo.y *= t.y; md.albedo.z *= t.z; md.albedo.w *= t.w;
     }
-    const V4 mr = unpack_unorm4x8(fac.y);                                                // :41-43
+    const V4 mr = unpack_unorm4x8(fac.y, lut);                                              // :41-43
     md.roughness = mr.y; md.metallic = mr.z;
     if (tex[1].texels) {                                                                 // :44-48
-        const V4 t = filter_taps(taps[1]);
+        const V4 t = filter_taps(taps[1], lut);
         md.roughness *= t.y; md.metallic *= t.z;
     }
-    const V4 e = unpack_unorm4x8(fac.z);                                                 // :50
+    const V4 e = unpack_unorm4x8(fac.z, lut);                                            // :50
     md.emissive = v3(e.x, e.y, e.z);
     if (tex[2].texels) {                                                                 // :51-53
-        const V4 t = filter_taps(taps[2]);
+        const V4 t = filter_taps(taps[2], lut);
         md.emissive = md.emissive * v3(t.x, t.y, t.z);
     }
     md.normal = td.normal;                                                               // :55
     if (tex[3].texels) {                                                                 // :56-66
-        const V4 t = filter_taps(taps[3]);
+        const V4 t = filter_taps(taps[3], lut);
         const V3 nts = v3(t.x, t.y, t.z);
         const V3 T = v3(td.tangent.x, td.tangent.y, td.tangent.z);
         const V3 bitangent = cross(td.normal, T) * td.tangent.w;
@@ -367,11 +373,11 @@ PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& t
 // of getTriangleData / getMaterialData nothing but `emissive` is consumed, so only the emissive factor and --
 // when the material has an emissive map -- the interpolated uv and that map's four texels are fetched.
 // Same expressions as above for everything that is computed, hence the same bits.
-PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h) {
+PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h, const float* lut = nullptr) {
     const PrimRec p = sc.prims[h.primitive_index];
     const MatRec* mp = sc.materials + (p.info & PT_MATERIAL_INDEX_MASK);
     const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));
-    const V4 e = unpack_unorm4x8(fac.z);                                                 // material.glsl:50
+    const V4 e = unpack_unorm4x8(fac.z, lut);                                            // material.glsl:50
     V3 emissive = v3(e.x, e.y, e.z);
     if ((fac.w >> 2) & 1u) {                                                             // :51-53
         const V3 c = v3(1.0f - h.b1 - h.b2, h.b1, h.b2);
@@ -388,7 +394,7 @@ PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h) {
         TexRec tex;
         tex.texels = reinterpret_cast<const uint32_t*>(((uint64_t)w.y << 32) | w.x);
         tex.width = w.z; tex.height = w.w;
-        const V4 t = sample_texture(tex, uv);
+        const V4 t = sample_texture(tex, uv, lut);
         emissive = emissive * v3(t.x, t.y, t.z);
     }
     return emissive;
