@@ -252,6 +252,9 @@ int pt_camera_pack(const PtCameraState* camera, uint32_t frame_count, PtCamera* 
 /* ------------------------------------------------------------------ RaytracingPass
  * init    src/RaytracingPass.zig:87-200  (scene upload, BLAS/TLAS build -> GPU BVH8 builder) */
 int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer** out);
+/* RaytracingPass.init as the reference calls it, with a scene PATH (RaytracingPass.zig:87-103: Scene.load, upload,
+ * `defer scene.deinit()`): pt_scene_load + pt_create + pt_scene_free in one call.  Loader errors keep their Zig names. */
+int pt_create_from_gltf(const char* scene_path, const PtRenderConfig* config, PtRenderer** out);
 /* frames in flight (the reference: one command buffer + fence per swapchain image, src/main.zig:209-217,255-259): a second
  * frame context over the SAME device scene and acceleration structures -- own stream, path state, image and
  * read-back pipeline.  `parent` must outlive it and owns the scene (pt_set_instance_transforms goes to the parent,

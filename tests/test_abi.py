@@ -121,3 +121,15 @@ def test_new_round_one_entry_points_reject_null_arguments():
     assert L.pt_debug_bvh_digest(None, None) == -1
     assert L.pt_read_rgba32f_overlapped(None, None) == -1
     assert C.sizeof(b200pt.PtCameraState) == 26 * 4 and C.sizeof(b200pt.PtInput) == 20
+
+
+def test_create_from_gltf_surfaces_loader_errors_with_zig_names(tmp_path):
+    """pt_create_from_gltf = Scene.load + init: the loader's error wins, no renderer is returned."""
+    with pytest.raises(b200pt.PtError) as e:
+        b200pt.Renderer.from_gltf(str(tmp_path / "missing.glb"), 64, 64)
+    assert e.value.name == "IoError"
+    (tmp_path / "scene.obj").write_text("o")
+    with pytest.raises(b200pt.PtError) as e:
+        b200pt.Renderer.from_gltf(str(tmp_path / "scene.obj"), 64, 64)
+    assert e.value.name == "InvalidFileExtension"
+    assert b200pt.lib().pt_create_from_gltf(None, None, None) == -1

@@ -527,3 +527,18 @@ def test_sibling_context_shares_the_scene_and_keeps_two_frames_in_flight():
     with pytest.raises(b200pt.PtError):
         b.set_instance_transforms(np.eye(4, dtype=np.float32).reshape(1, 16))     # the scene belongs to the parent
     b.deinit(); a.deinit()
+
+
+def test_create_from_gltf_equals_load_then_create(tmp_path):
+    sb = S.cornell(1234)
+    cwd = os.getcwd(); os.chdir(tmp_path)
+    try:
+        path = sb.write_gltf(str(tmp_path), "cornell", glb=True)
+    finally:
+        os.chdir(cwd)
+    a = b200pt.Renderer.from_gltf(path, 96, 64, 2, 3)
+    b = b200pt.Renderer(sb.pack(), 96, 64, 2, 3)
+    cam = S.camera_default(96, 64, 1)
+    a.record(cam); b.record(cam); a.sync(); b.sync()
+    assert bits_equal(a.image(), b.image()).all() and all((x == y).all() for x, y in zip(a.ids(), b.ids()))
+    a.deinit(); b.deinit()

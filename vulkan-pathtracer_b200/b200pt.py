@@ -111,6 +111,7 @@ def lib():
         L.pt_camera_update.argtypes = [C.POINTER(PtCameraState), C.POINTER(PtInput)]
         L.pt_camera_update_aspect_ratio.argtypes = [C.POINTER(PtCameraState), C.c_float]
         L.pt_camera_pack.argtypes = [C.POINTER(PtCameraState), C.c_uint32, C.POINTER(PtCamera)]
+        L.pt_create_from_gltf.argtypes = [C.c_char_p, C.POINTER(PtRenderConfig), C.POINTER(C.c_void_p)]
         L.pt_create_sibling.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.pt_debug_bvh_digest.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 6)]
         L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
@@ -201,6 +202,18 @@ class Renderer:
         w, h = C.c_uint32(), C.c_uint32()
         check(lib().pt_render_extent(self.handle, C.byref(w), C.byref(h)))
         self.width, self.height = w.value, h.value
+
+    @classmethod
+    def from_gltf(cls, path, width=1920, height=1080, num_samples=1, num_bounces=2, divider=1, device=0, flags=0):
+        """RaytracingPass.init with a scene path (RaytracingPass.zig:87-103)."""
+        self = cls.__new__(cls)
+        self.handle = C.c_void_p()
+        self.cfg = PtRenderConfig(width, height, num_samples, num_bounces, divider, device, 0, 1, PT_PARTITION_NONE, flags)
+        check(lib().pt_create_from_gltf(os.fsencode(path), C.byref(self.cfg), C.byref(self.handle)))
+        w, h = C.c_uint32(), C.c_uint32()
+        check(lib().pt_render_extent(self.handle, C.byref(w), C.byref(h)))
+        self.width, self.height = w.value, h.value
+        return self
 
     def sibling(self):
         """A second frame context over the same device scene (frames in flight, main.zig:209-217,255-259): own stream,

@@ -380,6 +380,22 @@ int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer
     return PT_OK;
 }
 
+// RaytracingPass.init(..., scene_path, ...) (RaytracingPass.zig:87-103): load, upload, drop the host scene.
+int pt_create_from_gltf(const char* scene_path, const PtRenderConfig* config, PtRenderer** out) {
+    PT_REQUIRE(scene_path && config && out, "pt_create_from_gltf: null argument");
+    *out = nullptr;
+    PtScene* scene = nullptr;
+    int rc = pt_scene_load(scene_path, &scene);                 // Scene.load, :102
+    if (rc != PT_OK) return rc;
+    PtSceneDesc desc;
+    rc = pt_scene_desc(scene, &desc);
+    if (rc == PT_OK) rc = pt_create(&desc, config, out);
+    const std::string keep = g_last_error;
+    pt_scene_free(scene);                                       // defer scene.deinit(), :103
+    if (rc != PT_OK) g_last_error = keep;
+    return rc;
+}
+
 // A second frame context over the same device scene: its own stream, path state, image and read-back pipeline,
 // sharing scene data and acceleration structures with `parent` (which must outlive it).  Alternating pt_render
 // between a renderer and its sibling keeps two frames in flight -- the reference does the same with one command
