@@ -258,7 +258,8 @@ int pt_create_from_gltf(const char* scene_path, const PtRenderConfig* config, Pt
 /* frames in flight (the reference: one command buffer + fence per swapchain image, src/main.zig:209-217,255-259): a second
  * frame context over the SAME device scene and acceleration structures -- own stream, path state, image and
  * read-back pipeline.  `parent` must outlive it and owns the scene (pt_set_instance_transforms goes to the parent,
- * with no frame in flight on either).  Alternate pt_render between the two to overlap consecutive frames. */
+ * with no frame in flight on either; the sibling picks the new top level up at its next pt_render).  pt_resize
+ * applies to one context at a time.  Alternate pt_render between the two to overlap consecutive frames. */
 int pt_create_sibling(PtRenderer* parent, PtRenderer** out);
 /* deinit  src/RaytracingPass.zig:202-222 */
 void pt_destroy(PtRenderer* r);

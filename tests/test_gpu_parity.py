@@ -526,6 +526,12 @@ def test_sibling_context_shares_the_scene_and_keeps_two_frames_in_flight():
     assert not hits_mismatch(a.trace(rays), b.trace(rays)).any()
     with pytest.raises(b200pt.PtError):
         b.set_instance_transforms(np.eye(4, dtype=np.float32).reshape(1, 16))     # the scene belongs to the parent
+    # the parent moves its (single, identity) instance: the sibling follows at its next frame
+    T = np.eye(4, dtype=np.float32); T[0, 3] = 0.75; T[2, 3] = -0.5
+    a.set_instance_transforms(T.reshape(1, 16))
+    cam = S.camera_default(W, H, 5)
+    a.record(cam); b.record(cam); a.sync(); b.sync()
+    assert bits_equal(a.image(), b.image()).all() and not bits_equal(a.image(), want[0]).all()
     b.deinit(); a.deinit()
 
 

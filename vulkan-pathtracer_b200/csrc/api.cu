@@ -70,6 +70,7 @@ struct PtRenderer {
     uint32_t* d_cursor = nullptr;
     bool peer_root = false;   // pt_ipc_export_image was called: other ranks store their tiles into d_image
     bool owns_scene = true;   // false for a sibling (pt_create_sibling): scene + BVH belong to the parent
+    PtRenderer* parent = nullptr;   // sibling: where the current DeviceScene is read from (the parent may rebuild its top level)
 };
 
 namespace {
@@ -407,7 +408,7 @@ int pt_create_sibling(PtRenderer* parent, PtRenderer** out) {
     PT_REQUIRE(parent->owns_scene, "pt_create_sibling: the parent must be a renderer made by pt_create");
     PT_CUDA_CHECK(cudaSetDevice(parent->device));
     PtRenderer* r = new PtRenderer();
-    r->cfg = parent->cfg; r->device = parent->device; r->num_sms = parent->num_sms; r->owns_scene = false;
+    r->cfg = parent->cfg; r->device = parent->device; r->num_sms = parent->num_sms; r->owns_scene = false; r->parent = parent;
     r->d_blob = parent->d_blob; r->d_prims = parent->d_prims; r->d_materials = parent->d_materials; r->d_textures = parent->d_textures;
     r->d_instances_raw = parent->d_instances_raw; r->d_instances = parent->d_instances;
     r->bvh = parent->bvh; r->scene = parent->scene; r->num_triangles = parent->num_triangles; r->trace_mode = parent->trace_mode;
@@ -425,6 +426,7 @@ int pt_create_sibling(PtRenderer* parent, PtRenderer** out) {
 void pt_destroy(PtRenderer* r) { destroy_impl(r); }
 
 static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, TraceMode mode) {
+    if (r->parent) { r->scene = r->parent->scene; r->bvh.tlas2_count = r->parent->bvh.tlas2_count; }   // follow pt_set_instance_transforms on the parent
     PathBuffers& pb = r->pb;
     FrameParams fp;
     fp.cam = *camera;
@@ -667,6 +669,7 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
     PT_REQUIRE(n < 0xFFFFFF00ull, "pt_trace_rays: too many rays");
     if (n == 0) return PT_OK;
     PT_CUDA_CHECK(cudaSetDevice(r->device));
+    if (r->parent) r->scene = r->parent->scene;
     RayRec* d_rays = nullptr; HitRec* d_hits = nullptr; float4* d_setup = nullptr;
     int rc;
     if ((rc = dev_alloc(&d_rays, n)) != PT_OK) return rc;
