@@ -262,7 +262,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     if ((rc = dev_alloc(&r->d_instances_raw, inst.size())) != PT_OK) return rc;
     if (!inst.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_instances_raw, inst.data(), inst.size() * sizeof(PtInstance), cudaMemcpyHostToDevice, r->stream));
     // acceleration structures (createBlases + Tlas.init)
-    if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, (r->cfg.flags & PT_FLAG_BVH_PLOC) != 0, r->stream, &r->bvh)) != PT_OK) return rc;
+    if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, r->cfg.flags & (PT_FLAG_BVH_PLOC | PT_FLAG_BVH_SAH | PT_FLAG_BVH_OPTIMAL_COLLAPSE), r->stream, &r->bvh)) != PT_OK) return rc;
     r->h_instances = inst;
     if ((rc = dev_alloc(&r->d_instances, inst.size())) != PT_OK) return rc;
     if ((rc = upload_instance_records(r)) != PT_OK) return rc;

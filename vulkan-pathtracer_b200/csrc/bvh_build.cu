@@ -39,6 +39,14 @@ __device__ __forceinline__ void atomic_max_f(float* a, float v) {
     else atomicMin(reinterpret_cast<unsigned int*>(a), __float_as_uint(v));
 }
 
+}  // namespace
+}  // namespace pt
+
+#include "bvh_sah.cuh"   // opt-in stages: binned-SAH hierarchy, cost table of the optimal collapse
+
+namespace pt {
+namespace {
+
 __global__ void k_init_bounds(float* b) {
     if (threadIdx.x < 3) b[threadIdx.x] = 3.0e38f;
     else if (threadIdx.x < 6) b[threadIdx.x] = -3.0e38f;
@@ -424,6 +432,7 @@ struct CollapseArgs {
     const float* leaf_lo;       // source leaf boxes
     const float* leaf_hi;
     uint32_t max_leaf;          // 3 for a BLAS (triangles per leaf slot), 1 for the TLAS
+    const uint8_t* dp;          // decisions of k_collapse_dp (8 per binary node), or nullptr: greedy surface-area expansion
     uint32_t pack_below;        // subtrees with at most this many leaves become ONE leaf-only node (0 = off; needs
                                 // contiguous leaf ranges, i.e. the Morton radix tree)
     // outputs
@@ -443,7 +452,7 @@ struct CollapseArgs {
     uint32_t* overflow;
 };
 
-struct CChild { uint32_t ref, count; float lo[3], hi[3]; uint32_t first; };   // first: sorted index of a packed run, else ~0
+struct CChild { uint32_t ref, count; float lo[3], hi[3]; uint32_t first; bool leaf; };   // first: sorted index of a packed run, else ~0
 
 __device__ __forceinline__ CChild load_child(const CollapseArgs& a, uint32_t ref) {
     CChild c;
@@ -460,6 +469,7 @@ __device__ __forceinline__ CChild load_child(const CollapseArgs& a, uint32_t ref
         uint2 r = a.range[ref];
         c.count = r.y - r.x + 1;
     }
+    c.leaf = (ref & 0x80000000u) || c.count <= a.max_leaf;   // greedy rule; the optimal collapse overrides it
     return c;
 }
 
@@ -474,16 +484,43 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
     const uint32_t b2 = a.wq2[w], b8 = a.wq8[w];
     CChild ch[8];
     int cnt = 0;
-    {
+    const bool optimal = a.dp != nullptr && a.nodes2[b2].right != 0xFFFFFFFFu;
+    if (optimal) {
+        // follow k_collapse_dp: the node's 8 slots are split D[0] : 8 - D[0] between the two subtrees, and a subtree
+        // that was given i slots either stays one slot (leaf or inner wide node) or hands k : i - k to its children
+        struct { uint32_t ref; int i; } st[16];
+        int sp = 0;
+        const Bvh2Node& n = a.nodes2[b2];
+        const int k8 = a.dp[8 * (size_t)b2];
+        st[sp++] = {n.right, 8 - k8};
+        st[sp++] = {n.left, k8};
+        while (sp && cnt < 8) {
+            const uint32_t ref = st[sp - 1].ref;
+            int i = st[sp - 1].i;
+            --sp;
+            if (ref & 0x80000000u) { ch[cnt++] = load_child(a, ref); continue; }
+            const uint8_t* d = a.dp + 8 * (size_t)ref;
+            while (i >= 2 && d[i] == 0) --i;
+            if (i <= 1) {
+                CChild c = load_child(a, ref);
+                c.leaf = d[1] == 0;
+                ch[cnt++] = c;
+                continue;
+            }
+            const Bvh2Node& m = a.nodes2[ref];
+            st[sp++] = {m.right, i - (int)d[i]};
+            st[sp++] = {m.left, (int)d[i]};
+        }
+    } else {
         const Bvh2Node& n = a.nodes2[b2];
         ch[cnt++] = load_child(a, n.left);
         if (n.right != 0xFFFFFFFFu) ch[cnt++] = load_child(a, n.right);
     }
     // greedy surface-area expansion up to 8 children
-    while (cnt < 8) {
+    while (!optimal && cnt < 8) {
         int best = -1; float best_a = -1.0f;
         for (int c = 0; c < cnt; ++c) {
-            if ((ch[c].ref & 0x80000000u) || ch[c].count <= a.max_leaf) continue;
+            if (ch[c].leaf) continue;
             float ar = half_area(ch[c]);
             if (ar > best_a) { best_a = ar; best = c; }
         }
@@ -497,16 +534,16 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
     // one node (<= 8 slots of <= max_leaf leaves), the leftover inner children would become tiny nodes with two
     // or three slots each -- a full node test per ray for very little culling.  Pack the subtree instead: its
     // leaves are a contiguous run of the Morton order, cut into consecutive groups of max_leaf.
-    if (a.pack_below) {
+    if (a.pack_below && !optimal) {
         bool leftover = false;
-        for (int c = 0; c < cnt; ++c) leftover = leftover || (!(ch[c].ref & 0x80000000u) && ch[c].count > a.max_leaf);
+        for (int c = 0; c < cnt; ++c) leftover = leftover || !ch[c].leaf;
         const uint2 rg = a.range[b2];
         const uint32_t total = rg.y - rg.x + 1u;
         if (leftover && total <= a.pack_below) {
             cnt = 0;
             for (uint32_t j0 = rg.x; j0 <= rg.y; j0 += a.max_leaf) {
                 CChild c;
-                c.first = j0; c.count = min(a.max_leaf, rg.y - j0 + 1u); c.ref = 0x80000000u | j0;
+                c.first = j0; c.count = min(a.max_leaf, rg.y - j0 + 1u); c.ref = 0x80000000u | j0; c.leaf = true;
                 for (int k = 0; k < 3; ++k) { c.lo[k] = 3.0e38f; c.hi[k] = -3.0e38f; }
                 for (uint32_t t = 0; t < c.count; ++t) {
                     const size_t src = a.order[j0 + t];
@@ -560,8 +597,7 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
     for (int s = 0; s < 8; ++s) {
         int c = child_in_slot[s];
         if (c < 0) continue;
-        bool leaf = (ch[c].ref & 0x80000000u) || ch[c].count <= a.max_leaf;
-        if (leaf) n_leaf_items += ch[c].count; else n_inner++;
+        if (ch[c].leaf) n_leaf_items += ch[c].count; else n_inner++;
     }
     uint32_t child_base = n_inner ? atomicAdd(a.node_counter, n_inner) : 0u;
     uint32_t tri_base = n_leaf_items ? atomicAdd(a.tri_counter, n_leaf_items) : 0u;
@@ -592,8 +628,7 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
         }
         out.qlo_x[s] = ql[0]; out.qlo_y[s] = ql[1]; out.qlo_z[s] = ql[2];
         out.qhi_x[s] = qh[0]; out.qhi_y[s] = qh[1]; out.qhi_z[s] = qh[2];
-        bool leaf = (ch[c].ref & 0x80000000u) || ch[c].count <= a.max_leaf;
-        if (!leaf) {
+        if (!ch[c].leaf) {
             imask |= 1u << s;
             out.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
             cbits[s] = 1u << (24u + (uint32_t)s);
@@ -662,6 +697,14 @@ struct Scratch {
     uint32_t *cid[2] = {nullptr, nullptr}, *nn = nullptr, *keep = nullptr, *pos = nullptr;
     float *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
     bool lbvh = false;
+    // opt-in stages of bvh_sah.cuh
+    bool sah = false;             // binary hierarchy by top-down binned SAH instead of the Morton radix tree / PLOC
+    bool optimal = false;         // cost-optimal collapse (k_collapse_dp) instead of the greedy expansion
+    SahScratch sahs{};            // allocated when sah
+    float* dp_F = nullptr;        // 8 per binary node, allocated when optimal
+    uint8_t* dp_D = nullptr;
+    uint32_t* cur_parent = nullptr;   // parent links of the tree just built (Karras layout), for k_collapse_dp
+    uint32_t sah_levels = 0;
     uint32_t capacity = 0;        // entries of wq2 / wq8
     uint32_t pack_below = 0;      // CollapseArgs::pack_below for BLASes (measured slower on C2 / C4: off)
     uint32_t max_leaf = 2;        // triangles per BLAS leaf slot (format limit 3; measured 1 / 2 / 3 on C2: 1.438 / 1.406 /
@@ -673,6 +716,9 @@ struct Scratch {
         cudaFree(tmp_tris); cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(bounds); cudaFree(keys_in); cudaFree(keys_out);
         cudaFree(vals_in); cudaFree(vals_out); cudaFree(parent); cudaFree(flags); cudaFree(wq2); cudaFree(wq8);
         cudaFree(counters); cudaFree(range); cudaFree(prim_prefix); cudaFree(cub_temp);
+        cudaFree(sahs.idx[0]); cudaFree(sahs.idx[1]); cudaFree(sahs.seg[0]); cudaFree(sahs.seg[1]); cudaFree(sahs.segs[0]); cudaFree(sahs.segs[1]);
+        cudaFree(sahs.counters); cudaFree(sahs.cb); cudaFree(sahs.bins); cudaFree(sahs.flag); cudaFree(sahs.scan);
+        cudaFree(dp_F); cudaFree(dp_D);
     }
 };
 
@@ -683,7 +729,7 @@ int build_tree(Scratch& s, uint32_t n, Bvh2Node* nodes2_out, cudaStream_t st) {
     if (n == 1) {
         // vals_out[0] == 0
         k_single_leaf<<<1, 1, 0, st>>>(s.leaf_lo, s.leaf_hi, nodes2_out, s.range);
-    } else if (!s.lbvh) {
+    } else if (!s.lbvh && !s.sah) {
         uint32_t* counter = s.counters + 6;     // [6] nodes created, [7] clusters left
         PT_CUDA_CHECK(cudaMemsetAsync(counter, 0, 8, st));
         k_ploc_init<<<blocks_for(n), kThreads, 0, st>>>(n, s.vals_out, s.leaf_lo, s.leaf_hi, s.cid[0], s.clo[0], s.chi[0]);
@@ -706,7 +752,16 @@ int build_tree(Scratch& s, uint32_t n, Bvh2Node* nodes2_out, cudaStream_t st) {
         }
     } else {
         PT_CUDA_CHECK(cudaMemsetAsync(s.flags, 0, sizeof(uint32_t) * n, st));
-        k_karras<<<blocks_for(n - 1), kThreads, 0, st>>>(s.keys_out, (int)n, nodes2_out, s.parent, s.range);
+        if (s.sah) {
+            // the Morton sort above is not needed by this stage (it orders the leaves itself); vals_out receives its order
+            const uint32_t* order = nullptr;
+            const int rc = build_tree_sah(s.sahs, n, s.leaf_lo, s.leaf_hi, nodes2_out, s.range, s.parent, &order, &s.sah_levels, st);
+            if (rc == 2) { set_error("binned-SAH build exceeded its level budget"); return PT_ERR_CUDA; }
+            if (rc != 0) { set_error(std::string("binned-SAH build: ") + cudaGetErrorString(cudaGetLastError())); return PT_ERR_CUDA; }
+            PT_CUDA_CHECK(cudaMemcpyAsync(s.vals_out, order, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st));
+        } else {
+            k_karras<<<blocks_for(n - 1), kThreads, 0, st>>>(s.keys_out, (int)n, nodes2_out, s.parent, s.range);
+        }
         k_refit<<<blocks_for(n), kThreads, 0, st>>>((int)n, s.vals_out, s.leaf_lo, s.leaf_hi, nodes2_out, s.parent, s.flags);
         uint32_t* changed = s.counters + 8;
         for (int pass = 0;; ++pass) {
@@ -726,6 +781,19 @@ int build_tree(Scratch& s, uint32_t n, Bvh2Node* nodes2_out, cudaStream_t st) {
 
 // level-synchronous collapse of the tree just built; returns the BVH8 root index
 int collapse_tree(Scratch& s, CollapseArgs a, uint32_t n, uint32_t* root_out, cudaStream_t st) {
+    a.dp = nullptr;
+    // The cost table needs parent links, which the Morton radix tree and the SAH stage record (PLOC does not).
+    if (s.optimal && n >= 2 && (s.lbvh || s.sah)) {
+        DpArgs d;
+        d.n = n; d.nodes = a.nodes2; d.range = a.range; d.parent = s.parent; d.order = a.order; d.leaf_lo = a.leaf_lo; d.leaf_hi = a.leaf_hi;
+        d.visit = s.flags; d.F = s.dp_F; d.D = s.dp_D; d.max_leaf = a.max_leaf;
+        // one node test costs what ~1.4 triangle tests cost in K-trace (profiles/r1_experiments.md: leaf-size sweeps)
+        d.c_node = 1.0f; d.c_tri = 0.7f;
+        PT_CUDA_CHECK(cudaMemsetAsync(s.flags, 0, sizeof(uint32_t) * n, st));
+        k_collapse_dp<<<blocks_for(n), kThreads, 0, st>>>(d);
+        PT_CUDA_CHECK(cudaGetLastError());
+        a.dp = s.dp_D;
+    }
     // allocate the root node
     uint32_t root;
     PT_CUDA_CHECK(cudaMemcpyAsync(&root, a.node_counter, 4, cudaMemcpyDeviceToHost, st));
@@ -757,7 +825,8 @@ namespace {
 #define PT_CU(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return PT_ERR_CUDA; } } while (0)
 
 // scratch for trees of up to L leaves (the caller releases it, also on failure)
-int alloc_scratch(Scratch& s, uint32_t L, size_t max_prims, bool use_ploc, cudaStream_t st) {
+int alloc_scratch(Scratch& s, uint32_t L, size_t max_prims, uint32_t builder_flags, cudaStream_t st) {
+    const bool use_ploc = (builder_flags & PT_FLAG_BVH_PLOC) != 0;
     PT_CU(cudaMalloc(&s.tmp_tris, sizeof(Bvh8Tri) * L));
     PT_CU(cudaMalloc(&s.leaf_lo, sizeof(float) * 3 * L)); PT_CU(cudaMalloc(&s.leaf_hi, sizeof(float) * 3 * L));
     PT_CU(cudaMalloc(&s.bounds, sizeof(float) * 8));
@@ -780,10 +849,30 @@ int alloc_scratch(Scratch& s, uint32_t L, size_t max_prims, bool use_ploc, cudaS
         s.lbvh = !(use_ploc || (e && e[0] == '1'));
         const char* pk = std::getenv("PT_BVH_PACK");    // A/B switch for tools/
         if (pk) s.pack_below = (uint32_t)std::atoi(pk);
+        const char* sh = std::getenv("PT_BVH_SAH");     // A/B switches for tools/; the API switches are PT_FLAG_BVH_SAH / _OPTIMAL_COLLAPSE
+        s.sah = (builder_flags & PT_FLAG_BVH_SAH) != 0 || (sh && sh[0] == '1');
+        const char* oc = std::getenv("PT_BVH_OPTCOLLAPSE");
+        s.optimal = (builder_flags & PT_FLAG_BVH_OPTIMAL_COLLAPSE) != 0 || (oc && oc[0] == '1');
         const char* ml = std::getenv("PT_BVH_MAXLEAF");
         if (ml) s.max_leaf = (uint32_t)std::max(1, std::min(3, std::atoi(ml)));
     }
-    if (!s.lbvh) {
+    if (s.sah) {
+        const size_t S = (size_t)L / 2 + 1;
+        for (int k = 0; k < 2; ++k) {
+            PT_CU(cudaMalloc(&s.sahs.idx[k], 4 * (size_t)L)); PT_CU(cudaMalloc(&s.sahs.seg[k], 4 * (size_t)L));
+            PT_CU(cudaMalloc(&s.sahs.segs[k], sizeof(SahSeg) * S));
+        }
+        PT_CU(cudaMalloc(&s.sahs.counters, 8)); PT_CU(cudaMemsetAsync(s.sahs.counters, 0, 8, st));
+        PT_CU(cudaMalloc(&s.sahs.cb, sizeof(float) * 6 * S));
+        PT_CU(cudaMalloc(&s.sahs.bins, sizeof(SahBin) * 3 * kSahBins * S));
+        PT_CU(cudaMalloc(&s.sahs.flag, 4 * (size_t)L)); PT_CU(cudaMalloc(&s.sahs.scan, 4 * (size_t)L));
+        s.sahs.scan_temp = s.cub_temp; s.sahs.scan_temp_bytes = s.cub_bytes;
+    }
+    if (s.optimal) {
+        PT_CU(cudaMalloc(&s.dp_F, sizeof(float) * 8 * (size_t)L));
+        PT_CU(cudaMalloc(&s.dp_D, 8 * (size_t)L));
+    }
+    if (!s.lbvh && !s.sah) {
         for (int k = 0; k < 2; ++k) {
             PT_CU(cudaMalloc(&s.cid[k], 4 * (size_t)L)); PT_CU(cudaMalloc(&s.clo[k], 12 * (size_t)L)); PT_CU(cudaMalloc(&s.chi[k], 12 * (size_t)L));
         }
@@ -841,7 +930,7 @@ int build_tlas(Scratch& s, SceneBvh* out, const PtInstance* d_instances, cudaStr
 
 int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::vector<PrimRec>& h_prims,
                     const std::vector<PtMesh>& meshes, const PtInstance* d_instances,
-                    const std::vector<PtInstance>& h_instances, bool use_ploc, cudaStream_t st, SceneBvh* out) {
+                    const std::vector<PtInstance>& h_instances, uint32_t builder_flags, cudaStream_t st, SceneBvh* out) {
     const size_t M = meshes.size();
     out->tri_off.assign(M, 0); out->tri_count.assign(M, 0); out->blas_root8.assign(M, kInvalidId);
     uint32_t total = 0, max_n = 1;
@@ -870,7 +959,7 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
     auto fail = [&](int code) { s.release(); cudaEventDestroy(ev0); cudaEventDestroy(ev1); return code; };
 #define PT_TRY(expr) do { rc = (expr); if (rc != PT_OK) return fail(rc); } while (0)
 #define PT_CU(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return fail(PT_ERR_CUDA); } } while (0)
-    PT_TRY(alloc_scratch(s, L, max_prims, use_ploc, st));
+    PT_TRY(alloc_scratch(s, L, max_prims, builder_flags, st));
     s.capacity = L + 8;
 
     const size_t cap_nodes = (size_t)total + M + NI + 8;
@@ -928,7 +1017,7 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
     PT_CU(cudaMemcpyAsync(&out->tlas_node_base, node_counter, 4, cudaMemcpyDeviceToHost, st));
     PT_CU(cudaStreamSynchronize(st));
     out->valid_inst = valid_inst;
-    out->use_ploc = !s.lbvh;
+    out->builder_flags = builder_flags;
     PT_TRY(build_tlas(s, out, d_instances, st));
     PT_CU(cudaMemcpyAsync(&out->num_nodes8, node_counter, 4, cudaMemcpyDeviceToHost, st));
     PT_CU(cudaEventRecord(ev1, st));
@@ -953,7 +1042,7 @@ int rebuild_tlas(SceneBvh* bvh, const PtInstance* d_instances, cudaStream_t st, 
     cudaEvent_t ev0, ev1;
     PT_CUDA_CHECK(cudaEventCreate(&ev0)); PT_CUDA_CHECK(cudaEventCreate(&ev1));
     Scratch s;
-    int rc = alloc_scratch(s, NI, 1, bvh->use_ploc, st);
+    int rc = alloc_scratch(s, NI, 1, bvh->builder_flags, st);
     s.capacity = NI + 8;
     if (rc == PT_OK) {
         cudaEventRecord(ev0, st);

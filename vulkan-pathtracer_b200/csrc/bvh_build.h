@@ -31,7 +31,7 @@ struct SceneBvh {
     // TLAS rebuild state (animated instances)
     uint32_t tlas_node_base = 0;        // first BVH8 node of the TLAS (everything below belongs to BLASes)
     std::vector<uint32_t> valid_inst;   // instances that reference a non-empty mesh
-    bool use_ploc = false;
+    uint32_t builder_flags = 0;         // PT_FLAG_BVH_* the scene was built with (a TLAS rebuild uses the same stages)
     float ms_build = 0.0f;
     uint32_t refit_repairs = 0;         // nodes corrected by the refit verification (expected 0)
 
@@ -41,7 +41,7 @@ struct SceneBvh {
 // d_* are device pointers, h_* their host copies.
 int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::vector<PrimRec>& h_prims,
                     const std::vector<PtMesh>& meshes, const PtInstance* d_instances,
-                    const std::vector<PtInstance>& h_instances, bool use_ploc, cudaStream_t stream, SceneBvh* out);
+                    const std::vector<PtInstance>& h_instances, uint32_t builder_flags, cudaStream_t stream, SceneBvh* out);
 
 // Rebuilds the top level in place after the transforms in d_instances changed (mesh indices unchanged).
 int rebuild_tlas(SceneBvh* bvh, const PtInstance* d_instances, cudaStream_t stream, float* ms_out);
