@@ -136,7 +136,7 @@ enum {
                                              material that share one extent are interleaved per texel on the device */
     PT_FLAG_BVH_PLOC = 1u << 4,           /* build the binary hierarchy by locally-ordered clustering (PLOC) instead of
                                              the Morton radix tree (LBVH): slower build, better trees for irregular meshes */
-    PT_FLAG_BVH_SAH = 1u << 6,            /* build the binary hierarchy top-down by binned SAH on the GPU (16 bins x 3 axes
+    PT_FLAG_BVH_SAH = 1u << 6,            /* build the binary hierarchy top-down by binned SAH on the GPU (32 bins x 3 axes
                                              per segment, level-synchronous; csrc/bvh_sah.cuh).  Takes precedence over PLOC */
     PT_FLAG_BVH_OPTIMAL_COLLAPSE = 1u << 7 /* BVH2 -> BVH8 by the cost-optimal collapse (dynamic programme of Ylitie et al.
                                              2017) instead of the greedy surface-area expansion; LBVH and SAH hierarchies */

@@ -268,7 +268,7 @@ static std::vector<uint8_t> dp_kernel(const Bvh2& t, uint32_t max_leaf, float c_
 }
 
 // ------------------------------------------------------------------ wide tree
-struct WChild { Box qb; int inner; uint32_t tri_first, tri_cnt; int slot; };
+struct WChild { Box qb, xb; int inner; uint32_t tri_first, tri_cnt; int slot; };   // quantised and exact box
 struct WNode { int nc; WChild c[8]; };
 struct Wide { std::vector<WNode> nodes; std::vector<uint32_t> tris; double sah = 0.0; };
 
@@ -322,6 +322,7 @@ static void emit_node(const Bvh2& t, Wide& w, int widx, std::vector<CC>& ch, std
     for (int c = 0; c < cnt; ++c) {
         WChild& o = out.c[c];
         o.slot = slot_of[c];
+        o.xb = ch[c].b;
         for (int k = 0; k < 3; ++k) {
             float fl = std::floor((ch[c].b.lo[k] - p[k]) / scale[k] - dq);
             float fh = std::ceil((ch[c].b.hi[k] - p[k]) / scale[k] + dq);
@@ -495,28 +496,38 @@ static bool tri_hit(uint32_t tr, const Ray& r, float tmax, float& t_out) {
 
 struct Counts { uint64_t nodes = 0, tris = 0, rays = 0; };
 
+// diagnostics (what-if bounds, not buildable variants): exact child boxes instead of the 8-bit grid; inner children
+// visited by true entry distance instead of octant priority; a popped node skipped when the closest hit found since
+// it was pushed already lies in front of its entry point (needs the entry distance on the stack)
+static bool g_exact_boxes = false, g_sort_by_distance = false, g_cull_on_pop = false;
+
 static HitR walk(const Wide& w, const Ray& r, Counts& cnt) {
     HitR best{1e32f, 0xFFFFFFFFu};
     float id[3]; uint32_t rs = 0;
     for (int k = 0; k < 3; ++k) { id[k] = 1.0f / (r.d[k] == 0.0f ? 1e-30f : r.d[k]); if (id[k] >= 0.0f) rs |= 1u << k; }
-    int stack[512]; int sp = 0;
-    stack[sp++] = 0;
+    int stack[512]; float stack_t[512]; int sp = 0;
+    stack_t[sp] = 0.0f; stack[sp++] = 0;
     cnt.rays++;
     while (sp) {
-        const WNode& n = w.nodes[stack[--sp]];
+        --sp;
+        if (g_cull_on_pop && stack_t[sp] > best.t) continue;
+        const WNode& n = w.nodes[stack[sp]];
         cnt.nodes++;
         const float tlim = std::fmin(r.tmax, best.t);
-        struct { int prio, node; } inner[8]; int ni = 0;
+        struct { int prio, node; float tn; } inner[8]; int ni = 0;
         uint32_t leaf_hit = 0;
         for (int c = 0; c < n.nc; ++c) {
-            const Box& b = n.c[c].qb;
+            const Box& b = g_exact_boxes ? n.c[c].xb : n.c[c].qb;
             float tn = r.tmin, tf = tlim;
             for (int k = 0; k < 3; ++k) {
                 float a = (b.lo[k] - r.o[k]) * id[k], bb = (b.hi[k] - r.o[k]) * id[k];
                 tn = std::fmax(tn, std::fmin(a, bb)); tf = std::fmin(tf, std::fmax(a, bb));
             }
             if (!(tn <= tf * 1.0000019f)) continue;
-            if (n.c[c].inner >= 0) { inner[ni].prio = (int)((uint32_t)n.c[c].slot ^ rs); inner[ni].node = n.c[c].inner; ni++; }
+            if (n.c[c].inner >= 0) {
+                inner[ni].prio = g_sort_by_distance ? -(int)(std::fmin(tn, 1.0e6f) * 1024.0f) : (int)((uint32_t)n.c[c].slot ^ rs);
+                inner[ni].node = n.c[c].inner; inner[ni].tn = tn; ni++;
+            }
             else leaf_hit |= 1u << c;
         }
         // the node's hit triangles first (all of them, against the ray's own tmax like test_triangle)
@@ -531,7 +542,7 @@ static HitR walk(const Wide& w, const Ray& r, Counts& cnt) {
         }
         // inner children: highest priority is visited first, so it is pushed last
         for (int i = 1; i < ni; ++i) { auto e = inner[i]; int j = i - 1; while (j >= 0 && inner[j].prio > e.prio) { inner[j + 1] = inner[j]; --j; } inner[j + 1] = e; }
-        for (int k = 0; k < ni; ++k) stack[sp++] = inner[k].node;
+        for (int k = 0; k < ni; ++k) { stack_t[sp] = inner[k].tn; stack[sp++] = inner[k].node; }
     }
     return best;
 }
@@ -638,6 +649,24 @@ int main(int argc, char** argv) {
                     (double)cp.nodes / cp.rays, (double)cp.tris / cp.rays, (double)cb.nodes / std::max<uint64_t>(1, cb.rays),
                     (double)cb.tris / std::max<uint64_t>(1, cb.rays), an, at, an + 0.7 * at, mism ? "  HIT MISMATCH" : "");
         if (mism) std::printf("   (%zu rays with a different closest hit)\n", mism);
+    }
+    // what-if bounds on the last SAH + optimal variant
+    {
+        const Wide* w = nullptr; const char* nm = nullptr;
+        for (auto& v : vs) if (std::strstr(v.name, "bvh_sah.cuh + k_collapse_dp, 2")) { w = &v.w; nm = v.name; }
+        if (w) {
+            std::printf("\nwhat-if bounds on '%s' (not buildable variants):\n", nm);
+            for (int mode = 0; mode < 4; ++mode) {
+                g_exact_boxes = mode == 1; g_sort_by_distance = mode == 2; g_cull_on_pop = mode == 3;
+                Counts c;
+                for (auto& r : primary) walk(*w, r, c);
+                for (auto& r : bounce) walk(*w, r, c);
+                const double an = (double)c.nodes / c.rays, at = (double)c.tris / c.rays;
+                std::printf("  %-52s %7.2f %6.2f %7.2f\n", mode == 0 ? "as shipped (8-bit boxes, octant order)" : mode == 1 ? "exact child boxes" :
+                            mode == 2 ? "inner children by entry distance" : "popped node skipped when behind the closest hit", an, at, an + 0.7 * at);
+            }
+            g_exact_boxes = g_sort_by_distance = g_cull_on_pop = false;
+        }
     }
     return 0;
 }

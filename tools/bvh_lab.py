@@ -49,7 +49,8 @@ def main():
     os.makedirs(build, exist_ok=True)
     exe = os.path.join(build, "bvh_lab")
     src = os.path.join(HERE, "bvh_lab.cpp")
-    if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(src):
+    deps = [src, os.path.join(ROOT, "vulkan-pathtracer_b200", "csrc", "bvh_sah.cuh")]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-Wall", "-Wno-unused-function", "-o", exe, src])
     path = os.path.join(build, f"{which}_tris.bin")
     with open(path, "wb") as f:

@@ -1,7 +1,7 @@
 // bvh_sah.cuh — two opt-in builder stages (included by bvh_build.cu; replaces nothing by default):
 //
 //  (1) build_tree_sah(): top-down binned-SAH binary hierarchy on the GPU, level-synchronous.  Every level
-//      bins the centroids of all live segments at once (16 bins x 3 axes per segment, float min/max + count
+//      bins the centroids of all live segments at once (32 bins x 3 axes per segment, float min/max + count
 //      atomics), one thread per segment sweeps its bins for the cheapest split, and a stable partition
 //      (flags -> exclusive scan -> scatter) moves the leaves.  Leaves end up in hierarchy order, every node
 //      covers a contiguous run of them, node ids are derived from the split position (the gap between two
@@ -65,7 +65,7 @@ static inline int sah_scan(const uint32_t* in, uint32_t* out, uint32_t n, cudaSt
 }
 #endif
 
-constexpr int kSahBins = 16;
+constexpr int kSahBins = 32;     // 16 bins cost C5 5 % more traversal work than 32 in the CPU model (tools/bvh_lab)
 constexpr uint32_t kSahNone = 0xFFFFFFFFu;
 constexpr uint32_t kSahNoSplit = 3u;     // SahSeg::axis: leaves stay where they are, cut at `mid`
 
