@@ -272,6 +272,7 @@ struct WChild { Box qb, xb; int inner; uint32_t tri_first, tri_cnt; int slot; };
 struct WNode { int nc; WChild c[8]; };
 struct Wide { std::vector<WNode> nodes; std::vector<uint32_t> tris; double sah = 0.0; };
 
+static bool g_optimal_slots = false;
 struct CC { uint32_t ref; uint32_t count; Box b; bool leaf; };
 
 static void leaves_under(const Bvh2& t, uint32_t ref, std::vector<uint32_t>& out) {
@@ -300,8 +301,33 @@ static void emit_node(const Bvh2& t, Wide& w, int widx, std::vector<CC>& ch, std
         p[k] = nb.lo[k] - 0.5f * scale[k];
     }
     int slot_of[8]; bool slot_used[8] = {false}, assigned[8] = {false};
+    if (g_optimal_slots) {
+        // exact assignment: maximise the sum of dot(child centroid - node centroid, octant direction) over all injective
+        // child -> slot maps (dynamic programme over slot subsets, children in order)
+        const float ncx[3] = {0.5f * (nb.lo[0] + nb.hi[0]), 0.5f * (nb.lo[1] + nb.hi[1]), 0.5f * (nb.lo[2] + nb.hi[2])};
+        float score[8][8];
+        for (int c = 0; c < cnt; ++c) {
+            float d[3];
+            for (int k = 0; k < 3; ++k) d[k] = 0.5f * (ch[c].b.lo[k] + ch[c].b.hi[k]) - ncx[k];
+            for (int sl = 0; sl < 8; ++sl) score[c][sl] = ((sl & 1) ? d[0] : -d[0]) + ((sl & 2) ? d[1] : -d[1]) + ((sl & 4) ? d[2] : -d[2]);
+        }
+        static float best[9][256]; static int8_t pick[9][256];
+        for (int m = 0; m < 256; ++m) best[cnt][m] = 0.0f;
+        for (int c = cnt - 1; c >= 0; --c)
+            for (int m = 0; m < 256; ++m) {
+                best[c][m] = -3.0e38f; pick[c][m] = -1;
+                if (__builtin_popcount(m) != c) continue;
+                for (int sl = 0; sl < 8; ++sl) {
+                    if (m >> sl & 1) continue;
+                    const float v = score[c][sl] + best[c + 1][m | (1 << sl)];
+                    if (v > best[c][m]) { best[c][m] = v; pick[c][m] = (int8_t)sl; }
+                }
+            }
+        int m = 0;
+        for (int c = 0; c < cnt; ++c) { slot_of[c] = pick[c][m]; m |= 1 << slot_of[c]; assigned[c] = true; }
+    }
     const float nc[3] = {0.5f * (nb.lo[0] + nb.hi[0]), 0.5f * (nb.lo[1] + nb.hi[1]), 0.5f * (nb.lo[2] + nb.hi[2])};
-    for (int it = 0; it < cnt; ++it) {
+    for (int it = 0; it < cnt && !g_optimal_slots; ++it) {
         float best = -3.0e38f; int bc = -1, bs = -1;
         for (int c = 0; c < cnt; ++c) {
             if (assigned[c]) continue;
@@ -604,6 +630,13 @@ int main(int argc, char** argv) {
     vs.push_back({"bvh_sah.cuh + k_collapse_dp, 2 tris/slot", collapse_optimal(ks, 2, 1.0f, 0.7f, true)});
     vs.push_back({"bvh_sah.cuh + k_collapse_dp, 3 tris/slot", collapse_optimal(ks, 3, 1.0f, 0.7f, true)});
     vs.push_back({"LBVH + k_collapse_dp, 2 tris/slot", collapse_optimal(lb, 2, 1.0f, 0.7f, true)});
+    vs.push_back({"bvh_sah.cuh + dp, c_tri 0.4", collapse_optimal(ks, 2, 1.0f, 0.4f)});
+    vs.push_back({"bvh_sah.cuh + dp, c_tri 1.0", collapse_optimal(ks, 2, 1.0f, 1.0f)});
+    vs.push_back({"bvh_sah.cuh + dp, c_tri 1.5", collapse_optimal(ks, 2, 1.0f, 1.5f)});
+    g_optimal_slots = true;
+    vs.push_back({"bvh_sah.cuh + dp, exact slot assignment", collapse_optimal(ks, 2, 1.0f, 0.7f)});
+    vs.push_back({"LBVH + greedy, exact slot assignment", collapse_greedy(lb, 2)});
+    g_optimal_slots = false;
 
     // bounce rays from the first variant's primary hits (the closest hit does not depend on the hierarchy)
     std::vector<Ray> bounce;

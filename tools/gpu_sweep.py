@@ -47,6 +47,27 @@ def main():
         print(f"trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays   "
               f"bvh8 nodes {st.bvh_nodes}  per ray: {nn/max(nr,1):.2f} nodes {nt/max(nr,1):.2f} tris  build {st.ms_build:.2f} ms")
         r.deinit()
+    elif what == "builders":
+        # A/B of the binary-hierarchy stages and collapses: per-ray counts (pt_count_traversal), kernel times, and the image
+        # must be bit-identical to the default build (the closest-hit rule does not depend on the hierarchy)
+        ref = None
+        for flags, label in ((0, "LBVH + greedy (default)"), (128, "LBVH + optimal collapse"), (64, "SAH + greedy"), (192, "SAH + optimal collapse"),
+                             (16, "PLOC + greedy")):
+            try:
+                r = b200pt.Renderer(ps, W, H, spp, seg, flags=flags)
+            except Exception as e:   # an opt-in stage that fails must not hide the others
+                print(f"{label:26s}: build failed: {e}")
+                continue
+            tr, sh, ot, rays = measure(r, W, H)
+            st = r.stats()
+            nn, nt, nr = r.count_traversal()
+            r.record(S.camera_default(W, H, 0)); r.sync()
+            img = r.image()
+            if ref is None: ref = img
+            same = np.array_equal(ref.view(np.uint32), img.view(np.uint32))
+            print(f"{label:26s}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  bvh8 nodes {st.bvh_nodes}  "
+                  f"per ray: {nn/max(nr,1):.2f} nodes {nt/max(nr,1):.2f} tris  build {st.ms_build:.2f} ms  same_image={same}")
+            r.deinit()
     elif what == "modes":
         for flags, label in ((0, "persistent"), (8, "walker"), (2, "bvh2")):
             r = b200pt.Renderer(ps, W, H, spp, seg, flags=flags)

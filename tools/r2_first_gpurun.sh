@@ -1,0 +1,12 @@
+#!/bin/bash
+# First gpurun of round 2 (from the repo root): the opt-in builder stages of csrc/bvh_sah.cuh have only run as a serial CPU
+# model so far.  (1) the default suite must still be green, (2) the gated hardware tests of the new stages, (3) A/B of the
+# builders on C2 / C4 / C5 with per-ray counts, kernel times and image identity, (4) bench lines with and without them.
+#   gpurun --timeout 1500 -- 'bash tools/r2_first_gpurun.sh > gpurun_out/r2a_first.log 2>&1'
+O=gpurun_out; mkdir -p $O
+python -m pytest tests -m gpu -x -q > $O/r2a_pytest_gpu.log 2>&1; tail -3 $O/r2a_pytest_gpu.log
+B200PT_TEST_UNVERIFIED=1 timeout 900 python -m pytest tests/test_zz_gpu_bvh_sah.py -q > $O/r2a_pytest_sah.log 2>&1; tail -15 $O/r2a_pytest_sah.log
+for c in c2 c4 c5 c1; do echo "== $c"; timeout 600 python tools/gpu_sweep.py builders $c; done 2>&1 | tee $O/r2a_builders.txt
+python bench.py --no-cpu-baseline > $O/r2a_bench_c2_default.json 2> /dev/null
+python bench.py --no-cpu-baseline --flags 192 > $O/r2a_bench_c2_sah_opt.json 2> $O/r2a_bench_c2_sah_opt.err
+for f in $O/r2a_bench_c2_*.json; do echo $f; cut -c1-300 $f; echo; done
