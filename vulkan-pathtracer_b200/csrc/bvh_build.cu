@@ -30,11 +30,14 @@ constexpr int kThreads = 256;
 inline int blocks_for(size_t n) { return (int)((n + kThreads - 1) / kThreads); }
 
 // ------------------------------------------------------------------ float atomics on bounds
+// (v + 0.0f turns -0.0f into +0.0f: as an int, -0.0f is INT_MIN and would win every signed minimum)
 __device__ __forceinline__ void atomic_min_f(float* a, float v) {
+    v += 0.0f;
     if (v >= 0.0f) atomicMin(reinterpret_cast<int*>(a), __float_as_int(v));
     else atomicMax(reinterpret_cast<unsigned int*>(a), __float_as_uint(v));
 }
 __device__ __forceinline__ void atomic_max_f(float* a, float v) {
+    v += 0.0f;
     if (v >= 0.0f) atomicMax(reinterpret_cast<int*>(a), __float_as_int(v));
     else atomicMin(reinterpret_cast<unsigned int*>(a), __float_as_uint(v));
 }
