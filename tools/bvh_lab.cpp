@@ -520,7 +520,8 @@ static bool tri_hit(uint32_t tr, const Ray& r, float tmax, float& t_out) {
     return true;
 }
 
-struct Counts { uint64_t nodes = 0, tris = 0, rays = 0; };
+struct Counts { uint64_t nodes = 0, tris = 0, rays = 0, big_tris = 0; };
+static float g_big_area = 3.0e38f;   // triangle tests on leaves with a larger box half-area are counted separately
 
 // diagnostics (what-if bounds, not buildable variants): exact child boxes instead of the 8-bit grid; inner children
 // visited by true entry distance instead of octant priority; a popped node skipped when the closest hit found since
@@ -561,6 +562,7 @@ static HitR walk(const Wide& w, const Ray& r, Counts& cnt) {
             if (!(leaf_hit >> c & 1u)) continue;
             for (uint32_t k = 0; k < n.c[c].tri_cnt; ++k) {
                 cnt.tris++;
+                if (g_leaf[w.tris[n.c[c].tri_first + k]].half_area() > g_big_area) cnt.big_tris++;
                 float tt;
                 const uint32_t tr = w.tris[n.c[c].tri_first + k];
                 if (tri_hit(tr, r, r.tmax, tt) && (tt < best.t || (tt == best.t && tr < best.tri))) { best.t = tt; best.tri = tr; }
@@ -689,6 +691,22 @@ int main(int argc, char** argv) {
         for (auto& v : vs) if (std::strstr(v.name, "bvh_sah.cuh + k_collapse_dp, 2")) { w = &v.w; nm = v.name; }
         if (w) {
             std::printf("\nwhat-if bounds on '%s' (not buildable variants):\n", nm);
+            {
+                // how many triangle tests go to the few large triangles (candidates for pre-splitting)
+                std::vector<float> areas(g_n);
+                for (uint32_t i = 0; i < g_n; ++i) areas[i] = g_leaf[i].half_area();
+                std::vector<float> sorted = areas;
+                std::sort(sorted.begin(), sorted.end());
+                for (double q : {0.90, 0.99, 0.999}) {
+                    g_big_area = sorted[(size_t)(q * (g_n - 1))];
+                    Counts c;
+                    for (auto& r : primary) walk(*w, r, c);
+                    for (auto& r : bounce) walk(*w, r, c);
+                    std::printf("  triangle tests on the largest %.1f %% of triangles (box half-area > %.3g): %.2f of %.2f per ray\n", 100.0 * (1.0 - q),
+                                g_big_area, (double)c.big_tris / c.rays, (double)c.tris / c.rays);
+                }
+                g_big_area = 3.0e38f;
+            }
             for (int mode = 0; mode < 4; ++mode) {
                 g_exact_boxes = mode == 1; g_sort_by_distance = mode == 2; g_cull_on_pop = mode == 3;
                 Counts c;

@@ -1,0 +1,6 @@
+#!/bin/sh
+# Run HERE (no GPU needed) before tools/r2_first_gpurun.sh: A/B kernel variants for tools/gpu_variants.sh.
+set -e
+cd "$(dirname "$0")/.."
+for k in 4 8 16; do sh tools/build_variant.sh refill$k -DPT_TRACE_REFILL_MIN=$k; done
+ls -la vulkan-pathtracer_b200/variants/

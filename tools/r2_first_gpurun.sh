@@ -10,3 +10,7 @@ for c in c2 c4 c5 c1; do echo "== $c"; timeout 600 python tools/gpu_sweep.py bui
 python bench.py --no-cpu-baseline > $O/r2a_bench_c2_default.json 2> /dev/null
 python bench.py --no-cpu-baseline --flags 192 > $O/r2a_bench_c2_sah_opt.json 2> $O/r2a_bench_c2_sah_opt.err
 for f in $O/r2a_bench_c2_*.json; do echo $f; cut -c1-300 $f; echo; done
+# kernel variants built beforehand by tools/r2_build_variants.sh (refill threshold of K-trace's dynamic fetch)
+if ls vulkan-pathtracer_b200/variants/*.so > /dev/null 2>&1; then
+  for c in c2 c4; do echo "== variants $c"; python tools/gpu_sweep.py one $c | tail -1; sh tools/gpu_variants.sh $c; done 2>&1 | tee $O/r2a_variants.txt
+fi

@@ -173,7 +173,14 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     for (;;) {
         // ---- dynamic fetch: refill idle lanes from the warp's chunk
         const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+#ifdef PT_TRACE_REFILL_MIN
+        // A/B variant (tools/build_variant.sh refill8 -DPT_TRACE_REFILL_MIN=8): refill only once that many lanes are idle.
+        // The fetch path runs at ~3.6 lanes and is 5-7 % of K-trace's warp instructions (profiles/r1g_ncu_lines_trace.txt);
+        // waiting trades it against idle lanes in the node phase.  Results do not depend on it.
+        if (__popc(idle) >= PT_TRACE_REFILL_MIN && !exhausted) {
+#else
         if (idle != 0u && !exhausted) {
+#endif
             if (w_next == w_end) {
                 uint32_t base = 0;
                 if (lane == 0) base = atomicAdd(io.cursor, chunk);
