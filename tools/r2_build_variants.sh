@@ -3,4 +3,5 @@
 set -e
 cd "$(dirname "$0")/.."
 for k in 4 8 16; do sh tools/build_variant.sh refill$k -DPT_TRACE_REFILL_MIN=$k; done
+sh tools/build_variant.sh latebary -DPT_TRACE_LATE_BARY
 ls -la vulkan-pathtracer_b200/variants/

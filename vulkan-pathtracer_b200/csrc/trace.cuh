@@ -37,8 +37,9 @@ PT_D RayPre ray_precompute(V3 d) {
     return r;
 }
 
-PT_D bool intersect_tri(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2, float tmin, float tmax, float& t_out,
-                        float& b1, float& b2) {
+// hit distance + the unnormalised barycentrics (b1 = V / det, b2 = W / det)
+PT_D bool intersect_tri_raw(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2, float tmin, float tmax, float& t_out,
+                            float& V_out, float& W_out, float& det_out) {
     const V3 A = v3(p0.x, p0.y, p0.z) - o, B = v3(p1.x, p1.y, p1.z) - o, C = v3(p2.x, p2.y, p2.z) - o;
     const float Ax = (rp.m0x * A.x + rp.m0y * A.y) + rp.m0z * A.z, Ay = (rp.m1x * A.x + rp.m1y * A.y) + rp.m1z * A.z;
     const float Bx = (rp.m0x * B.x + rp.m0y * B.y) + rp.m0z * B.z, By = (rp.m1x * B.x + rp.m1y * B.y) + rp.m1z * B.z;
@@ -60,7 +61,15 @@ PT_D bool intersect_tri(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2,
     const float T = U * Az + V * Bz + W * Cz;
     const float t = T / det;
     if (!(t > tmin && t < tmax)) return false;
-    t_out = t; b1 = V / det; b2 = W / det;
+    t_out = t; V_out = V; W_out = W; det_out = det;
+    return true;
+}
+
+PT_D bool intersect_tri(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2, float tmin, float tmax, float& t_out,
+                        float& b1, float& b2) {
+    float V, W, det;
+    if (!intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t_out, V, W, det)) return false;
+    b1 = V / det; b2 = W / det;
     return true;
 }
 
@@ -80,12 +89,21 @@ PT_D void test_triangle(const Bvh8Tri* __restrict__ tris, uint32_t idx, V3 o, co
                         uint32_t inst, Hit& best) {
     const float4* q = reinterpret_cast<const float4*>(tris + idx);
     const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
-    float t, b1, b2;
     // tmax stays the ray's tmax: candidates with t == best.t must reach the tie-break
+#ifdef PT_TRACE_LATE_BARY
+    // A/B variant: the two barycentric divisions only for candidates that replace the closest hit (same operands, same bits)
+    float t, V, W, det;
+    if (intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t, V, W, det)) {
+        const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
+        if (hit_better(t, inst, prim, tri, best)) { best.t = t; best.b1 = V / det; best.b2 = W / det; best.inst = inst; best.prim = prim; best.tri = tri; }
+    }
+#else
+    float t, b1, b2;
     if (intersect_tri(o, rp, p0, p1, p2, tmin, tmax, t, b1, b2)) {
         const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
         if (hit_better(t, inst, prim, tri, best)) { best.t = t; best.b1 = b1; best.b2 = b2; best.inst = inst; best.prim = prim; best.tri = tri; }
     }
+#endif
 }
 
 // ------------------------------------------------------------------ ray frame for box tests
