@@ -4,4 +4,5 @@ set -e
 cd "$(dirname "$0")/.."
 for k in 4 8 16; do sh tools/build_variant.sh refill$k -DPT_TRACE_REFILL_MIN=$k; done
 sh tools/build_variant.sh latebary -DPT_TRACE_LATE_BARY
+for k in 8 12; do sh tools/build_variant.sh smem$k -DPT_TRACE_SMEM_STACK=$k; done
 ls -la vulkan-pathtracer_b200/variants/
