@@ -41,6 +41,16 @@ PT_HD float comp(V3 a, int k) { return k == 0 ? a.x : (k == 1 ? a.y : a.z); }
 // correctly rounded fp32 sin / cos: evaluated in double, rounded once
 PT_D float sin_cr(float x) { return (float)sin((double)x); }
 PT_D float cos_cr(float x) { return (float)cos((double)x); }
+#ifdef PT_SHADE_SINCOS
+// A/B variant: one double-precision sincos() (one argument reduction) instead of sin() + cos().  Its double results may
+// differ from sin() / cos() in the last place, which changes the rounded float only when the double lands within that
+// distance of a float rounding boundary -- the parity tests decide whether it ships.
+PT_D void sincos_cr(float x, float& s, float& c) {
+    double sd, cd;
+    sincos((double)x, &sd, &cd);
+    s = (float)sd; c = (float)cd;
+}
+#endif
 
 // row-major 3x3
 struct M3 { float m[3][3]; };
