@@ -34,6 +34,7 @@ def run(lab, tris, tmp_path, name, size=96):
     assert p.returncode == 0, p.stdout + p.stderr
     assert "HIT MISMATCH" not in p.stdout, p.stdout
     assert "0 differing decisions" in p.stdout, p.stdout
+    assert "dp_cover vs the lab's recursion: 0 differing" in p.stdout, p.stdout
     return p.stdout
 
 

@@ -482,13 +482,34 @@ static Wide collapse_optimal(const Bvh2& t, uint32_t max_leaf, float c_node, flo
         cover(t.nodes[ref].left, k, out);
         cover(t.nodes[ref].right, i - k, out);
     };
+    std::vector<pt::Bvh2Node> kn;
+    std::vector<uint8_t> KD;
+    if (kernel_table) {   // k_collapse's own child selection (pt::dp_cover) on the kernel's table
+        kn.resize(N); KD.resize(8 * N);
+        for (size_t n = 0; n < N; ++n) {
+            kn[n].left = t.nodes[n].left; kn[n].right = t.nodes[n].right;
+            KD[8 * n] = D8[n];
+            for (int i = 1; i <= 7; ++i) KD[8 * n + i] = D[8 * n + i];
+        }
+    }
+    size_t cover_diff = 0;
     while (head < todo.size()) {
         auto [b2, widx] = todo[head++];
         std::vector<CC> ch;
         cover(t.nodes[b2].left, D8[b2], ch);
         cover(t.nodes[b2].right, 8 - D8[b2], ch);
+        if (kernel_table) {
+            uint32_t refs[8]; bool leaf[8];
+            const int cnt = pt::dp_cover(KD.data(), kn.data(), b2, refs, leaf);
+            bool same = cnt == (int)ch.size();
+            for (int c = 0; same && c < cnt; ++c) same = refs[c] == ch[c].ref && leaf[c] == ch[c].leaf;
+            if (!same) cover_diff++;
+            ch.clear();
+            for (int c = 0; c < cnt; ++c) { CC x; x.ref = refs[c]; x.count = ref_count(t, refs[c]); x.b = ref_box(t, refs[c]); x.leaf = leaf[c]; ch.push_back(x); }
+        }
         emit_node(t, w, widx, ch, todo);
     }
+    if (kernel_table) std::printf("dp_cover vs the lab's recursion: %zu differing wide nodes of %zu\n", cover_diff, w.nodes.size());
     return w;
 }
 

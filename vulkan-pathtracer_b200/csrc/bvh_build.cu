@@ -489,31 +489,9 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
     int cnt = 0;
     const bool optimal = a.dp != nullptr && a.nodes2[b2].right != 0xFFFFFFFFu;
     if (optimal) {
-        // follow k_collapse_dp: the node's 8 slots are split D[0] : 8 - D[0] between the two subtrees, and a subtree
-        // that was given i slots either stays one slot (leaf or inner wide node) or hands k : i - k to its children
-        struct { uint32_t ref; int i; } st[16];
-        int sp = 0;
-        const Bvh2Node& n = a.nodes2[b2];
-        const int k8 = a.dp[8 * (size_t)b2];
-        st[sp++] = {n.right, 8 - k8};
-        st[sp++] = {n.left, k8};
-        while (sp && cnt < 8) {
-            const uint32_t ref = st[sp - 1].ref;
-            int i = st[sp - 1].i;
-            --sp;
-            if (ref & 0x80000000u) { ch[cnt++] = load_child(a, ref); continue; }
-            const uint8_t* d = a.dp + 8 * (size_t)ref;
-            while (i >= 2 && d[i] == 0) --i;
-            if (i <= 1) {
-                CChild c = load_child(a, ref);
-                c.leaf = d[1] == 0;
-                ch[cnt++] = c;
-                continue;
-            }
-            const Bvh2Node& m = a.nodes2[ref];
-            st[sp++] = {m.right, i - (int)d[i]};
-            st[sp++] = {m.left, (int)d[i]};
-        }
+        uint32_t refs[8]; bool is_leaf[8];
+        cnt = dp_cover(a.dp, a.nodes2, b2, refs, is_leaf);      // bvh_sah.cuh
+        for (int c = 0; c < cnt; ++c) { ch[c] = load_child(a, refs[c]); ch[c].leaf = is_leaf[c]; }
     } else {
         const Bvh2Node& n = a.nodes2[b2];
         ch[cnt++] = load_child(a, n.left);

@@ -381,4 +381,28 @@ PT_KERNEL k_collapse_dp(DpArgs a) {
     }
 }
 
+// Children of the wide node rooted at binary node b2 under the decisions D of k_collapse_dp: the node's 8 slots are split
+// D[0] : 8 - D[0] between its two subtrees, and a subtree that was given i slots either stays one slot (a leaf, or an
+// inner wide node of its own) or hands k : i - k to its children.  refs[] receives binary child references left to
+// right, is_leaf[] whether the slot is a leaf; returns the number of slots used (<= 8).  Used by k_collapse.
+PT_DEV int dp_cover(const uint8_t* D, const Bvh2Node* nodes, uint32_t b2, uint32_t* refs, bool* is_leaf) {
+    uint32_t st_ref[16]; int st_i[16];
+    int sp = 0, cnt = 0;
+    const int k8 = D[8 * (size_t)b2];
+    st_ref[sp] = nodes[b2].right; st_i[sp] = 8 - k8; ++sp;
+    st_ref[sp] = nodes[b2].left; st_i[sp] = k8; ++sp;
+    while (sp && cnt < 8) {
+        --sp;
+        const uint32_t ref = st_ref[sp];
+        int i = st_i[sp];
+        if (ref & 0x80000000u) { refs[cnt] = ref; is_leaf[cnt] = true; ++cnt; continue; }
+        const uint8_t* d = D + 8 * (size_t)ref;
+        while (i >= 2 && d[i] == 0) --i;
+        if (i <= 1) { refs[cnt] = ref; is_leaf[cnt] = d[1] == 0; ++cnt; continue; }
+        st_ref[sp] = nodes[ref].right; st_i[sp] = i - (int)d[i]; ++sp;
+        st_ref[sp] = nodes[ref].left; st_i[sp] = (int)d[i]; ++sp;
+    }
+    return cnt;
+}
+
 }  // namespace pt
