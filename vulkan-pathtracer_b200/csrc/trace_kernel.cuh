@@ -284,6 +284,18 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             const uint32_t hits = node_test_fast(sc.nodes, sc.node_bits, node, f, tmin, fminf(tmax, best.t), bias, perm_lut, cb, tb, im);
             G = make_uint2(cb, (hits & 0xFF000000u) | im);
             T = make_uint2(tb, hits & 0x00FFFFFFu);
+#ifdef PT_TRACE_PREFETCH
+            // A/B variant: while this node's triangles are tested, bring in the inner child that will be visited next
+            // (same slot arithmetic as the top of phase 2).  Aimed at the tail of a launch, where a lone ray per warp pays
+            // a full L2 round trip per step.
+            if (T.y != 0u && (G.y & 0xFF000000u) != 0u) {
+                const uint32_t k2 = 31u - (uint32_t)__clz(G.y);
+                const uint32_t s2 = (k2 - 24u) ^ f.rs;
+                const uint32_t nx = G.x + __popc(G.y & 0xffu & ((1u << s2) - 1u));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.nodes + nx));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.node_bits + 2 * (size_t)nx));
+            }
+#endif
         }
     }
 }
