@@ -164,6 +164,9 @@ def main():
                     help="N>1: frames = rank r renders frame_count r, r+N, ... (weak scaling, default); tiles = every rank renders "
                          "its interleaved 32x8 tiles of the SAME frame + NCCL reduce (strong scaling); tiles-peer = same, but owned "
                          "pixels are stored straight into rank 0's image over NVLink (CUDA IPC), one 4-byte NCCL all-reduce as fence")
+    ap.add_argument("--tile-shares", type=int, default=1,
+                    help="tiles partitions only: contexts per GPU, each rendering a share of the rank's tiles on its own stream "
+                         "(pt_create_sibling_part), so that the tail of one share's wavefronts overlaps the others' work")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--single-frame-in-flight", action="store_true", help="e2e leg without the sibling frame context")
@@ -194,10 +197,13 @@ def main():
     _, W, H, spp, seg = WORKLOADS[name]
     ps, t_gen = build_scene(name)
     t0 = time.time()
-    tiles = world > 1 and args.partition != "frames"
+    tiles = (world > 1 or args.tile_shares > 1) and args.partition != "frames"
     peer = world > 1 and args.partition == "tiles-peer"
-    r = b200pt.Renderer(ps, W, H, spp, seg, device=local_rank, flags=args.flags, rank=rank if tiles else 0, world=world if tiles else 1,
+    shares = max(1, args.tile_shares) if (tiles and args.partition == "tiles") else 1
+    r = b200pt.Renderer(ps, W, H, spp, seg, device=local_rank, flags=args.flags, rank=rank if tiles else 0, world=world * shares if tiles else 1,
                         partition=b200pt.PT_PARTITION_TILES if tiles else b200pt.PT_PARTITION_NONE)
+    # further shares of this rank's tiles: share k of rank r owns the tiles `tile % (K * world) == k * world + r`
+    parts = [r.sibling_part(k * world + rank, world * shares) for k in range(1, shares)]
     t_create = time.time() - t0
     if peer:
         # rank 0 exports its image buffer; the others map it and their K-shade writes owned pixels into it
@@ -219,6 +225,8 @@ def main():
     sp = C.c_void_p(stream.cuda_stream)
     assert sp.value, "expected a non-default CUDA stream"
     img_t = torch.as_tensor(DevArray(r.device_image_ptr(), (H, W, 4)), device=f"cuda:{local_rank}")
+    part_img = [torch.as_tensor(DevArray(p.device_image_ptr(), (H, W, 4)), device=f"cuda:{local_rank}") for p in parts]
+    part_streams = [torch.cuda.Stream() for _ in parts]
     flush = None if args.no_l2_flush else torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")
     total_steps = args.warmup + args.steps
 
@@ -238,9 +246,18 @@ def main():
         else:
             dist.reduce(img_t, dst=0, op=dist.ReduceOp.SUM)
 
-    def step(i):
-        r.record(S.camera_default(W, H, frame_of(i)), sp)
+    def render_frame(cam):
+        for p, ps_ in zip(parts, part_streams):     # the other shares start with this one and join before the reduce
+            ps_.wait_stream(stream)
+            p.record(cam, C.c_void_p(ps_.cuda_stream))
+        r.record(cam, sp)
+        for ps_, im in zip(part_streams, part_img):
+            stream.wait_stream(ps_)
+            img_t.add_(im)                           # disjoint tiles, zero elsewhere
         combine()
+
+    def step(i):
+        render_frame(S.camera_default(W, H, frame_of(i)))
 
     # ---------------- device-timed region: inputs resident, per-step CUDA events, L2 flushed between steps
     r.set_profiling(True)
@@ -264,6 +281,10 @@ def main():
         trace_ms += s.ms_trace; shade_ms += s.ms_shade; other_ms += s.ms_other
         launches += s.kernel_launches
         rays_local += s.rays_traced
+        for p in parts:
+            sp_ = p.stats()
+            launches += sp_.kernel_launches + 1     # + the add of its image
+            rays_local += sp_.rays_traced
     barrier()
     clocks = sampler.stop()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
@@ -284,7 +305,7 @@ def main():
     # One GPU: two frames in flight, like the reference's one command buffer + fence per swapchain image
     # (main.zig:209-217,255-259): a sibling context shares the device scene and has its own stream, path state,
     # image and pinned destination, so the tail of frame k overlaps ray generation + primary traversal of frame k+1.
-    in_flight = 2 if (world == 1 and not args.single_frame_in_flight) else 1
+    in_flight = 2 if (world == 1 and not parts and not args.single_frame_in_flight) else 1
     if in_flight == 2:
         ctx = [r, r.sibling()]
         hosts = [host_img, torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)]
@@ -304,10 +325,9 @@ def main():
         ctx[0].sync(); ctx[1].sync()
     for k in range(args.steps if in_flight == 1 else 0):
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
-        r.record(cam, sp)
-        combine()
+        render_frame(cam)
         if rank == 0:
-            if peer:    # the fence below is ordered on `sp`, so the copy has to be too
+            if peer or parts:    # ordered on `sp` (the fence below, or the sum of the tile shares, is)    # the fence below is ordered on `sp`, so the copy has to be too
                 b200pt.check(b200pt.lib().pt_read_rgba32f_async(r.handle, host_img.data_ptr(), sp))
             else:       # copy of frame k overlaps ray generation + primary traversal of frame k+1
                 b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, host_img.data_ptr()))
@@ -371,9 +391,9 @@ def main():
         line = {"metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
-                "config": {"workload": WORKLOAD_DESC[name], "partition": ("none" if world == 1 else "frames (rank r renders frame_count r, r+N, ...) + NCCL reduce(sum) to rank 0" if not tiles
+                "config": {"workload": WORKLOAD_DESC[name], "partition": ("none" if (world == 1 and not tiles) else "frames (rank r renders frame_count r, r+N, ...) + NCCL reduce(sum) to rank 0" if not tiles
                                          else "interleaved 32x8 tiles of one frame, peer stores into rank 0 over NVLink + 4-byte NCCL fence" if peer
-                                         else "interleaved 32x8 tiles of one frame + NCCL reduce(sum) to rank 0"),
+                                         else "interleaved 32x8 tiles of one frame + NCCL reduce(sum) to rank 0") + (f", {shares} tile shares per GPU on own streams" if shares > 1 else ""),
                            "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed; per-step path state (365 MB) exceeds L2",
                            "triangles": int(st0.num_triangles), "bvh8_nodes": int(st0.bvh_nodes), "bvh_build_ms": st0.ms_build,
                            "scene_gen_s": t_gen, "create_s": t_create},
@@ -385,6 +405,8 @@ def main():
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     if in_flight == 2:
         ctx[1].deinit()     # the sibling goes first: the scene belongs to r
+    for p in parts:
+        p.deinit()
     r.deinit()
     if world > 1:
         dist.destroy_process_group()

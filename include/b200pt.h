@@ -265,6 +265,11 @@ int pt_create_from_gltf(const char* scene_path, const PtRenderConfig* config, Pt
  * with no frame in flight on either; the sibling picks the new top level up at its next pt_render).  pt_resize
  * applies to one context at a time.  Alternate pt_render between the two to overlap consecutive frames. */
 int pt_create_sibling(PtRenderer* parent, PtRenderer** out);
+/* the same, but the new context renders the interleaved tiles `tile % world == rank` only (PT_PARTITION_TILES with its own
+ * rank / world, whatever the parent's): several contexts on ONE GPU, each with a share of the tiles and its own stream, so
+ * that the tail of one share's wavefront (its slowest rays, a few per warp) overlaps the other shares' work.  Images of
+ * the shares are disjoint and zero elsewhere: their sum is the frame.  With N GPUs use rank = k * N + gpu_rank, world = K * N. */
+int pt_create_sibling_part(PtRenderer* parent, int rank, int world, PtRenderer** out);
 /* deinit  src/RaytracingPass.zig:202-222 */
 void pt_destroy(PtRenderer* r);
 /* record  src/RaytracingPass.zig:520-675: enqueue one frame on `cuda_stream` (a cudaStream_t, or

@@ -120,6 +120,8 @@ def test_new_round_one_entry_points_reject_null_arguments():
     assert L.pt_set_instance_transforms(None, None, 0, None) == -1
     assert L.pt_debug_bvh_digest(None, None) == -1
     assert L.pt_read_rgba32f_overlapped(None, None) == -1
+    assert L.pt_create_sibling(None, None) == -1
+    assert L.pt_create_sibling_part(None, 0, 2, None) == -1
     assert C.sizeof(b200pt.PtCameraState) == 26 * 4 and C.sizeof(b200pt.PtInput) == 20
 
 

@@ -1,4 +1,5 @@
-"""GPU tests of the opt-in builder stages (PT_FLAG_BVH_SAH, PT_FLAG_BVH_OPTIMAL_COLLAPSE; csrc/bvh_sah.cuh).
+"""GPU tests of the opt-in builder stages (PT_FLAG_BVH_SAH, PT_FLAG_BVH_OPTIMAL_COLLAPSE; csrc/bvh_sah.cuh) and of
+pt_create_sibling_part (tile shares on one GPU).
 
 STATUS: these stages were written after round 1's GPU minutes were spent.  Their kernel bodies are checked on the CPU
 (tests/test_bvh_sah_model.py runs the same source serially) but they have NOT run on hardware yet, so the tests below
@@ -86,3 +87,28 @@ def test_sah_build_is_deterministic():
         r.deinit()
     if d[0] is not None:
         assert d[0] == d[1] == d[2]
+
+
+def test_tile_shares_on_one_gpu_sum_to_the_frame():
+    """pt_create_sibling_part: three contexts on one GPU, each with a third of the interleaved tiles and its own stream; their
+    images are disjoint and sum to the single-context frame bit for bit."""
+    ps = S.cornell().pack()
+    W, H = 200, 120
+    cam = S.camera_default(W, H, 3)
+    whole = b200pt.Renderer(ps, W, H, 2, 3)
+    whole.record(cam); whole.sync()
+    want = whole.image()
+    whole.deinit()
+    a = b200pt.Renderer(ps, W, H, 2, 3, rank=0, world=3, partition=b200pt.PT_PARTITION_TILES)
+    parts = [a, a.sibling_part(1, 3), a.sibling_part(2, 3)]
+    for p in parts:
+        p.record(cam)
+    for p in parts:
+        p.sync()
+    imgs = [p.image() for p in parts]
+    nz = sum((im != 0).any(axis=2).astype(np.int32) for im in imgs)
+    assert nz.max() <= 1, "tile shares overlap"
+    assert bits_equal(imgs[0] + imgs[1] + imgs[2], want).all()
+    for p in parts[:0:-1]:
+        p.deinit()
+    a.deinit()

@@ -14,3 +14,11 @@ for f in $O/r2a_bench_c2_*.json; do echo $f; cut -c1-300 $f; echo; done
 if ls vulkan-pathtracer_b200/variants/*.so > /dev/null 2>&1; then
   for c in c2 c4; do echo "== variants $c"; python tools/gpu_sweep.py one $c | tail -1; sh tools/gpu_variants.sh $c; done 2>&1 | tee $O/r2a_variants.txt
 fi
+# tile shares on one GPU (pt_create_sibling_part): does overlapping the wavefront tails of 2 / 4 shares pay?  C3 is where the
+# tails cost most (449 iterations per frame); C2 for the headline.  Compare ms_per_step.
+for sh in 2 4; do
+  python bench.py --workload c3 --steps 2 --warmup 3 --no-cpu-baseline --partition tiles --tile-shares $sh > $O/r2a_bench_c3_shares$sh.json 2> $O/r2a_bench_c3_shares$sh.err
+  python bench.py --no-cpu-baseline --partition tiles --tile-shares $sh > $O/r2a_bench_c2_shares$sh.json 2> $O/r2a_bench_c2_shares$sh.err
+done
+python bench.py --workload c3 --steps 2 --warmup 3 --no-cpu-baseline > $O/r2a_bench_c3_default.json 2> /dev/null
+for f in $O/r2a_bench_c3_*.json $O/r2a_bench_c2_shares*.json; do echo $f; cut -c1-200 $f; echo; done

@@ -114,6 +114,7 @@ def lib():
         L.pt_camera_pack.argtypes = [C.POINTER(PtCameraState), C.c_uint32, C.POINTER(PtCamera)]
         L.pt_create_from_gltf.argtypes = [C.c_char_p, C.POINTER(PtRenderConfig), C.POINTER(C.c_void_p)]
         L.pt_create_sibling.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.pt_create_sibling_part.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.pt_debug_bvh_digest.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 6)]
         L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
         L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
@@ -223,6 +224,16 @@ class Renderer:
         other.handle = C.c_void_p()
         other.cfg = self.cfg
         check(lib().pt_create_sibling(self.handle, C.byref(other.handle)))
+        other.width, other.height = self.width, self.height
+        return other
+
+    def sibling_part(self, rank, world):
+        """A further context on the same GPU that renders the interleaved tiles `tile % world == rank` only (own stream, path
+        state, zero-initialised image); the images of all shares sum to the frame.  Deinit it before this renderer."""
+        other = Renderer.__new__(Renderer)
+        other.handle = C.c_void_p()
+        other.cfg = self.cfg
+        check(lib().pt_create_sibling_part(self.handle, rank, world, C.byref(other.handle)))
         other.width, other.height = self.width, self.height
         return other
 

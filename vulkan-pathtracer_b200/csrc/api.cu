@@ -402,13 +402,29 @@ int pt_create_from_gltf(const char* scene_path, const PtRenderConfig* config, Pt
 // between a renderer and its sibling keeps two frames in flight -- the reference does the same with one command
 // buffer and fence per swapchain image (main.zig:209-217,255-259) -- so the tail of one frame's last wavefront
 // overlaps the next frame's ray generation and primary traversal.
+static int create_sibling_impl(PtRenderer* parent, const int* part, PtRenderer** out);
+
 int pt_create_sibling(PtRenderer* parent, PtRenderer** out) {
     PT_REQUIRE(parent && out, "pt_create_sibling: null argument");
+    return create_sibling_impl(parent, nullptr, out);
+}
+
+int pt_create_sibling_part(PtRenderer* parent, int rank, int world, PtRenderer** out) {
+    PT_REQUIRE(parent && out, "pt_create_sibling_part: null argument");
+    *out = nullptr;
+    PT_REQUIRE(world >= 1 && rank >= 0 && rank < world, "pt_create_sibling_part: invalid rank/world");
+    const int part[2] = {rank, world};
+    return create_sibling_impl(parent, part, out);
+}
+
+static int create_sibling_impl(PtRenderer* parent, const int* part, PtRenderer** out) {
     *out = nullptr;
     PT_REQUIRE(parent->owns_scene, "pt_create_sibling: the parent must be a renderer made by pt_create");
     PT_CUDA_CHECK(cudaSetDevice(parent->device));
     PtRenderer* r = new PtRenderer();
-    r->cfg = parent->cfg; r->device = parent->device; r->num_sms = parent->num_sms; r->owns_scene = false; r->parent = parent;
+    r->cfg = parent->cfg;
+    if (part) { r->cfg.partition = PT_PARTITION_TILES; r->cfg.rank = part[0]; r->cfg.world = part[1]; }
+    r->device = parent->device; r->num_sms = parent->num_sms; r->owns_scene = false; r->parent = parent;
     r->d_blob = parent->d_blob; r->d_prims = parent->d_prims; r->d_materials = parent->d_materials; r->d_textures = parent->d_textures;
     r->d_instances_raw = parent->d_instances_raw; r->d_instances = parent->d_instances;
     r->bvh = parent->bvh; r->scene = parent->scene; r->num_triangles = parent->num_triangles; r->trace_mode = parent->trace_mode;
