@@ -327,7 +327,7 @@ def main():
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
         render_frame(cam)
         if rank == 0:
-            if peer or parts:    # ordered on `sp` (the fence below, or the sum of the tile shares, is)    # the fence below is ordered on `sp`, so the copy has to be too
+            if peer or parts:    # the fence below / the sum of the tile shares is ordered on `sp`, so the copy has to be too
                 b200pt.check(b200pt.lib().pt_read_rgba32f_async(r.handle, host_img.data_ptr(), sp))
             else:       # copy of frame k overlaps ray generation + primary traversal of frame k+1
                 b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, host_img.data_ptr()))
