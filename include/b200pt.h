@@ -362,6 +362,10 @@ int pt_write_pfm(const char* path, const float* rgba, uint32_t width, uint32_t h
 int pt_write_exr(const char* path, const float* rgba, uint32_t width, uint32_t height);
 
 /* Library/device introspection. */
+/* measurement (SURVEY 8d "which roofline"): read bandwidth of a `bytes`-sized device buffer over `iters` coalesced passes;
+ * a buffer that fits the L2 gives the L2 read bandwidth that bounds the traversal working set, a large one HBM's.  Also
+ * returns the SM count (FP32 / issue peaks = SMs x 4 schedulers x clock). */
+int pt_debug_read_bandwidth(int device, size_t bytes, int iters, float* gb_per_s, int* num_sms);
 int pt_device_count(void);
 const char* pt_version(void);
 

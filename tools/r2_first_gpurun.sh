@@ -5,6 +5,7 @@
 #   gpurun --timeout 1500 -- 'bash tools/r2_first_gpurun.sh > gpurun_out/r2a_first.log 2>&1'
 O=gpurun_out; mkdir -p $O
 python -m pytest tests -m gpu -x -q > $O/r2a_pytest_gpu.log 2>&1; tail -3 $O/r2a_pytest_gpu.log
+python tools/gpu_peaks.py > $O/r2a_peaks.json 2> $O/r2a_peaks.err; cat $O/r2a_peaks.json
 B200PT_TEST_UNVERIFIED=1 timeout 900 python -m pytest tests/test_zz_gpu_bvh_sah.py -q > $O/r2a_pytest_sah.log 2>&1; tail -15 $O/r2a_pytest_sah.log
 for c in c2 c4 c5 c1; do echo "== $c"; timeout 600 python tools/gpu_sweep.py builders $c; done 2>&1 | tee $O/r2a_builders.txt
 python bench.py --no-cpu-baseline > $O/r2a_bench_c2_default.json 2> /dev/null

@@ -335,6 +335,15 @@ class Renderer:
         return n.value, t.value, r.value
 
 
+def read_bandwidth(nbytes, iters=50, device=0):
+    """(GB/s, SM count): read bandwidth of an nbytes device buffer (fits the L2 -> L2 bandwidth; large -> HBM)."""
+    g, n = C.c_float(0.0), C.c_int(0)
+    L = lib()
+    L.pt_debug_read_bandwidth.argtypes = [C.c_int, C.c_size_t, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    check(L.pt_debug_read_bandwidth(device, nbytes, iters, C.byref(g), C.byref(n)))
+    return g.value, n.value
+
+
 def debug_bsdf(N, V, kd, f0, rough, xi, device=0):
     """sample_brdf / get_brdf_density / brdf evaluated by the CUDA restatement."""
     n = len(rough)

@@ -865,6 +865,56 @@ int pt_debug_texture(int device, const uint8_t* rgba, uint32_t width, uint32_t h
     return PT_OK;
 }
 
+// ------------------------------------------------------------------ roofline denominators measured on the box
+// Coalesced 16-byte reads of a buffer, `iters` passes by a grid of 8 CTAs per SM: a buffer that fits the L2 (B200: 126 MB)
+// gives the L2 read bandwidth the traversal working set can at best be served at, a large one the HBM read
+// bandwidth.  The first pass of a small buffer comes from HBM: use iters >= 50.
+__global__ void __launch_bounds__(256) k_read_bandwidth(const uint4* __restrict__ buf, size_t n16, int iters, uint32_t* sink) {
+    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int it = 0; it < iters; ++it) {
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+            const uint4 v = __ldcg(buf + i);     // L2 only: the L1 must not serve repeated passes
+            acc.x ^= v.x; acc.y ^= v.y; acc.z ^= v.z; acc.w ^= v.w;
+        }
+    }
+    if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x9e3779b9u) *sink = 1u;   // keeps the loads alive
+}
+
+int pt_debug_read_bandwidth(int device, size_t bytes, int iters, float* gb_per_s, int* num_sms) {
+    PT_REQUIRE(gb_per_s && bytes >= 4096 && iters >= 1, "pt_debug_read_bandwidth: invalid argument");
+    int rc = debug_begin(device); if (rc != PT_OK) return rc;
+    cudaDeviceProp prop;
+    PT_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    if (num_sms) *num_sms = prop.multiProcessorCount;
+    const size_t n16 = bytes / 16;
+    uint4* buf = nullptr; uint32_t* sink = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaError_t e = cudaMalloc(&buf, n16 * 16);
+    if (e == cudaSuccess) e = cudaMalloc(&sink, 4);
+    if (e == cudaSuccess) e = cudaMemset(buf, 0x5a, n16 * 16);
+    if (e == cudaSuccess) e = cudaMemset(sink, 0, 4);
+    if (e == cudaSuccess) e = cudaEventCreate(&e0);
+    if (e == cudaSuccess) e = cudaEventCreate(&e1);
+    float ms = 0.0f;
+    if (e == cudaSuccess) {
+        const int grid = prop.multiProcessorCount * 8;
+        k_read_bandwidth<<<grid, 256>>>(buf, n16, 1, sink);            // warm-up: brings a small buffer into the L2
+        cudaEventRecord(e0);
+        k_read_bandwidth<<<grid, 256>>>(buf, n16, iters, sink);
+        cudaEventRecord(e1);
+        e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+        if (e == cudaSuccess) e = cudaGetLastError();
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaFree(buf); cudaFree(sink);
+    if (e != cudaSuccess) { set_error(std::string("pt_debug_read_bandwidth: ") + cudaGetErrorString(e)); return PT_ERR_CUDA; }
+    *gb_per_s = ms > 0.0f ? (float)((double)n16 * 16.0 * iters / (ms * 1e-3) / 1e9) : 0.0f;
+    return PT_OK;
+}
+
 int pt_set_option(const char* key, int value) {
     PT_REQUIRE(key, "pt_set_option: null key");
     if (set_option(key, value) != 0) { set_error(std::string("pt_set_option: unknown key ") + key); return PT_ERR_INVALID_ARGUMENT; }
