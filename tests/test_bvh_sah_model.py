@@ -66,3 +66,13 @@ def test_long_thin_outliers(lab, tmp_path):
     out = run(lab, np.concatenate([t, big]), str(tmp_path), "outliers")
     levels = [int(l.split(":")[1].split()[0]) for l in out.splitlines() if l.startswith("csrc/bvh_sah.cuh (serial model)")]
     assert levels and levels[0] < 96
+
+
+def test_every_small_leaf_count(lab, tmp_path):
+    """2 ... 48 leaves (every shape of the last levels: pairs, triples, runs that end in single leaves), a third of them
+    with duplicated triangles mixed in."""
+    for n in range(2, 49):
+        t = soup(100 + n, n, 1.0)
+        if n % 3 == 0:
+            t[n // 2:] = t[0]
+        run(lab, t, str(tmp_path), f"small{n}", size=24)
