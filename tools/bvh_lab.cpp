@@ -548,6 +548,7 @@ static float g_big_area = 3.0e38f;   // triangle tests on leaves with a larger b
 // visited by true entry distance instead of octant priority; a popped node skipped when the closest hit found since
 // it was pushed already lies in front of its entry point (needs the entry distance on the stack)
 static bool g_exact_boxes = false, g_sort_by_distance = false, g_cull_on_pop = false;
+static bool g_any_hit = false;   // stop at the first intersection found (what an occlusion query would cost)
 
 static HitR walk(const Wide& w, const Ray& r, Counts& cnt) {
     HitR best{1e32f, 0xFFFFFFFFu};
@@ -589,6 +590,7 @@ static HitR walk(const Wide& w, const Ray& r, Counts& cnt) {
                 if (tri_hit(tr, r, r.tmax, tt) && (tt < best.t || (tt == best.t && tr < best.tri))) { best.t = tt; best.tri = tr; }
             }
         }
+        if (g_any_hit && best.tri != 0xFFFFFFFFu) break;
         // inner children: highest priority is visited first, so it is pushed last
         for (int i = 1; i < ni; ++i) { auto e = inner[i]; int j = i - 1; while (j >= 0 && inner[j].prio > e.prio) { inner[j + 1] = inner[j]; --j; } inner[j + 1] = e; }
         for (int k = 0; k < ni; ++k) { stack_t[sp] = inner[k].tn; stack[sp++] = inner[k].node; }
@@ -738,6 +740,18 @@ int main(int argc, char** argv) {
                             mode == 2 ? "inner children by entry distance" : "popped node skipped when behind the closest hit", an, at, an + 0.7 * at);
             }
             g_exact_boxes = g_sort_by_distance = g_cull_on_pop = false;
+            {
+                // the last segment of a sample only adds the emission of what it hits (ray_gen.rgen:75-77) or the sky: with
+                // few emissive triangles it is an occlusion query plus a test of those triangles
+                Counts c0, c1;
+                for (auto& r : bounce) walk(*w, r, c0);
+                g_any_hit = true;
+                for (auto& r : bounce) walk(*w, r, c1);
+                g_any_hit = false;
+                std::printf("  bounce rays as closest-hit queries: %.2f nodes %.2f tris (%.2f units); as first-hit queries: %.2f nodes %.2f tris (%.2f units)\n",
+                            (double)c0.nodes / c0.rays, (double)c0.tris / c0.rays, ((double)c0.nodes + 0.7 * c0.tris) / c0.rays,
+                            (double)c1.nodes / c1.rays, (double)c1.tris / c1.rays, ((double)c1.nodes + 0.7 * c1.tris) / c1.rays);
+            }
         }
     }
     return 0;
