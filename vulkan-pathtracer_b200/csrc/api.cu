@@ -33,6 +33,7 @@ struct PtRenderer {
     cudaEvent_t ev_frame_done = nullptr, ev_copy_done = nullptr;
     bool copy_pending = false;
     // scene on the device
+    Bvh8Tri* d_emissive = nullptr;       // PT_OCCLUSION_LAST variant: the scene's emissive triangles (DeviceScene::emissive_tris)
     uint8_t* d_blob = nullptr;
     PrimRec* d_prims = nullptr;
     MatRec* d_materials = nullptr;
@@ -272,6 +273,42 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     sc.nodes2 = r->bvh.nodes2; sc.tris2 = r->bvh.tris2; sc.tlas2 = r->bvh.tlas2; sc.tlas_root = r->bvh.tlas_root8;
     sc.num_instances = (uint32_t)inst.size(); sc.num_prims = (uint32_t)prims.size();
     sc.num_materials = (uint32_t)s->num_materials; sc.num_textures = (uint32_t)s->num_textures;
+#ifdef PT_OCCLUSION_LAST
+    {
+        // every (instance, triangle) with a non-zero emissive factor (material.glsl:50-53: factor 0 makes the emission exactly 0
+        // whatever the texture says); more than 32 of them and the variant stays off for this scene
+        std::vector<Bvh8Tri> em;
+        bool too_many = false;
+        auto bits = [](uint32_t v) { float f; std::memcpy(&f, &v, 4); return f; };
+        for (size_t i = 0; i < inst.size() && !too_many; ++i) {
+            const PtMesh& m = meshes[inst[i].mesh_index];
+            for (uint32_t p = m.start; p < m.end && !too_many; ++p) {
+                const PtPrimitive& pr = s->primitives[p];
+                if ((s->materials[pr.info & PT_MATERIAL_INDEX_MASK].emissive_factor & 0xFFFFFFu) == 0u) continue;
+                for (uint32_t t = 0; t < pr.triangle_count; ++t) {
+                    if (em.size() >= 32) { too_many = true; break; }
+                    uint32_t id[3];
+                    for (int k = 0; k < 3; ++k)
+                        id[k] = (pr.info & PT_UINT32_INDICES_MASK) ? reinterpret_cast<const uint32_t*>(s->triangle_data + pr.indices_offset)[3 * (size_t)t + k]
+                                                                   : reinterpret_cast<const uint16_t*>(s->triangle_data + pr.indices_offset)[3 * (size_t)t + k];
+                    const float* pos = reinterpret_cast<const float*>(s->triangle_data + pr.positions_offset);
+                    Bvh8Tri tr;
+                    tr.v0 = make_float4(pos[3 * (size_t)id[0]], pos[3 * (size_t)id[0] + 1], pos[3 * (size_t)id[0] + 2], bits(p));
+                    tr.v1 = make_float4(pos[3 * (size_t)id[1]], pos[3 * (size_t)id[1] + 1], pos[3 * (size_t)id[1] + 2], bits(t));
+                    tr.v2 = make_float4(pos[3 * (size_t)id[2]], pos[3 * (size_t)id[2] + 1], pos[3 * (size_t)id[2] + 2], bits((uint32_t)i));
+                    em.push_back(tr);
+                }
+            }
+        }
+        if ((rc = dev_alloc(&r->d_emissive, std::max<size_t>(em.size(), 1))) != PT_OK) return rc;
+        if (!too_many && !em.empty()) {
+            PT_CUDA_CHECK(cudaMemcpyAsync(r->d_emissive, em.data(), em.size() * sizeof(Bvh8Tri), cudaMemcpyHostToDevice, r->stream));
+            PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));     // em is a stack temporary
+        }
+        sc.emissive_tris = r->d_emissive;
+        sc.num_emissive = too_many ? kInvalidId : (uint32_t)em.size();
+    }
+#endif
     return PT_OK;
 }
 
@@ -284,6 +321,7 @@ void destroy_impl(PtRenderer* r) {
     if (r->owns_scene) {
         for (auto p : r->d_texels) cudaFree(p);
         for (auto p : r->d_atlases) cudaFree(p);
+        cudaFree(r->d_emissive);
         cudaFree(r->d_blob); cudaFree(r->d_prims); cudaFree(r->d_materials); cudaFree(r->d_textures);
         cudaFree(r->d_instances_raw); cudaFree(r->d_instances);
         r->bvh.release();

@@ -110,6 +110,13 @@ struct DeviceScene {
     // starts at that instance's BLAS root with the instance already entered
     uint32_t start_root, start_inst;
     uint32_t num_instances, num_prims, num_materials, num_textures;
+#ifdef PT_OCCLUSION_LAST
+    // A/B variant ("last segments as occlusion queries"): every (instance, triangle) whose material has a
+    // non-zero emissive factor, object-space vertices, ids in the w lanes (v0.w primitive, v1.w triangle, v2.w instance).
+    // num_emissive == kInvalidId: too many of them, the variant is off for this scene.
+    const Bvh8Tri* emissive_tris;
+    uint32_t num_emissive;
+#endif
 };
 
 // Hit record in HBM: 32 bytes (2 x 16 B)

@@ -359,7 +359,37 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                 from_cache = true;
             }
             if (emit) {
+#ifdef PT_OCCLUSION_LAST
+                // The ray just sampled is the last segment of its sample: it only adds the emission of what it hits, or the
+                // sky.  Take the lexicographically closest hit among the scene's few emissive triangles here (same
+                // intersect_tri and object-space frames as K-trace, all lanes busy), hand it to K-trace as the slot's
+                // initial hit and flag the ray: K-trace stops it at the first candidate that beats that hit -- a non-emissive
+                // blocker by construction, so the sample adds the same exact zero as its true closest hit would.
+                uint32_t occl = 0u;
+                if (sc.num_emissive != kInvalidId && j > 0u && j + 1u >= B && !(fp.flags & (PT_FLAG_TRACE_BVH2 | PT_FLAG_TRACE_WALKER))) {
+                    Hit cand;
+                    hit_init(cand);
+                    for (uint32_t e = 0; e < sc.num_emissive; ++e) {
+                        const float4* q = reinterpret_cast<const float4*>(sc.emissive_tris + e);
+                        const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
+                        const uint32_t inst = __float_as_uint(p2.w);
+                        V3 oo = origin, dd = direction;
+                        if (!(__ldg(&sc.instances[inst].mesh) & kInstIdentity)) to_object(sc.instances, inst, origin, direction, oo, dd);
+                        const RayPre rp = ray_precompute(dd);
+                        float t, b1, b2;
+                        if (intersect_tri(oo, rp, p0, p1, p2, 0.001f, 10000.0f, t, b1, b2)) {
+                            const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
+                            if (hit_better(t, inst, prim, tri, cand)) { cand.t = t; cand.b1 = b1; cand.b2 = b2; cand.inst = inst; cand.prim = prim; cand.tri = tri; }
+                        }
+                    }
+                    pb.hit_a[slot] = make_float4(cand.t, cand.b1, cand.b2, __uint_as_float(cand.inst));
+                    pb.hit_b[slot] = make_uint2(cand.prim, cand.tri);
+                    occl = 32u;
+                }
+                store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, origin, direction, 0.001f, 10000.0f, occl);
+#else
                 store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, origin, direction, 0.001f, 10000.0f);
+#endif
                 pb.atten_sx[slot] = make_float4(atten.x, atten.y, atten.z, __uint_as_float(seed.x));
                 pb.color_sy[slot] = make_float4(color.x, color.y, color.z, __uint_as_float(seed.y));
                 pb.final_sb[slot] = make_float4(final_color.x, final_color.y, final_color.z, __uint_as_float(s | (j << 16)));

@@ -131,11 +131,11 @@ PT_D void frame_set(RayFrame& f, V3 o, V3 d) {
 // where rays are born (K-raygen / K-shade / k_ray_setup, all lanes busy) instead of in K-trace,
 // where refilled lanes would do it two at a time (profiles/r1a: 22 % of K-trace's issue slots).
 PT_D void store_ray(float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ ray_e, float4* __restrict__ ray_s,
-                    float4* __restrict__ ray_m, uint32_t slot, V3 o, V3 d, float tmin, float tmax) {
+                    float4* __restrict__ ray_m, uint32_t slot, V3 o, V3 d, float tmin, float tmax, uint32_t extra_bits = 0u) {
     RayFrame f;
     frame_set(f, o, d);
     const RayPre rp = ray_precompute(d);
-    const uint32_t bits = f.rs | ((uint32_t)rp.kz << 3);
+    const uint32_t bits = f.rs | ((uint32_t)rp.kz << 3) | extra_bits;     // bit 5: occlusion query (PT_OCCLUSION_LAST variant)
     ray_o[slot] = make_float4(o.x, o.y, o.z, tmin);
     ray_d[slot] = make_float4(d.x, d.y, d.z, tmax);
     ray_e[slot] = make_float4(f.idir.x, f.idir.y, f.idir.z, __uint_as_float(bits));

@@ -162,6 +162,9 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     RayPre rp;
     float tmin = 0.0f, tmax = 0.0f;
     uint32_t cur_inst = kInvalidId;
+#ifdef PT_OCCLUSION_LAST
+    bool occl = false;
+#endif
     Hit best;
     uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
 #ifdef PT_TRACE_SMEM_STACK
@@ -211,6 +214,14 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                         load_ray(io, slot, f, rp, tmin, tmax);
                         cur_inst = sc.start_inst;
                         hit_init(best);
+#ifdef PT_OCCLUSION_LAST
+                        occl = (__float_as_uint(io.ray_e[slot].w) & 32u) != 0u;
+                        if (occl) {   // the closest emissive hit found by K-shade (or a miss): anything that beats it ends the ray
+                            const float4 ha = io.hit_a[(size_t)slot * io.hit_a_stride];
+                            const uint2 hb = io.hit_b[(size_t)slot * io.hit_b_stride];
+                            best.t = ha.x; best.b1 = ha.y; best.b2 = ha.z; best.inst = __float_as_uint(ha.w); best.prim = hb.x; best.tri = hb.y;
+                        }
+#endif
                         sp = 0;
                         G = make_uint2(sc.start_root, 0x80000000u);
                         T = make_uint2(0u, 0u);
@@ -232,7 +243,17 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
             T.y &= T.y - 1u;
             if (cur_inst != kInvalidId) {
+#ifdef PT_OCCLUSION_LAST
+                const float t_before = best.t;
+                const uint32_t inst_before = best.inst, prim_before = best.prim, tri_before = best.tri;
                 test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
+                // an accepted candidate is lexicographically smaller, so at least one of the four changed
+                if (occl && (best.t != t_before || best.inst != inst_before || best.prim != prim_before || best.tri != tri_before)) {
+                    sp = 0; T.y = 0u; G.y &= 0x00FFFFFFu;    // blocker found: drop the remaining work, the pop below retires the ray
+                }
+#else
+                test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
+#endif
             } else {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
                 if (T.y && sp < kStackSize) PT_STACK_PUSH(T);
