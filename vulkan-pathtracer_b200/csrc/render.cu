@@ -100,7 +100,20 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace(DeviceScene sc, PathBuf
             const float4 ro = pb.ray_o[slot], rd = pb.ray_d[slot];
             Hit h;
             if (MODE == TRACE_BVH2) trace_bvh2(sc, tlas2_count, tlas2_leaf_instance, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h);
+#ifdef PT_OCCLUSION_LAST
+            else if (MODE == TRACE_BVH8_COUNT) {
+                // the algorithmic-byte counter follows the same rule as K-trace: flagged rays are first-hit queries
+                Hit init;
+                const bool occl = (__float_as_uint(pb.ray_e[slot].w) & 32u) != 0u;
+                if (occl) {
+                    const float4 ha = pb.hit_a[slot]; const uint2 hb = pb.hit_b[slot];
+                    init.t = ha.x; init.b1 = ha.y; init.b2 = ha.z; init.inst = __float_as_uint(ha.w); init.prim = hb.x; init.tri = hb.y;
+                }
+                trace_bvh8<true>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, &cnt_nodes, &cnt_tris, occl ? &init : nullptr);
+            }
+#else
             else if (MODE == TRACE_BVH8_COUNT) trace_bvh8<true>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, &cnt_nodes, &cnt_tris);
+#endif
             else trace_bvh8<false>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, nullptr, nullptr);
             pb.hit_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.inst));
             pb.hit_b[slot] = make_uint2(h.prim, h.tri);

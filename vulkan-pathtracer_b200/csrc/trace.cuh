@@ -214,8 +214,15 @@ PT_D uint32_t node_test(const Bvh8Node* __restrict__ nodes, uint32_t idx, const 
 // Single-ray traversal; the persistent kernel in render.cu calls this per fetched ray.
 // counters (optional): [0] += nodes decoded, [1] += triangles tested.
 template <bool kCount>
-PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, Hit& best, uint32_t* n_nodes, uint32_t* n_tris) {
+PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, Hit& best, uint32_t* n_nodes, uint32_t* n_tris
+#ifdef PT_OCCLUSION_LAST
+                     , const Hit* init = nullptr      // occlusion query: start from this hit, return at the first candidate that beats it
+#endif
+) {
     hit_init(best);
+#ifdef PT_OCCLUSION_LAST
+    if (init) best = *init;
+#endif
     if (sc.tlas_root == kInvalidId) return;
     RayFrame world, f;
     frame_set(world, o, d);
@@ -253,6 +260,9 @@ PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, 
                 T.y &= T.y - 1u;
                 test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
                 if (kCount) ++*n_tris;
+#ifdef PT_OCCLUSION_LAST
+                if (init && (best.t != init->t || best.inst != init->inst || best.prim != init->prim || best.tri != init->tri)) return;
+#endif
             }
         } else if (T.y) {
             // TLAS leaf item = instance: enter the first, keep the rest for later
