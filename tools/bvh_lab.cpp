@@ -646,6 +646,11 @@ int main(int argc, char** argv) {
     vs.push_back({"SAH32 + optimal, 1 tri/slot", collapse_optimal(sah, 1, 1.0f, 0.7f)});
     vs.push_back({"SAH32 + optimal, 2 tris/slot", collapse_optimal(sah, 2, 1.0f, 0.7f)});
     vs.push_back({"SAH32 + optimal, 3 tris/slot", collapse_optimal(sah, 3, 1.0f, 0.7f)});
+    {
+        Bvh2 sah64 = build_sah(64), sah128 = build_sah(128);
+        vs.push_back({"SAH64 + optimal, 2 tris/slot", collapse_optimal(sah64, 2, 1.0f, 0.7f)});
+        vs.push_back({"SAH128 + optimal, 2 tris/slot", collapse_optimal(sah128, 2, 1.0f, 0.7f)});
+    }
     Bvh2 sah16 = build_sah(16);
     vs.push_back({"SAH16 + optimal, 2 tris/slot", collapse_optimal(sah16, 2, 1.0f, 0.7f)});
     uint32_t levels = 0;
