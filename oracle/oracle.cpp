@@ -599,6 +599,9 @@ static inline PtHit closest_hit(const SceneView& sv, V3 o, V3 d, float tmin, flo
 // sample adds the same exact zero as the true closest hit would; without one the answer is the emissive hit or a miss.
 // tests/test_oracle_trace.py asserts that images rendered this way are bit-identical to the plain loop.
 static bool g_occlusion_last = false;
+static bool g_skip_dead_last = false;
+static bool g_count_dead = false;
+static std::atomic<uint64_t> g_dead_rays{0};
 
 static inline PtHit last_segment_hit(const SceneView& sv, V3 o, V3 d, float tmin, float tmax, bool use_bvh) {
     PtHit best; best.t = 1e32f; best.b1 = best.b2 = 0.0f;
@@ -764,6 +767,9 @@ static inline PixelOut shade_pixel(const SceneView& sv, const PtCamera& cam, uin
         V3 origin = pos;                                                        // :47
         V3 direction = normalize(fwd + hor * dx - ver * dy);                    // :48
         for (uint32_t j = 0; j < B; ++j) {                                      // :49
+            // second proposed saving: the last segment draws no random numbers and only adds atten * (emission or sky), so
+            // with a throughput of exactly zero it adds exactly nothing and need not be traced (both factors are finite)
+            if (g_skip_dead_last && j == B - 1 && j > 0 && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) break;
             const PtHit h = (g_occlusion_last && j == B - 1 && !(i == 0 && j == 0))
                                 ? last_segment_hit(sv, origin, direction, tmin, tmax, use_bvh)
                                 : closest_hit(sv, origin, direction, tmin, tmax, use_bvh);  // :50-63
@@ -792,6 +798,9 @@ static inline PixelOut shade_pixel(const SceneView& sv, const PtCamera& cam, uin
                 float lambert_in = dot(s.normal, direction);                    // :90
                 if (lambert_in <= 0.0f) break;                                  // :91-93
                 atten = atten * (brdf(s, direction) * lambert_in / density);    // :95
+                // statistic for DESIGN.md section 10: last segments about to be traced with a throughput of exactly zero (brdf()
+                // returns 0 when the shading normal faces away from the viewer)
+                if (g_count_dead && j + 2 == B && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) g_dead_rays.fetch_add(1, std::memory_order_relaxed);
             }
         }
         final_color = final_color + color;                                      // :99
@@ -954,6 +963,9 @@ int orc_intersect_tri(const float o[3], const float d[3], const float v[9], floa
 }
 // test-only switch: last segments of a sample as first-hit queries behind the closest emissive hit (see last_segment_hit)
 void orc_set_occlusion_last(int on) { g_occlusion_last = on != 0; }
+
+void orc_set_skip_dead_last(int on) { g_skip_dead_last = on != 0; }
+uint64_t orc_dead_ray_statistic(int enable) { g_count_dead = enable != 0; return g_dead_rays.exchange(0); }
 
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }
 

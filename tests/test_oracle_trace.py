@@ -185,3 +185,31 @@ def test_last_segment_as_occlusion_query_is_bit_identical(oracle_lib, scene, W, 
             assert bits_equal(a, c).all()
     finally:
         oracle_lib.orc_set_occlusion_last(0)
+
+
+@pytest.mark.parametrize("scene,W,H,spp,seg", [("cornell", 96, 96, 3, 2), ("soup", 96, 64, 2, 3), ("atrium", 160, 90, 2, 2)])
+def test_zero_throughput_last_segments_need_no_trace(oracle_lib, scene, W, H, spp, seg):
+    """The last segment of a sample draws no random numbers and only adds atten * (emission | sky), both finite: when atten is
+    exactly (0, 0, 0) -- brdf() returns 0 for a shading normal that faces away from the viewer -- it adds exactly nothing.
+    Skipping those rays (orc_set_skip_dead_last) leaves every bit of the image alone and traces fewer rays; combined with the
+    occlusion-query rule as well."""
+    if scene == "cornell":
+        ps = S.cornell().pack()
+    elif scene == "soup":
+        ps = S.random_soup(17, 1500, 3, 6).pack()
+    else:
+        ps = S.atrium(1234, 20_000, 6, 64, (0.1, 1.0), 0.2, True).pack()
+    osc = orc.OracleScene(ps, True)
+    cfg = S.render_config(W, H, spp, seg)
+    cam = S.camera_default(W, H, 0)
+    try:
+        a, _, rays_a = osc.render(cfg, cam, True)
+        oracle_lib.orc_set_skip_dead_last(1)
+        b, _, rays_b = osc.render(cfg, cam, True)
+        oracle_lib.orc_set_occlusion_last(1)
+        c, _, rays_c = osc.render(cfg, cam, True)
+        assert bits_equal(a, b).all() and bits_equal(a, c).all()
+        assert rays_b <= rays_a and rays_c == rays_b
+    finally:
+        oracle_lib.orc_set_skip_dead_last(0)
+        oracle_lib.orc_set_occlusion_last(0)

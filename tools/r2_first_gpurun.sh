@@ -25,7 +25,7 @@ python bench.py --workload c3 --steps 2 --warmup 3 --no-cpu-baseline > $O/r2a_be
 for f in $O/r2a_bench_c3_*.json $O/r2a_bench_c2_shares*.json; do echo $f; cut -c1-200 $f; echo; done
 # parity of the variants whose results are not bit-identical by construction (occlusion-query last segments: proven in the CPU
 # restatement, kernels never run; sincos: last-place differences possible)
-for v in occl sincos; do
+for v in skipdead occl occlskip sincos; do
   f=$PWD/vulkan-pathtracer_b200/variants/libb200pt_$v.so
   [ -f $f ] && { echo "== parity with $v"; B200PT_LIB=$f timeout 900 python -m pytest tests/test_gpu_parity.py -q 2>&1 | tail -5; } | tee -a $O/r2a_variant_parity.txt
 done

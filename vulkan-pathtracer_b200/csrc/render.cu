@@ -355,6 +355,13 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                             atten = atten * (brdf(si, direction) * lambert_in / density);   // :95
                             ++j;
                             emit = true;
+#ifdef PT_SKIP_DEAD_LAST
+                            // A/B variant: the last segment draws no random numbers and only adds atten * (emission | sky), both
+                            // finite, so with a throughput of exactly zero (brdf() == 0: shading normal facing away from the
+                            // viewer) it adds exactly nothing and is not traced.  11 % of C2's bounce rays; bit-identity checked
+                            // in the CPU restatement (tests/test_oracle_trace.py).
+                            if (j + 1u >= B && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) { emit = false; end_sample = true; }
+#endif
                         }
                     } else {
                         end_sample = true;   // last segment: loop bound reached (:49)
