@@ -517,8 +517,10 @@ static Wide collapse_optimal(const Bvh2& t, uint32_t max_leaf, float c_node, flo
 struct Ray { float o[3], d[3], tmin, tmax; };
 struct HitR { float t; uint32_t tri; };
 
+static const float* g_tri_ptr = nullptr;     // triangles the walker tests (g_tris unless a BLAS of the two-level model is walked)
+
 static bool tri_hit(uint32_t tr, const Ray& r, float tmax, float& t_out) {
-    const float* v = &g_tris[9 * (size_t)tr];
+    const float* v = (g_tri_ptr ? g_tri_ptr : g_tris.data()) + 9 * (size_t)tr;
     double e1[3], e2[3], n[3];
     for (int k = 0; k < 3; ++k) { e1[k] = (double)v[3 + k] - v[k]; e2[k] = (double)v[6 + k] - v[k]; }
     n[0] = e1[1] * e2[2] - e1[2] * e2[1]; n[1] = e1[2] * e2[0] - e1[0] * e2[2]; n[2] = e1[0] * e2[1] - e1[1] * e2[0];
@@ -584,7 +586,7 @@ static HitR walk(const Wide& w, const Ray& r, Counts& cnt) {
             if (!(leaf_hit >> c & 1u)) continue;
             for (uint32_t k = 0; k < n.c[c].tri_cnt; ++k) {
                 cnt.tris++;
-                if (g_leaf[w.tris[n.c[c].tri_first + k]].half_area() > g_big_area) cnt.big_tris++;
+                if (g_big_area < 3.0e38f && g_leaf[w.tris[n.c[c].tri_first + k]].half_area() > g_big_area) cnt.big_tris++;
                 float tt;
                 const uint32_t tr = w.tris[n.c[c].tri_first + k];
                 if (tri_hit(tr, r, r.tmax, tt) && (tt < best.t || (tt == best.t && tr < best.tri))) { best.t = tt; best.tri = tr; }
@@ -600,8 +602,200 @@ static HitR walk(const Wide& w, const Ray& r, Counts& cnt) {
 
 static uint32_t hash32(uint32_t x) { x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16; return x; }
 
+// ------------------------------------------------------------------ two-level model (instanced scenes, C4)
+// scene file: u32 M; per mesh u32 n + n x 9 floats; u32 I; per instance u32 mesh + 12 floats (rows of the 3x4 transform)
+struct Inst { uint32_t mesh; float m[12]; double inv[9]; };
+struct Mesh { std::vector<float> tris; Wide shipped, better; };
+
+static void set_leaves(const std::vector<float>& tris) {
+    g_tris = tris;
+    g_n = (uint32_t)(tris.size() / 9);
+    g_leaf.assign(g_n, Box());
+    for (uint32_t i = 0; i < g_n; ++i)
+        for (int v = 0; v < 3; ++v)
+            for (int k = 0; k < 3; ++k) {
+                g_leaf[i].lo[k] = std::fmin(g_leaf[i].lo[k], g_tris[9 * (size_t)i + 3 * v + k]);
+                g_leaf[i].hi[k] = std::fmax(g_leaf[i].hi[k], g_tris[9 * (size_t)i + 3 * v + k]);
+            }
+}
+
+static Wide build_variant(bool better, uint32_t max_leaf) {
+    if (g_n < 2) {   // a single leaf: one wide node with one slot
+        Wide w; WNode n; n.nc = 1; n.c[0].qb = n.c[0].xb = g_leaf[0]; n.c[0].inner = -1; n.c[0].tri_first = 0; n.c[0].tri_cnt = 1; n.c[0].slot = 0;
+        w.nodes.push_back(n); w.tris.push_back(0); return w;
+    }
+    if (!better) { Bvh2 t = build_lbvh(); return collapse_greedy(t, max_leaf); }
+    uint32_t levels = 0;
+    Bvh2 t = build_sah_kernel(&levels);
+    return collapse_optimal(t, max_leaf, 1.0f, 0.7f, true);
+}
+
+struct Counts2 { uint64_t nodes = 0, tris = 0, entries = 0, rays = 0; };
+
+static HitR walk2(const Wide& tlas, const std::vector<Mesh>& meshes, const std::vector<Inst>& inst, bool better, const Ray& r, Counts2& c2) {
+    HitR best{1e32f, 0xFFFFFFFFu};
+    float id[3]; uint32_t rs = 0;
+    for (int k = 0; k < 3; ++k) { id[k] = 1.0f / (r.d[k] == 0.0f ? 1e-30f : r.d[k]); if (id[k] >= 0.0f) rs |= 1u << k; }
+    int stack[512]; int sp = 0;
+    stack[sp++] = 0;
+    c2.rays++;
+    while (sp) {
+        const WNode& n = tlas.nodes[stack[--sp]];
+        c2.nodes++;
+        const float tlim = std::fmin(r.tmax, best.t);
+        struct { int prio, node; } inner[8]; int ni = 0;
+        uint32_t leaf_hit = 0;
+        for (int c = 0; c < n.nc; ++c) {
+            const Box& b = n.c[c].qb;
+            float tn = r.tmin, tf = tlim;
+            for (int k = 0; k < 3; ++k) {
+                float a = (b.lo[k] - r.o[k]) * id[k], bb = (b.hi[k] - r.o[k]) * id[k];
+                tn = std::fmax(tn, std::fmin(a, bb)); tf = std::fmin(tf, std::fmax(a, bb));
+            }
+            if (!(tn <= tf * 1.0000019f)) continue;
+            if (n.c[c].inner >= 0) { inner[ni].prio = (int)((uint32_t)n.c[c].slot ^ rs); inner[ni].node = n.c[c].inner; ni++; }
+            else leaf_hit |= 1u << c;
+        }
+        for (int c = 0; c < n.nc; ++c) {
+            if (!(leaf_hit >> c & 1u)) continue;
+            const Inst& in = inst[tlas.tris[n.c[c].tri_first]];
+            c2.entries++;
+            Ray o;
+            o.tmin = r.tmin; o.tmax = std::fmin(r.tmax, best.t);
+            const double q[3] = {(double)r.o[0] - in.m[3], (double)r.o[1] - in.m[7], (double)r.o[2] - in.m[11]};
+            for (int k = 0; k < 3; ++k) {
+                o.o[k] = (float)(in.inv[3 * k] * q[0] + in.inv[3 * k + 1] * q[1] + in.inv[3 * k + 2] * q[2]);
+                o.d[k] = (float)(in.inv[3 * k] * r.d[0] + in.inv[3 * k + 1] * r.d[1] + in.inv[3 * k + 2] * r.d[2]);
+            }
+            const Mesh& m = meshes[in.mesh];
+            g_tri_ptr = m.tris.data();
+            Counts cb;
+            const HitR h = walk(better ? m.better : m.shipped, o, cb);
+            g_tri_ptr = nullptr;
+            c2.nodes += cb.nodes; c2.tris += cb.tris;
+            if (h.tri != 0xFFFFFFFFu && h.t < best.t) { best.t = h.t; best.tri = h.tri; }
+        }
+        for (int i = 1; i < ni; ++i) { auto e = inner[i]; int j = i - 1; while (j >= 0 && inner[j].prio > e.prio) { inner[j + 1] = inner[j]; --j; } inner[j + 1] = e; }
+        for (int k = 0; k < ni; ++k) stack[sp++] = inner[k].node;
+    }
+    return best;
+}
+
+static int scene_mode(const char* path, int W, int H, int step) {
+    FILE* fp = std::fopen(path, "rb");
+    if (!fp) { std::perror(path); return 1; }
+    uint32_t M = 0, I = 0;
+    if (std::fread(&M, 4, 1, fp) != 1) return 1;
+    std::vector<Mesh> meshes(M);
+    for (auto& m : meshes) {
+        uint32_t n = 0;
+        if (std::fread(&n, 4, 1, fp) != 1) return 1;
+        m.tris.resize(9 * (size_t)n);
+        if (std::fread(m.tris.data(), 36, n, fp) != n) return 1;
+    }
+    if (std::fread(&I, 4, 1, fp) != 1) return 1;
+    std::vector<Inst> inst(I);
+    for (auto& in : inst) {
+        if (std::fread(&in.mesh, 4, 1, fp) != 1 || std::fread(in.m, 4, 12, fp) != 12) return 1;
+        const double a[9] = {in.m[0], in.m[1], in.m[2], in.m[4], in.m[5], in.m[6], in.m[8], in.m[9], in.m[10]};
+        const double det = a[0] * (a[4] * a[8] - a[5] * a[7]) - a[1] * (a[3] * a[8] - a[5] * a[6]) + a[2] * (a[3] * a[7] - a[4] * a[6]);
+        const double c[9] = {a[4] * a[8] - a[5] * a[7], a[2] * a[7] - a[1] * a[8], a[1] * a[5] - a[2] * a[4],
+                             a[5] * a[6] - a[3] * a[8], a[0] * a[8] - a[2] * a[6], a[2] * a[3] - a[0] * a[5],
+                             a[3] * a[7] - a[4] * a[6], a[1] * a[6] - a[0] * a[7], a[0] * a[4] - a[1] * a[3]};
+        for (int k = 0; k < 9; ++k) in.inv[k] = c[k] / det;
+    }
+    std::fclose(fp);
+    std::printf("%u meshes, %u instances, %dx%d every %d pixels\n", M, I, W, H, step);
+    for (auto& m : meshes) { set_leaves(m.tris); m.shipped = build_variant(false, 2); m.better = build_variant(true, 2); }
+    // world-space triangles of every instance: the flattened scene, and the exact instance boxes (as the shipped TLAS uses)
+    std::vector<float> flat;
+    std::vector<float> boxes_as_tris;     // one degenerate "triangle" (lo, hi, lo) per instance: its box is the instance box
+    for (auto& in : inst) {
+        const std::vector<float>& t = meshes[in.mesh].tris;
+        Box b;
+        for (size_t v = 0; v < t.size() / 3; ++v) {
+            float w[3];
+            for (int r = 0; r < 3; ++r) w[r] = in.m[4 * r] * t[3 * v] + in.m[4 * r + 1] * t[3 * v + 1] + in.m[4 * r + 2] * t[3 * v + 2] + in.m[4 * r + 3];
+            for (int k = 0; k < 3; ++k) { flat.push_back(w[k]); b.lo[k] = std::fmin(b.lo[k], w[k]); b.hi[k] = std::fmax(b.hi[k], w[k]); }
+        }
+        for (int k = 0; k < 3; ++k) boxes_as_tris.push_back(b.lo[k]);
+        for (int k = 0; k < 3; ++k) boxes_as_tris.push_back(b.hi[k]);
+        for (int k = 0; k < 3; ++k) boxes_as_tris.push_back(b.lo[k]);
+    }
+    set_leaves(boxes_as_tris);
+    const Wide tlas_shipped = build_variant(false, 1), tlas_better = build_variant(true, 1);
+    std::printf("TLAS: %zu / %zu wide nodes (shipped / SAH + optimal)\n", tlas_shipped.nodes.size(), tlas_better.nodes.size());
+
+    std::vector<Ray> primary, bounce;
+    const float vh = 2.0f * std::tan(0.5f * 0.78539816339f), vw = vh * (float)W / (float)H;
+    for (int y = step / 2; y < H; y += step)
+        for (int x = step / 2; x < W; x += step) {
+            const float dx = 2.0f * ((float)x + 0.5f) / (float)W - 1.0f, dy = 2.0f * ((float)y + 0.5f) / (float)H - 1.0f;
+            float d[3] = {-vw * dx, -vh * dy, 1.0f};
+            const float inv = 1.0f / std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+            Ray r; r.tmin = 0.001f; r.tmax = 10000.0f;
+            for (int k = 0; k < 3; ++k) { r.o[k] = 0.0f; r.d[k] = d[k] * inv; }
+            primary.push_back(r);
+        }
+    {
+        // bounce rays: uniform directions in the hemisphere facing back along the incoming ray (no normals at hand here)
+        Counts2 dummy; uint32_t seed = 1;
+        for (auto& r : primary) {
+            const HitR h = walk2(tlas_shipped, meshes, inst, false, r, dummy);
+            if (h.tri == 0xFFFFFFFFu) continue;
+            Ray b; b.tmin = 0.001f; b.tmax = 10000.0f;
+            float d[3], len2;
+            do {
+                for (int k = 0; k < 3; ++k) d[k] = 2.0f * (float)(hash32(seed++) >> 8) / 16777216.0f - 1.0f;
+                len2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+            } while (len2 > 1.0f || len2 < 1e-4f);
+            const float il = 1.0f / std::sqrt(len2);
+            float dot = 0.0f;
+            for (int k = 0; k < 3; ++k) { d[k] *= il; dot += d[k] * r.d[k]; }
+            for (int k = 0; k < 3; ++k) { if (dot > 0.0f) d[k] = -d[k]; b.d[k] = d[k]; b.o[k] = r.o[k] + (h.t - 1e-3f) * r.d[k]; }
+            bounce.push_back(b);
+        }
+    }
+    std::printf("%zu primary rays, %zu bounce rays\n\n", primary.size(), bounce.size());
+    std::printf("%-52s %9s %7s %8s %8s\n", "variant", "nodes/ray", "tris", "entries", "n+.7t");
+    std::vector<float> ref_t;
+    for (int v = 0; v < 2; ++v) {
+        Counts2 c;
+        size_t idx = 0, mism = 0;
+        for (auto* rays : {&primary, &bounce})
+            for (auto& r : *rays) {
+                const HitR h = walk2(v ? tlas_better : tlas_shipped, meshes, inst, v != 0, r, c);
+                if (v == 0) ref_t.push_back(h.t); else if (std::fabs(h.t - ref_t[idx]) > 1e-3f * std::fmax(1.0f, ref_t[idx]) && !(h.t > 1e31f && ref_t[idx] > 1e31f)) mism++;
+                idx++;
+            }
+        const double n = (double)c.nodes / c.rays, t = (double)c.tris / c.rays;
+        std::printf("%-52s %9.2f %7.2f %8.2f %8.2f%s\n", v ? "two-level, SAH + optimal collapse on both levels" : "two-level as shipped (LBVH + greedy, exact boxes)",
+                    n, t, (double)c.entries / c.rays, n + 0.7 * t, mism ? "  HIT MISMATCH" : "");
+    }
+    // flattened: one hierarchy over the world-space triangles of all instances
+    set_leaves(flat);
+    std::printf("flattened scene: %u world-space triangles\n", g_n);
+    for (int v = 0; v < 2; ++v) {
+        const Wide w = build_variant(v != 0, 2);
+        Counts c;
+        size_t idx = 0, mism = 0;
+        for (auto* rays : {&primary, &bounce})
+            for (auto& r : *rays) {
+                const HitR h = walk(w, r, c);
+                if (std::fabs(h.t - ref_t[idx]) > 1e-3f * std::fmax(1.0f, ref_t[idx]) && !(h.t > 1e31f && ref_t[idx] > 1e31f)) mism++;
+                idx++;
+            }
+        const double n = (double)c.nodes / c.rays, t = (double)c.tris / c.rays;
+        std::printf("%-52s %9.2f %7.2f %8s %8.2f   (%zu wide nodes)%s\n", v ? "flattened, SAH + optimal collapse" : "flattened, LBVH + greedy collapse", n, t, "-", n + 0.7 * t,
+                    w.nodes.size(), mism ? "  HIT MISMATCH" : "");
+        if (mism) std::printf("   (%zu rays)\n", mism);
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
-    if (argc < 5) { std::fprintf(stderr, "usage: bvh_lab tris.bin width height step\n"); return 2; }
+    if (argc < 5) { std::fprintf(stderr, "usage: bvh_lab tris.bin|scene.scene width height step\n"); return 2; }
+    if (std::strstr(argv[1], ".scene")) return scene_mode(argv[1], std::atoi(argv[2]), std::atoi(argv[3]), std::atoi(argv[4]));
     FILE* fp = std::fopen(argv[1], "rb");
     if (!fp) { std::perror(argv[1]); return 1; }
     if (std::fread(&g_n, 4, 1, fp) != 1) return 1;

@@ -41,8 +41,10 @@ def main():
         sb, (W, H) = S.sponza_scale(textures=False), (1920, 1080)
     elif which == "c5":
         sb, (W, H) = S.atrium(1234, 1_000_000, 16, 64, (0.05, 0.5), 0.6, False), (1920, 1080)
+    elif which == "c4":
+        sb, (W, H) = S.instanced(), (1920, 1080)
     else:
-        raise SystemExit("c1 | c2 | c5")
+        raise SystemExit("c1 | c2 | c4 | c5")
     packed = sb.pack()
     tris = world_triangles(packed)
     build = os.path.join(HERE, "_build")
@@ -52,6 +54,22 @@ def main():
     deps = [src, os.path.join(ROOT, "vulkan-pathtracer_b200", "csrc", "bvh_sah.cuh")]
     if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-Wall", "-Wno-unused-function", "-o", exe, src])
+    if which == "c4":
+        # two-level model: per-mesh triangles + instance transforms
+        path = os.path.join(build, "c4.scene")
+        with open(path, "wb") as f:
+            f.write(np.uint32(len(packed.meshes)).tobytes())
+            for m in packed.meshes:
+                sub = S.PackedScene()
+                sub.triangle_data = packed.triangle_data
+                sub.primitives = [packed.primitives[p] for p in range(m.start, m.end)]
+                t = world_triangles(sub)
+                f.write(np.uint32(len(t)).tobytes()); f.write(t.tobytes())
+            f.write(np.uint32(len(packed.instances)).tobytes())
+            for i in packed.instances:
+                f.write(np.uint32(i.mesh_index).tobytes()); f.write(np.array(list(i.transform)[:12], np.float32).tobytes())
+        subprocess.check_call([exe, path, str(W), str(H), str(step)])
+        return
     path = os.path.join(build, f"{which}_tris.bin")
     with open(path, "wb") as f:
         f.write(np.uint32(len(tris)).tobytes())
