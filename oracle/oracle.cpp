@@ -920,6 +920,31 @@ void orc_trace(const OrcScene* s, const PtRay* rays, size_t n, int use_bvh, int 
     for (auto& t : th) t.join();
 }
 
+// One closest-hit query: the "driver" side of traceRayEXT for the reference's own shaders compiled as C++
+// (oracle/ref_glsl/ref_glsl_api.cpp takes this function's address as its trace callback).
+int orc_closest_hit_one(const void* scene, const float o[3], float tmin, const float d[3], float tmax, int use_bvh, PtHit* out) {
+    const OrcScene* s = static_cast<const OrcScene*>(scene);
+    *out = closest_hit(s->sv, v3(o[0], o[1], o[2]), v3(d[0], d[1], d[2]), tmin, tmax, use_bvh != 0);
+    return out->t != 1e32f;
+}
+
+// getTriangleData + getMaterialData of n hits, 25 floats each: uv(2) normal(3) tangent(4) geometry_normal(3)
+// material_index(1, raw bits) | albedo(4) normal(3) emissive(3) roughness metallic
+void orc_shade_hits(const OrcScene* s, const PtHit* hits, size_t n, float* out) {
+    for (size_t i = 0; i < n; ++i) {
+        const TriangleData td = get_triangle_data(s->sv, hits[i]);
+        const MaterialData md = get_material_data(s->sv, td);
+        float* o = out + 25 * i;
+        o[0] = td.uv.x; o[1] = td.uv.y; o[2] = td.normal.x; o[3] = td.normal.y; o[4] = td.normal.z;
+        o[5] = td.tangent.x; o[6] = td.tangent.y; o[7] = td.tangent.z; o[8] = td.tangent.w;
+        o[9] = td.geometry_normal.x; o[10] = td.geometry_normal.y; o[11] = td.geometry_normal.z;
+        std::memcpy(o + 12, &td.material_index, 4);
+        o[13] = md.albedo.x; o[14] = md.albedo.y; o[15] = md.albedo.z; o[16] = md.albedo.w;
+        o[17] = md.normal.x; o[18] = md.normal.y; o[19] = md.normal.z;
+        o[20] = md.emissive.x; o[21] = md.emissive.y; o[22] = md.emissive.z; o[23] = md.roughness; o[24] = md.metallic;
+    }
+}
+
 // --- scalar entry points for known-answer tests -------------------------------------------
 void orc_prng_seed(uint32_t x, uint32_t y, uint32_t frame, uint32_t out[2]) { U2 s = prng_seed(x, y, frame); out[0] = s.x; out[1] = s.y; }
 void orc_pcg2d(uint32_t seed[2], float out[2]) { U2 s{seed[0], seed[1]}; V2 r = pcg2d(s); seed[0] = s.x; seed[1] = s.y; out[0] = r.x; out[1] = r.y; }

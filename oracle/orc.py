@@ -1,5 +1,6 @@
-"""ctypes binding of the CPU oracle (oracle/_build/liboracle.so) and of the reference's own
-brdf.glsl / rand.glsl compiled as C++ (oracle/_ref/libref_glsl.so).
+"""ctypes binding of the CPU oracle (oracle/_build/liboracle.so) and of the reference's own shader
+sources (ray_gen.rgen, closest_hit.rchit, miss.rmiss, triangle/material/brdf/rand/common.glsl) compiled
+as C++ (oracle/_ref/libref_glsl.so).
 
 TEST INFRASTRUCTURE: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 --impl reference legs may import this module.
@@ -56,6 +57,7 @@ def lib():
         L.orc_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
         L.orc_intersect_tri.restype = C.c_int
         L.orc_hardware_threads.restype = C.c_int
+        L.orc_shade_hits.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         _lib = L
     return _lib
 
@@ -64,7 +66,13 @@ def ref_lib():
     """The reference's brdf.glsl/rand.glsl as C++; None when it was never built (no /root/reference)."""
     global _ref
     if _ref is None and os.path.exists(REF_PATH):
-        _ref = C.CDLL(REF_PATH)
+        R = C.CDLL(REF_PATH)
+        if hasattr(R, "ref_render"):
+            R.ref_render.restype = C.c_uint64
+            R.ref_render.argtypes = [C.POINTER(PtSceneDesc), C.POINTER(PtRenderConfig), C.POINTER(PtCamera), C.c_void_p, C.c_void_p,
+                                     C.c_int, C.c_int, C.c_void_p]
+            R.ref_shade_hits.argtypes = [C.POINTER(PtSceneDesc), C.c_void_p, C.c_size_t, C.c_void_p]
+        _ref = R
     return _ref
 
 
@@ -118,6 +126,29 @@ class OracleScene:
         nt = nthreads or lib().orc_hardware_threads()
         rays = lib().orc_render_rows(self.handle, C.byref(cfg), C.byref(cam), 1, nt, y0, y1, row_step, _fp(rgba))
         return rgba, rays
+
+    def shade_hits(self, hits):
+        """getTriangleData + getMaterialData of every hit -> (n, 25) float32 (layout: orc_shade_hits)."""
+        hits = np.ascontiguousarray(hits, dtype=PtHit_dtype)
+        out = np.zeros((len(hits), 25), np.float32)
+        lib().orc_shade_hits(self.handle, _fp(hits), len(hits), _fp(out))
+        return out
+
+    # -- the same two through the REFERENCE's own shader sources (oracle/_ref/libref_glsl.so); the acceleration-structure
+    # query behind traceRayEXT is this oracle's closest_hit (the Vulkan driver's part has no source)
+    def ref_render(self, cfg, cam, use_bvh=True, nthreads=None):
+        W, H = cfg.width // max(1, cfg.divider), cfg.height // max(1, cfg.divider)
+        rgba = np.zeros((H, W, 4), np.float32)
+        nt = nthreads or lib().orc_hardware_threads()
+        fn = C.cast(lib().orc_closest_hit_one, C.c_void_p)
+        rays = ref_lib().ref_render(C.byref(self.desc), C.byref(cfg), C.byref(cam), fn, self.handle, 1 if use_bvh else 0, nt, _fp(rgba))
+        return rgba, rays
+
+    def ref_shade_hits(self, hits):
+        hits = np.ascontiguousarray(hits, dtype=PtHit_dtype)
+        out = np.zeros((len(hits), 25), np.float32)
+        ref_lib().ref_shade_hits(C.byref(self.desc), _fp(hits), len(hits), _fp(out))
+        return out
 
     def trace(self, rays, use_bvh=True, nthreads=None):
         rays = np.ascontiguousarray(rays, dtype=PtRay_dtype)

@@ -166,6 +166,22 @@ def test_cornell_golden_fixture():
     assert (ids[0] == g["inst"]).all() and (ids[1] == g["prim"]).all() and (ids[2] == g["tri"]).all()
 
 
+@pytest.mark.parametrize("name", ["atrium", "cornell", "instanced", "soup"])
+def test_frames_equal_golden_frames_of_the_reference_raygen(name):
+    """tests/golden/raygen_ref_frames.npz: whole frames rendered by the reference's own ray_gen.rgen main()
+    (+ closest_hit.rchit, miss.rmiss, triangle/material/brdf/rand.glsl) compiled as C++ (tools/make_golden.py);
+    the CUDA image equals them bit for bit, and so does the executed-ray count."""
+    from tools.make_golden import REF_FRAMES
+    g = np.load(os.path.join(GOLD, "raygen_ref_frames.npz"))
+    builder, W, H, spp, seg, frame = REF_FRAMES[name]
+    img, ids, st = render(builder().pack(), W, H, spp, seg, frame, flags=b200pt.PT_FLAG_NO_PRIMARY_REUSE)
+    eq = bits_equal(img, g[name])
+    assert eq.all(), f"{int((~eq.all(axis=2)).sum())} of {W * H} pixels differ from the reference raygen"
+    assert st.rays_traced == int(g[name + "_rays"])     # without primary-hit reuse: one query per traceRayEXT of the reference
+    img2, _, st2 = render(builder().pack(), W, H, spp, seg, frame)
+    assert bits_equal(img2, g[name]).all() and st2.rays_traced < st.rays_traced
+
+
 def test_config_c1_cornell_512():
     st, orays = assert_matches_oracle(S.cornell().pack(), 512, 512, 1, 2, use_bvh=False)
     assert st.rays_traced == orays          # 1 spp: no primary reuse, identical ray counts
@@ -235,6 +251,46 @@ def test_config_c2_sponza_scale_1080p_vs_oracle(sponza):
     """BASELINE.json configs[1] at full size, against the multi-threaded oracle."""
     st, orays = assert_matches_oracle(sponza, 1920, 1080, 1, 2)
     assert st.rays_traced == orays and st.num_triangles == sponza.num_triangles
+
+
+def assert_tile_sample_matches_oracle(ps, W, H, spp, seg, rank, world, frame=0):
+    """Config-size parity through the tile partition as a sampler: the GPU renders the interleaved tiles
+    `tile % world == rank` of the full-size frame (bit-identical to the same pixels of the whole frame by
+    test_tile_partition_sums_to_single_gpu_image), the oracle renders the same (rank, world) share
+    (oracle.cpp:orc_render) — ids and radiance bit-exact on every owned pixel, untouched elsewhere."""
+    T = b200pt.PT_PARTITION_TILES
+    img, ids, st = render(ps, W, H, spp, seg, frame, rank=rank, world=world, partition=T)
+    cfg = S.render_config(W, H, spp, seg, rank=rank, world=world, partition=T)
+    oimg, oids, orays = orc.OracleScene(ps, True).render(cfg, S.camera_default(W, H, frame), True)
+    ty, tx = np.meshgrid(np.arange(H) // 8, np.arange(W) // 32, indexing="ij")
+    owned = (ty * ((W + 31) // 32) + tx) % world == rank
+    assert owned.sum() >= W * H // world - 32 * 8 * 2
+    assert (oimg[owned][:, 3] == 1.0).all() and (oimg[~owned] == 0).all()
+    for name, a, b in zip(("instance", "primitive", "triangle"), ids, oids):
+        assert (a == b).all(), f"{name} ids differ in {int((a != b).sum())} pixels"
+    eq = bits_equal(img, oimg)
+    assert eq.all(), f"{int((~eq.all(axis=2)).sum())} of {int(owned.sum())} owned pixels differ from the oracle"
+    return st, orays
+
+
+def test_config_c3_4k_64spp_8seg_tile_sample_vs_oracle(sponza):
+    """BASELINE.json configs[2] (3840x2160, 64 spp, 8 segments): tile share 17 of 64 against the oracle."""
+    st, orays = assert_tile_sample_matches_oracle(sponza, 3840, 2160, 64, 8, 17, 64)
+    assert st.rays_traced < orays           # the primary hit is traced once for the 64 samples (quirk Q1)
+
+
+def test_config_c4_instanced_1000_tile_sample_vs_oracle():
+    """BASELINE.json configs[3] (1 000 rotated instances of a 10 080-triangle mesh, 1080p, 4 spp, 4 segments): tile share 1 of 4."""
+    ps = S.instanced(1234).pack()
+    assert len(ps.instances) == 1000 and ps.num_effective_triangles > 9_000_000
+    assert_tile_sample_matches_oracle(ps, 1920, 1080, 4, 4, 1, 4)
+
+
+def test_config_c5_heavy_material_tile_sample_vs_oracle():
+    """BASELINE.json configs[4] (~1 M triangles, 48 maps of 4096^2, 1080p, 16 spp, 6 segments): tile share 5 of 8."""
+    ps = S.heavy_material(1234).pack()
+    assert ps.num_triangles > 900_000 and max(t.shape[1] for t in ps.textures) == 4096
+    assert_tile_sample_matches_oracle(ps, 1920, 1080, 16, 6, 5, 8)
 
 
 def test_c2_reference_walker_and_no_reuse_equivalence(sponza):

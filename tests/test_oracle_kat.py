@@ -131,3 +131,67 @@ def test_furnace_bound(oracle_lib):
     w = np.where(ok, f[:, 0] * cos / np.where(ok, pdf, 1), 0)
     assert np.isfinite(w).all()
     assert w.mean() < 1.05
+
+
+# ------------------------------------------------------------------ the whole raygen loop, pinned to the reference's shader sources
+# oracle/_ref/libref_glsl.so holds ray_gen.rgen main(), closest_hit.rchit, miss.rmiss, getTriangleData (triangle.glsl:46-112),
+# getMaterialData (material.glsl:31-69), brdf.glsl and rand.glsl compiled as C++ from /root/reference (oracle/ref_glsl/rewrite.py).
+def _ref_frame_cases():
+    from tools.make_golden import REF_FRAMES
+    return sorted(REF_FRAMES)
+
+
+@pytest.mark.parametrize("name", _ref_frame_cases())
+def test_oracle_frames_equal_golden_frames_of_the_reference_raygen(oracle_lib, name):
+    """orc_render (the hand restatement) against frames rendered by the reference's own ray_gen.rgen main()."""
+    from tools import scene as S
+    from tools.make_golden import REF_FRAMES
+    g = np.load(os.path.join(GOLD, "raygen_ref_frames.npz"))
+    builder, W, H, spp, seg, frame = REF_FRAMES[name]
+    img, _, rays = orc.OracleScene(builder().pack(), True).render(S.render_config(W, H, spp, seg), S.camera_default(W, H, frame), True)
+    eq = bits_equal(img, g[name])
+    assert eq.all(), f"{int((~eq.all(axis=2)).sum())} of {W * H} pixels differ from the reference raygen"
+    assert rays == int(g[name + "_rays"])           # one traceRayEXT per executed segment (ray_gen.rgen:51)
+
+
+@pytest.mark.parametrize("case", ["cornell", "soup-bruteforce", "atrium", "instanced", "tiles"])
+def test_raygen_live_against_reference_glsl(oracle_lib, ref_glsl, case):
+    """Whole frames through the reference's main(), one invocation per pixel, against orc_render — bit for bit."""
+    from tools import scene as S
+    if not hasattr(ref_glsl, "ref_render"):
+        pytest.skip("prebuilt oracle/_ref predates the full-pipeline build")
+    builder, W, H, spp, seg, frame, use_bvh, part = {
+        "cornell": (lambda: S.cornell(), 160, 120, 3, 5, 7, True, (0, 1)),
+        "soup-bruteforce": (lambda: S.random_soup(5, 600, 3, 6), 96, 54, 2, 4, 1, False, (0, 1)),
+        "atrium": (lambda: S.atrium(1234, 20000, 6, 64), 240, 135, 2, 6, 2, True, (0, 1)),
+        "instanced": (lambda: S.instanced(1234, 4, 64), 192, 108, 3, 4, 0, True, (0, 1)),
+        "tiles": (lambda: S.atrium(1234, 20000, 6, 64), 200, 100, 1, 2, 3, True, (2, 3)),
+    }[case]
+    osc = orc.OracleScene(builder().pack(), True)
+    cfg = S.render_config(W, H, spp, seg, rank=part[0], world=part[1], partition=1 if part[1] > 1 else 0)
+    cam = S.camera_default(W, H, frame)
+    a, _, rays_a = osc.render(cfg, cam, use_bvh)
+    b, rays_b = osc.ref_render(cfg, cam, use_bvh)
+    eq = bits_equal(a, b)
+    assert eq.all(), f"{int((~eq.all(axis=2)).sum())} of {W * H} pixels differ"
+    assert rays_a == rays_b and rays_a > W * H // part[1]
+
+
+def test_hit_shading_live_against_reference_glsl(oracle_lib, ref_glsl):
+    """10^5 random hits through the reference's closest_hit.rchit + getTriangleData + getMaterialData against
+    oracle.cpp:get_triangle_data / get_material_data: uv, normal, tangent, geometric normal, material index, albedo,
+    shading normal, emission, roughness, metallic — every word."""
+    from parity_util import random_rays
+    from tools import scene as S
+    if not hasattr(ref_glsl, "ref_shade_hits"):
+        pytest.skip("prebuilt oracle/_ref predates the full-pipeline build")
+    total = 0
+    for builder, extent in ((lambda: S.atrium(1234, 20000, 6, 64), 6.0), (lambda: S.instanced(1234, 4, 64), 30.0),
+                            (lambda: S.random_soup(3, 3000, 3, 7), 8.0), (lambda: S.cornell(), 2.0)):
+        osc = orc.OracleScene(builder().pack(), True)
+        hits = osc.trace(random_rays(17, 60_000, extent, orc.PtRay_dtype))
+        hits = hits[hits["instance"] != 0xFFFFFFFF]
+        a, b = osc.shade_hits(hits), osc.ref_shade_hits(hits)
+        assert len(hits) > 1000 and bits_equal(a, b).all()
+        total += len(hits)
+    assert total >= 100_000

@@ -5,6 +5,10 @@
   reproduce them bit for bit.
 * cornell_64.npz — the oracle's image / primary-hit ids for the Cornell scene (regression + GPU parity
   without needing the oracle's BVH to agree with anything else).
+* raygen_ref_frames.npz — whole frames rendered by the REFERENCE's own ray_gen.rgen main() (+ closest_hit.rchit,
+  miss.rmiss, triangle.glsl, material.glsl, brdf.glsl, rand.glsl) compiled as C++, one invocation per pixel, with the
+  oracle's closest-hit query behind traceRayEXT (the Vulkan driver's part has no source).  The oracle and the CUDA
+  path must reproduce them bit for bit.  REF_FRAMES below is the list of (scene, extent, samples, segments, frame).
 """
 import ctypes as C
 import os
@@ -37,6 +41,25 @@ def bsdf_inputs(seed, n):
     return N, V, kd, f0, rough, xi
 
 
+# name -> (scene builder, W, H, samples, segments, frame_count); every generator is seeded and deterministic
+REF_FRAMES = {
+    "cornell": (lambda: S.cornell(), 64, 64, 2, 3, 5),                              # normal map + albedo map + emissive quad
+    "atrium": (lambda: S.atrium(1234, 20000, 6, 64), 96, 54, 2, 4, 1),            # 6 textured PBR materials, sky, u16 + u32 indices
+    "instanced": (lambda: S.instanced(1234, 4, 64), 80, 45, 2, 4, 2),             # rotated instances: the literal A^-1 normal matrix
+    "soup": (lambda: S.random_soup(3, 3000, 3, 7), 80, 45, 2, 4, 0),              # rotation + non-uniform scale
+}
+
+
+def ref_frames():
+    out = {}
+    for name, (builder, W, H, spp, seg, frame) in REF_FRAMES.items():
+        ps = builder().pack()
+        img, rays = orc.OracleScene(ps, True).ref_render(S.render_config(W, H, spp, seg), S.camera_default(W, H, frame), True)
+        out[name] = img
+        out[name + "_rays"] = np.uint64(rays)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     orc.build()
@@ -60,6 +83,7 @@ def main():
     cfg = S.render_config(64, 64, 2, 3); cam = S.camera_default(64, 64, 5)
     img, ids, rays = osc.render(cfg, cam, False)
     np.savez_compressed(os.path.join(OUT, "cornell_64.npz"), img=img, inst=ids[0], prim=ids[1], tri=ids[2], rays=np.uint64(rays))
+    np.savez_compressed(os.path.join(OUT, "raygen_ref_frames.npz"), **ref_frames())
     print("wrote", os.listdir(OUT))
 
 

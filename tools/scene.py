@@ -632,12 +632,20 @@ def atrium(seed=1234, target_tris=260_000, n_materials=25, tex_size=1024, rough_
     rng = np.random.default_rng(seed)
     sb = SceneBuilder()
     mats = []
+    params = []
     for i in range(n_materials):
         metal = bool(rng.random() < p_metal)
         tint = 0.35 + 0.6 * rng.random(3)
         rough = rough_range[0] + (rough_range[1] - rough_range[0]) * rng.random()
+        params.append((metal, tint, rough))
+    if textures:
+        # every material's maps come from their own generator (seed * 1000 + i): independent, so they are made in parallel
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max(1, min(n_materials, (os.cpu_count() or 4)))) as ex:
+            maps = list(ex.map(lambda i: make_pbr_textures(seed * 1000 + i, tex_size, params[i][1], (0.3, 1.0), params[i][0]), range(n_materials)))
+    for i, (metal, tint, rough) in enumerate(params):
         if textures:
-            a, mr, n = make_pbr_textures(seed * 1000 + i, tex_size, tint, (0.3, 1.0), metal)
+            a, mr, n = maps[i]
             ta, tm, tn = sb.add_texture(a), sb.add_texture(mr), sb.add_texture(n)
             mats.append(sb.add_material((1, 1, 1), rough, 1.0 if metal else 0.0, albedo_tex=ta, mr_tex=tm, normal_tex=tn))
         else:
