@@ -346,12 +346,43 @@ int pt_debug_bvh_digest(PtRenderer* r, uint64_t digest[6]);
  * NULL) receives the device time of the rebuild.  Resets the progressive accumulation. */
 int pt_set_instance_transforms(PtRenderer* r, const float* transforms, size_t num_instances, float* ms_rebuild);
 
-/* Process-wide kernel tuning knobs (measurement only; results never depend on them).
- *   "chunk": rays a K-trace warp takes from the queue per global atomic (default 32).
- *   "postpone": retired (triangle postponing was measured flat and removed); accepted, no effect. */
+/* Kernel tuning knob (measurement only; results never depend on it), applied to renderers created afterwards:
+ *   "chunk": rays a K-trace warp takes from the queue per global atomic (default 32). */
 int pt_set_option(const char* key, int value);
 
-/* Multi-GPU (one process per GPU).  Peer stores: rank 0 exports its image buffer as a CUDA IPC
+/* ------------------------------------------------------------------ multi-GPU combine  (north_star: "per-rank
+ * accumulation buffers are combined with an NCCL reduce over NVLink")
+ * The reference renders on one device; this is the additive multi-GPU surface.  Every rank holds the whole scene and
+ * renders its share — interleaved tiles of one frame (PtRenderConfig.partition = PT_PARTITION_TILES, rank, world) or its
+ * own frames (frame_count = k * world + rank, pt_set_accumulate) — and one reduce(sum) to `root` combines the shares.
+ * NCCL is opened at run time (libnccl.so.2; override with B200PT_NCCL_LIB); without it these calls fail with PT_ERR_NCCL.
+ *
+ *   one process per GPU:   rank 0: pt_comm_unique_id(id) -> ship the 128 bytes to the other ranks (any channel) ->
+ *                          every rank: pt_comm_init(r, rank, world, id)
+ *   one process, N GPUs:   pt_comm_init_all(renderers, n)   (renderer i = rank i; wrap the per-rank reduce calls of one
+ *                          step in pt_comm_group_start / pt_comm_group_end when a single thread issues them)
+ *
+ * pt_reduce_image / pt_reduce_accum: in-place sum of the image / the accumulation buffer over all ranks into root's.
+ * cuda_stream == NULL: the reduce runs on the library's communication stream, ordered after everything enqueued on the
+ * renderer's render stream so far; the renderer's next frame waits for it only before it writes the image again, and
+ * read-backs (pt_read_*) are ordered after it — so a reduce overlaps the ray generation and primary traversal of the next
+ * frame.  Tile shares are disjoint and zero elsewhere, so the reduced image equals the one-GPU image bit for bit; for
+ * frame shares read the mean with pt_read_accum_mean(r, dst, total_frames).  A renderer's siblings use its communicator. */
+int pt_comm_available(int* nccl_version);                          /* 1 when NCCL could be opened (version code in *nccl_version) */
+int pt_comm_unique_id(uint8_t id[128]);                            /* ncclGetUniqueId */
+int pt_comm_init(PtRenderer* r, int rank, int world, const uint8_t id[128]);
+int pt_comm_init_all(PtRenderer** renderers, int n);               /* ncclCommInitAll over the renderers' devices */
+int pt_comm_rank(PtRenderer* r, int* rank, int* world);
+int pt_comm_group_start(void);
+int pt_comm_group_end(void);
+int pt_reduce_image(PtRenderer* r, int root, void* cuda_stream);
+int pt_reduce_accum(PtRenderer* r, int root, void* cuda_stream);
+int pt_comm_destroy(PtRenderer* r);                                /* also done by pt_destroy */
+/* dst.accum += src.accum, dst.frames += src.frames (same device and extent): folds the accumulation of a sibling context
+ * (two frames in flight) into its parent's before the reduce. */
+int pt_add_accum(PtRenderer* dst, PtRenderer* src);
+
+/* Multi-GPU without a collective (one process per GPU).  Peer stores: rank 0 exports its image buffer as a CUDA IPC
  * handle, the other ranks open it and their accumulate kernel writes owned tiles straight into it
  * over NVLink.  `handle` is 64 bytes. */
 int pt_ipc_export_image(PtRenderer* r, uint8_t handle[64]);

@@ -76,6 +76,17 @@ def ref_lib():
     return _ref
 
 
+def ref_alt_lib():
+    """The same reference shaders under the other legal precision reading (glsl_compat.h, GLSL_ALT_PRECISION)."""
+    path = os.path.join(HERE, "_ref", "libref_glsl_alt.so")
+    if not os.path.exists(path):
+        return None
+    R = C.CDLL(path)
+    R.ref_render.restype = C.c_uint64
+    R.ref_render.argtypes = [C.POINTER(PtSceneDesc), C.POINTER(PtRenderConfig), C.POINTER(PtCamera), C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    return R
+
+
 def _fp(a):
     return a.ctypes.data_as(C.c_void_p)
 
@@ -136,12 +147,12 @@ class OracleScene:
 
     # -- the same two through the REFERENCE's own shader sources (oracle/_ref/libref_glsl.so); the acceleration-structure
     # query behind traceRayEXT is this oracle's closest_hit (the Vulkan driver's part has no source)
-    def ref_render(self, cfg, cam, use_bvh=True, nthreads=None):
+    def ref_render(self, cfg, cam, use_bvh=True, nthreads=None, alt=False):
         W, H = cfg.width // max(1, cfg.divider), cfg.height // max(1, cfg.divider)
         rgba = np.zeros((H, W, 4), np.float32)
         nt = nthreads or lib().orc_hardware_threads()
         fn = C.cast(lib().orc_closest_hit_one, C.c_void_p)
-        rays = ref_lib().ref_render(C.byref(self.desc), C.byref(cfg), C.byref(cam), fn, self.handle, 1 if use_bvh else 0, nt, _fp(rgba))
+        rays = (ref_alt_lib() if alt else ref_lib()).ref_render(C.byref(self.desc), C.byref(cfg), C.byref(cam), fn, self.handle, 1 if use_bvh else 0, nt, _fp(rgba))
         return rgba, rays
 
     def ref_shade_hits(self, hits):

@@ -111,13 +111,27 @@ inline uvec2& operator^=(uvec2& a, uvec2 b) { a.x ^= b.x; a.y ^= b.y; return a; 
 inline float dot(vec3 a, vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }                 // [contract] left to right
 inline vec3 cross(vec3 a, vec3 b) { return vec3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }  // 8.5
 inline float sqrt(float x) { return std::sqrt(x); }
+#ifdef GLSL_ALT_PRECISION
+// A second legal reading of the same shaders (oracle/_ref/libref_glsl_alt.so): the textbook forms the GLSL spec prints,
+// normalize(v) = v / length(v), and the C library's fp32 sin/cos (<= 1 ulp).  Used only to MEASURE how far two
+// conforming implementations of the reference drift apart (tests/test_oracle_kat.py states the tolerance).
+inline float sin(float x) { return std::sin(x); }
+inline float cos(float x) { return std::cos(x); }
+#else
 inline float sin(float x) { return (float)std::sin((double)x); }   // [contract] correctly rounded
 inline float cos(float x) { return (float)std::cos((double)x); }
+#endif
 inline float min(float x, float y) { return (y < x) ? y : x; }     // 8.3
 inline float max(float x, float y) { return (x < y) ? y : x; }
 inline float mix(float a, float b, float t) { return a * (1.0f - t) + b * t; }                  // 8.3
 inline vec3 mix(vec3 a, vec3 b, float t) { return vec3(mix(a.x, b.x, t), mix(a.y, b.y, t), mix(a.z, b.z, t)); }
-inline vec3 normalize(vec3 v) { return v * (1.0f / sqrt(dot(v, v))); }                          // [contract] one division
+#ifdef GLSL_ALT_PRECISION
+inline vec3 normalize(vec3 v) { return v / sqrt(dot(v, v)); }
+#else
+// [contract] one division.  The Vulkan spec states normalize()'s precision as inherited from x * inversesqrt(dot(x, x))
+// with inversesqrt() at 2 ulp; 1 / sqrt() with both operations correctly rounded is within that.
+inline vec3 normalize(vec3 v) { return v * (1.0f / sqrt(dot(v, v))); }
+#endif
 inline vec3 reflect(vec3 I, vec3 N) { return I - 2.0f * dot(N, I) * N; }                        // 8.5
 inline vec4 unpackUnorm4x8(uint p) {                                                            // 8.4: f / 255.0
     return vec4((float)(p & 0xffu) / 255.0f, (float)((p >> 8) & 0xffu) / 255.0f, (float)((p >> 16) & 0xffu) / 255.0f, (float)(p >> 24) / 255.0f);

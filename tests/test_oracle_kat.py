@@ -195,3 +195,31 @@ def test_hit_shading_live_against_reference_glsl(oracle_lib, ref_glsl):
         assert len(hits) > 1000 and bits_equal(a, b).all()
         total += len(hits)
     assert total >= 100_000
+
+
+def test_stated_tolerance_between_two_conforming_readings_of_the_reference(oracle_lib, ref_glsl):
+    """north_star: "radiance must agree within a stated per-pixel relative tolerance, with converged-image mean error <= 1 %".
+    Against the reference's shaders under the arithmetic contract (glsl_compat.h [contract] items) the oracle and the CUDA
+    path are bit-exact — tolerance 0.  GLSL leaves normalize() and sin()/cos() precision open, so a second conforming
+    reading (normalize = v / length(v), libm sinf/cosf; libref_glsl_alt.so) is rendered too and the drift between the two is
+    the tolerance that any comparison with a real Vulkan driver has to allow.  Measured here and asserted with margin:
+      * BASELINE's metric shape (1 spp, 2 segments): >= 99.8 % of pixels within 1e-4 relative, every image mean within 0.1 %;
+      * deep paths (4 spp, 5 segments): image mean within 1 % — per-pixel agreement is NOT claimed there: path tracing
+        amplifies a 1-ulp difference at every glossy bounce (atrium: 70 % of pixels within 1e-4, Cornell 99.8 %)."""
+    from tools import scene as S
+    if orc.ref_alt_lib() is None or not hasattr(ref_glsl, "ref_render"):
+        pytest.skip("oracle/_ref/libref_glsl_alt.so not available")
+    for builder, W, H in ((lambda: S.cornell(), 192, 192), (lambda: S.atrium(1234, 20000, 6, 64), 320, 180), (lambda: S.instanced(1234, 4, 64), 320, 180)):
+        osc = orc.OracleScene(builder().pack(), True)
+        for spp, seg in ((1, 2), (4, 5)):
+            cfg, cam = S.render_config(W, H, spp, seg), S.camera_default(W, H, 3)
+            a, _ = osc.ref_render(cfg, cam)
+            b, _ = osc.ref_render(cfg, cam, alt=True)
+            assert (np.isnan(a) == np.isnan(b)).all()
+            a3, b3 = np.nan_to_num(a[..., :3].astype(np.float64)), np.nan_to_num(b[..., :3].astype(np.float64))
+            rel = np.abs(a3 - b3).max(axis=2) / np.maximum(1e-3, np.maximum(a3.max(axis=2), b3.max(axis=2)))
+            mean_err = abs(a3.mean() - b3.mean()) / a3.mean()
+            if seg == 2:
+                assert (rel <= 1e-4).mean() >= 0.998 and mean_err <= 1e-3
+            else:
+                assert mean_err <= 1e-2

@@ -119,6 +119,15 @@ def lib():
         L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
         L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_write_exr.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.pt_comm_available.argtypes = [C.POINTER(C.c_int)]
+        L.pt_comm_unique_id.argtypes = [C.c_void_p]
+        L.pt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.pt_comm_init_all.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+        L.pt_comm_rank.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.pt_reduce_image.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.pt_reduce_accum.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.pt_comm_destroy.argtypes = [C.c_void_p]
+        L.pt_add_accum.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_scene_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
         L.pt_scene_desc.argtypes = [C.c_void_p, C.POINTER(PtSceneDesc)]
         L.pt_scene_free.argtypes = [C.c_void_p]
@@ -131,6 +140,40 @@ def check(status):
     if status != 0:
         L = lib()
         raise PtError(status, L.pt_status_name(status).decode(), (L.pt_last_error() or b"").decode())
+
+
+def comm_available():
+    """NCCL version code when the library could open NCCL, else 0."""
+    v = C.c_int(0)
+    return v.value if lib().pt_comm_available(C.byref(v)) else 0
+
+
+def comm_unique_id():
+    """ncclGetUniqueId: 128 bytes to ship from rank 0 to every other rank."""
+    buf = (C.c_uint8 * 128)()
+    check(lib().pt_comm_unique_id(buf))
+    return bytes(buf)
+
+
+def comm_init_all(renderers):
+    """One process, one renderer per device: renderer i becomes rank i (ncclCommInitAll)."""
+    arr = (C.c_void_p * len(renderers))(*[r.handle for r in renderers])
+    check(lib().pt_comm_init_all(arr, len(renderers)))
+
+
+class comm_group:
+    """ncclGroupStart / ncclGroupEnd around the per-rank reduce calls that ONE thread issues for several devices."""
+
+    def __enter__(self):
+        check(lib().pt_comm_group_start())
+
+    def __exit__(self, *exc):
+        check(lib().pt_comm_group_end())
+        return False
+
+
+def device_count():
+    return lib().pt_device_count()
 
 
 def camera_new(fov, aspect_ratio, position=(0.0, 0.0, 0.0), yaw=0.0, pitch=0.0, frame_count=0):
@@ -302,6 +345,21 @@ class Renderer:
         out = np.empty((self.height, self.width, 4), np.float32)
         check(lib().pt_read_accum_mean(self.handle, out.ctypes.data, total_frames))
         return out
+
+    # -- multi-GPU combine (NCCL inside the library; include/b200pt.h "multi-GPU combine")
+    def comm_init(self, rank, world, unique_id):
+        """One process per GPU: `unique_id` = the 128 bytes of comm_unique_id() made on rank 0."""
+        buf = (C.c_uint8 * 128)(*bytes(unique_id))
+        check(lib().pt_comm_init(self.handle, rank, world, buf))
+
+    def reduce_image(self, root=0, stream=None):
+        check(lib().pt_reduce_image(self.handle, root, stream))
+
+    def reduce_accum(self, root=0, stream=None):
+        check(lib().pt_reduce_accum(self.handle, root, stream))
+
+    def add_accum(self, other):
+        check(lib().pt_add_accum(self.handle, other.handle))
 
     def set_instance_transforms(self, transforms):
         """Animated instances: new (n, 16) row-major matrices, top level rebuilt on the device; returns the ms."""

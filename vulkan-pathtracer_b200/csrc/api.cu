@@ -9,8 +9,7 @@
 #include <map>
 #include <vector>
 
-#include "bvh_build.h"
-#include "render.h"
+#include "renderer.h"
 
 namespace pt {
 
@@ -21,58 +20,7 @@ void set_error(const std::string& msg) { g_last_error = msg; }
 
 using namespace pt;
 
-struct PtRenderer {
-    PtRenderConfig cfg{};
-    int device = 0;
-    int num_sms = 148;
-    cudaStream_t stream = nullptr;
-    cudaStream_t last_stream = nullptr;   // stream of the most recent pt_render (caller's or our own)
-    // pipelined read-back (pt_read_*_overlapped): the copy runs on its own stream, the next frame only
-    // waits for it before its first image write (K-shade of iteration 0)
-    cudaStream_t copy_stream = nullptr;
-    cudaEvent_t ev_frame_done = nullptr, ev_copy_done = nullptr;
-    bool copy_pending = false;
-    // scene on the device
-    Bvh8Tri* d_emissive = nullptr;       // PT_OCCLUSION_LAST variant: the scene's emissive triangles (DeviceScene::emissive_tris)
-    uint8_t* d_blob = nullptr;
-    PrimRec* d_prims = nullptr;
-    MatRec* d_materials = nullptr;
-    TexRec* d_textures = nullptr;
-    std::vector<uint32_t*> d_texels;
-    std::vector<uint4*> d_atlases;   // interleaved material textures (MatRec::atlas)
-    PtInstance* d_instances_raw = nullptr;
-    InstanceRec* d_instances = nullptr;
-    std::vector<PtInstance> h_instances;   // host copy (animated instances: pt_set_instance_transforms)
-    SceneBvh bvh;
-    DeviceScene scene{};
-    uint64_t num_triangles = 0;
-    // frame state
-    PixelMap pm{};
-    PathBuffers pb{};
-    uint32_t max_iters = 0;
-    uint32_t full_w = 0, full_h = 0;     // window extent (resolution-x/-y)
-    float* d_image = nullptr;            // render extent, RGBA32F
-    uint32_t* d_ids = nullptr;           // 3 * W*H
-    uint8_t* d_bgra = nullptr;
-    float* d_upscaled = nullptr;
-    float* d_accum = nullptr;
-    float* d_remote_image = nullptr;     // rank 0's image mapped through CUDA IPC (optional)
-    bool accumulate = false;
-    uint32_t accum_frames = 0;
-    bool profiling = false;
-    TraceMode trace_mode = TRACE_BVH8;
-    std::vector<cudaEvent_t> events;     // profiling: 2 per kernel launch
-    std::vector<int> event_kind;         // 0 trace, 1 shade, 2 other
-    uint32_t last_iters = 0;
-    uint32_t last_launches = 0;
-    PtCamera last_cam{};
-    bool have_last_cam = false;
-    // standalone trace buffers
-    uint32_t* d_cursor = nullptr;
-    bool peer_root = false;   // pt_ipc_export_image was called: other ranks store their tiles into d_image
-    bool owns_scene = true;   // false for a sibling (pt_create_sibling): scene + BVH belong to the parent
-    PtRenderer* parent = nullptr;   // sibling: where the current DeviceScene is read from (the parent may rebuild its top level)
-};
+void comm_release(PtRenderer* r);   // comm.cpp
 
 namespace {
 
@@ -327,6 +275,8 @@ void destroy_impl(PtRenderer* r) {
         r->bvh.release();
     }
     cudaFree(r->d_cursor);
+    comm_release(r);
+    if (r->ev_reduce_done) cudaEventDestroy(r->ev_reduce_done);
     if (r->d_remote_image) cudaIpcCloseMemHandle(r->d_remote_image);
     if (r->copy_stream) { cudaStreamSynchronize(r->copy_stream); cudaStreamDestroy(r->copy_stream); }
     if (r->ev_frame_done) cudaEventDestroy(r->ev_frame_done);
@@ -407,6 +357,7 @@ int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer
         cudaDeviceProp prop;
         if (cudaGetDeviceProperties(&prop, r->device) != cudaSuccess) { set_error("cudaGetDeviceProperties failed"); rc = PT_ERR_CUDA; break; }
         r->num_sms = prop.multiProcessorCount;
+        r->dims = compute_launch_dims(r->num_sms);
         if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); rc = PT_ERR_CUDA; break; }
         if ((rc = upload_scene(r, scene)) != PT_OK) break;
         if ((rc = alloc_frame(r, r->cfg.width, r->cfg.height, r->cfg.divider)) != PT_OK) break;
@@ -462,7 +413,7 @@ static int create_sibling_impl(PtRenderer* parent, const int* part, PtRenderer**
     PtRenderer* r = new PtRenderer();
     r->cfg = parent->cfg;
     if (part) { r->cfg.partition = PT_PARTITION_TILES; r->cfg.rank = part[0]; r->cfg.world = part[1]; }
-    r->device = parent->device; r->num_sms = parent->num_sms; r->owns_scene = false; r->parent = parent;
+    r->device = parent->device; r->num_sms = parent->num_sms; r->dims = parent->dims; r->owns_scene = false; r->parent = parent;
     r->d_blob = parent->d_blob; r->d_prims = parent->d_prims; r->d_materials = parent->d_materials; r->d_textures = parent->d_textures;
     r->d_instances_raw = parent->d_instances_raw; r->d_instances = parent->d_instances;
     r->bvh = parent->bvh; r->scene = parent->scene; r->num_triangles = parent->num_triangles; r->trace_mode = parent->trace_mode;
@@ -489,9 +440,11 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     const size_t px = (size_t)r->pm.width * r->pm.height;
     fp.id_inst = r->d_ids; fp.id_prim = r->d_ids + px; fp.id_tri = r->d_ids + 2 * px;
     PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * 3 * ((size_t)r->max_iters + 2), st));   // counts + both cursor arrays
-    bool waited_copy = !r->copy_pending;
+    bool waited_copy = !r->copy_pending && !r->reduce_pending;
     auto wait_copy = [&]() {   // a pipelined read-back of the previous frame must finish before the image is written again
-        if (!waited_copy) { cudaStreamWaitEvent(st, r->ev_copy_done, 0); waited_copy = true; r->copy_pending = false; }
+        if (!waited_copy) { if (r->copy_pending) cudaStreamWaitEvent(st, r->ev_copy_done, 0); waited_copy = true; r->copy_pending = false; }
+        // ... and so must a reduce of its image / accumulation buffer on the communication stream (comm.cpp)
+        if (r->reduce_pending) { cudaStreamWaitEvent(st, r->ev_reduce_done, 0); r->reduce_pending = false; }
     };
     if (r->pm.world > 1 && !r->d_remote_image && !r->peer_root) wait_copy();
     // tile partition: non-owned pixels must read as 0 for the sum-reduce; not when peers store into this image
@@ -512,10 +465,10 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     if (r->max_iters == 0) wait_copy();   // S == 0 or B == 0: K-raygen itself writes the (black) image
     mark(2); launch_raygen(r->pm, pb, fp, st); mark_end(); ++launches;
     for (uint32_t it = 0; it < r->max_iters; ++it) {
-        mark(0); launch_trace(r->scene, pb, it, mode, r->bvh.tlas2_count, r->bvh.tlas2_leaf_instance, r->num_sms, st); mark_end();
+        mark(0); launch_trace(r->scene, pb, it, mode, r->bvh.tlas2_count, r->bvh.tlas2_leaf_instance, r->dims, st); mark_end();
         if (fp.flags & PT_FLAG_SORT_BY_MATERIAL) { mark(2); launch_material_sort(r->scene, pb, it, r->num_sms, st); mark_end(); launches += 3; }
         wait_copy();
-        mark(1); launch_shade(r->scene, r->pm, pb, fp, it, r->num_sms, st); mark_end();
+        mark(1); launch_shade(r->scene, r->pm, pb, fp, it, r->dims, st); mark_end();
         launches += 2;
     }
     if (r->accumulate) {
@@ -686,6 +639,30 @@ int pt_read_accum_mean(PtRenderer* r, float* host_dst, uint32_t total_frames) {
     return pt_sync(r);
 }
 
+int pt_add_accum(PtRenderer* dst, PtRenderer* src) {
+    PT_REQUIRE(dst && src && dst != src, "pt_add_accum: invalid argument");
+    PT_REQUIRE(dst->device == src->device && dst->pm.width == src->pm.width && dst->pm.height == src->pm.height, "pt_add_accum: device or extent differ");
+    PT_REQUIRE(src->d_accum, "pt_add_accum: the source has no accumulation buffer");
+    PT_CUDA_CHECK(cudaSetDevice(dst->device));
+    const size_t px = (size_t)dst->pm.width * dst->pm.height;
+    cudaStream_t st = follow_stream(dst, nullptr);
+    if (!dst->d_accum) {
+        int rc = dev_alloc(&dst->d_accum, px * 4);
+        if (rc != PT_OK) return rc;
+        PT_CUDA_CHECK(cudaMemsetAsync(dst->d_accum, 0, px * 16, st));
+        dst->accum_frames = 0;
+    }
+    // ordered after the source's frames: an event on its stream, waited for on the destination's
+    cudaEvent_t ev;
+    PT_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    PT_CUDA_CHECK(cudaEventRecord(ev, follow_stream(src, nullptr)));
+    PT_CUDA_CHECK(cudaStreamWaitEvent(st, ev, 0));
+    PT_CUDA_CHECK(cudaEventDestroy(ev));
+    launch_accumulate(src->d_accum, dst->d_accum, (uint32_t)(px * 4), st);
+    dst->accum_frames += src->accum_frames;
+    return PT_OK;
+}
+
 int pt_set_profiling(PtRenderer* r, int enabled) {
     PT_REQUIRE(r, "pt_set_profiling: null renderer");
     r->profiling = enabled != 0;
@@ -734,7 +711,7 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
     if (e == cudaSuccess) e = cudaMemsetAsync(r->d_cursor, 0, 4, r->stream);
     if (e == cudaSuccess) {
         launch_trace_rays(r->scene, d_rays, (uint32_t)n, d_hits, r->trace_mode, r->bvh.tlas2_count,
-                          r->bvh.tlas2_leaf_instance, r->d_cursor, d_setup, r->num_sms, r->stream);
+                          r->bvh.tlas2_leaf_instance, r->d_cursor, d_setup, r->num_sms, r->dims, r->stream);
         e = cudaGetLastError();
     }
     std::vector<HitRec> tmp(n);

@@ -5,7 +5,10 @@
 // --scene-path/-s; help exits 0, a parse error exits 2, a missing scene path prints the reference's
 // message and returns normally.  The window/swapchain loop (main.zig:232-345) becomes `--frames N`
 // iterations of Camera -> RaytracingPass.record with frame_count = 0..N-1, and the present becomes a
-// PFM / EXR / raw BGRA8 file (--output).  Only the C ABI of include/b200pt.h is used.
+// PFM / EXR / raw BGRA8 file (--output).  `--gpus N` (additive) splits every frame into interleaved 32x8
+// tiles over N devices of this process — scene replicated, one renderer per device — and combines the shares with one
+// NCCL reduce to device 0 (pt_comm_init_all / pt_reduce_image / pt_reduce_accum): the written image is bit-identical to
+// the one-GPU image.  Only the C ABI of include/b200pt.h is used.
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -30,6 +33,7 @@ struct Args {
     float position[3] = {0.0f, 0.0f, 0.0f};
     float yaw = 0.0f, pitch = 0.0f;
     int device = 0;
+    uint32_t gpus = 1;
 };
 
 void usage(FILE* f) {
@@ -50,6 +54,7 @@ void usage(FILE* f) {
         "      --camera-path <file>                replay recorded input through Camera.update, one line per frame:\n"
         "                                          <delta_time_s> <keys|-> <mouse_left 0|1> <cursor_dx> <cursor_dy>\n"
         "                                          keys joined by '+': w s a d space left_ctrl left_shift\n"
+        "      --gpus <n>                          tile-partition every frame over devices device..device+n-1, NCCL reduce to the first\n"
         "      --device <ordinal>  --quiet\n",
         f);
 }
@@ -112,6 +117,7 @@ int parse(int argc, char** argv, Args& a) {
         else if (is("--yaw", nullptr)) ok = parse_f32(val, a.yaw);
         else if (is("--pitch", nullptr)) ok = parse_f32(val, a.pitch);
         else if (is("--device", nullptr)) { uint32_t d = 0; ok = parse_u32(val, d); a.device = (int)d; }
+        else if (is("--gpus", nullptr)) ok = parse_u32(val, a.gpus) && a.gpus >= 1 && a.gpus <= 64;
         else if (is("--camera-position", nullptr)) ok = std::sscanf(val, "%f,%f,%f", &a.position[0], &a.position[1], &a.position[2]) == 3;
         else { std::fprintf(stderr, "b200pt: unknown argument %s\n", key.c_str()); return 2; }
         if (!ok) { std::fprintf(stderr, "b200pt: invalid value '%s' for %s\n", val, key.c_str()); return 2; }
@@ -194,14 +200,19 @@ int main(int argc, char** argv) {
     PtRenderConfig cfg;
     std::memset(&cfg, 0, sizeof(cfg));
     cfg.width = a.resolution_x; cfg.height = a.resolution_y; cfg.num_samples = a.num_samples; cfg.num_bounces = a.num_bounces;
-    cfg.divider = a.divider; cfg.device = a.device; cfg.rank = 0; cfg.world = 1; cfg.partition = PT_PARTITION_NONE;
+    cfg.divider = a.divider; cfg.world = (int)a.gpus; cfg.partition = a.gpus > 1 ? PT_PARTITION_TILES : PT_PARTITION_NONE;
     const auto t_create = clock::now();
-    PtRenderer* r = nullptr;
-    st = pt_create(&desc, &cfg, &r);                                              // RaytracingPass.init, main.zig:196-206
+    std::vector<PtRenderer*> rs(a.gpus, nullptr);
+    for (uint32_t g = 0; g < a.gpus && st == PT_OK; ++g) {                         // scene replicated per device
+        cfg.device = a.device + (int)g; cfg.rank = (int)g;
+        st = pt_create(&desc, &cfg, &rs[g]);                                      // RaytracingPass.init, main.zig:196-206
+    }
     pt_scene_free(scene);                                                         // `defer scene.deinit()`, RaytracingPass.zig:103
     if (st != PT_OK) return die("RaytracingPass.init", st);
+    if (a.gpus > 1 && (st = pt_comm_init_all(rs.data(), (int)a.gpus)) != PT_OK) return die("pt_comm_init_all", st);
+    PtRenderer* r = rs[0];
     const double create_s = std::chrono::duration<double>(clock::now() - t_create).count();
-    if (a.accumulate) pt_set_accumulate(r, 1);
+    if (a.accumulate) for (PtRenderer* q : rs) pt_set_accumulate(q, 1);
 
     const float aspect = (float)a.resolution_x / (float)a.resolution_y;           // main.zig:222
     PtCameraState camera;
@@ -219,15 +230,23 @@ int main(int argc, char** argv) {
             st = pt_camera_new(3.14159265358979323846f * 0.25f, aspect, a.position, a.yaw, a.pitch, frame, &cam);
         }
         if (st != PT_OK) return die("Camera.update", st);
-        st = pt_render(r, &cam, nullptr);                                         // RaytracingPass.record, main.zig:263-270
-        if (st != PT_OK) return die("RaytracingPass.record", st);
+        for (PtRenderer* q : rs) {                                                // asynchronous: the devices run side by side
+            st = pt_render(q, &cam, nullptr);                                     // RaytracingPass.record, main.zig:263-270
+            if (st != PT_OK) return die("RaytracingPass.record", st);
+        }
         if (!a.quiet) {
             PtStats s;
-            if (pt_get_stats(r, &s) == PT_OK) rays += s.rays_traced;              // synchronises: the frame fence
+            for (PtRenderer* q : rs) if (pt_get_stats(q, &s) == PT_OK) rays += s.rays_traced;   // synchronises: the frame fence
         }
     }
-    st = pt_sync(r);
-    if (st != PT_OK) return die("pt_sync", st);
+    if (a.gpus > 1) {
+        // the shares are disjoint and zero elsewhere: one reduce(sum) of the last frame (or of the accumulation buffers)
+        st = pt_comm_group_start();
+        for (PtRenderer* q : rs) if (st == PT_OK) st = a.accumulate ? pt_reduce_accum(q, 0, nullptr) : pt_reduce_image(q, 0, nullptr);
+        if (st == PT_OK) st = pt_comm_group_end();
+        if (st != PT_OK) return die("NCCL reduce", st);
+    }
+    for (PtRenderer* q : rs) if ((st = pt_sync(q)) != PT_OK) return die("pt_sync", st);
     const double render_s = std::chrono::duration<double>(clock::now() - t0).count();
 
     uint32_t w = 0, h = 0;
@@ -266,10 +285,11 @@ int main(int argc, char** argv) {
         // Stats.zig:68-87: frames over the wall window and the mean frame time
         std::printf("scene: %llu triangles, %llu BVH8 nodes (%.1f MB), load %.2f s, init %.2f s (device build %.2f ms)\n",
                     (unsigned long long)s.num_triangles, (unsigned long long)s.bvh_nodes, s.bvh_bytes / 1.0e6, load_s, create_s, s.ms_build);
+        if (a.gpus > 1) std::printf("gpus: %u (interleaved 32x8 tiles, NCCL reduce to device %d)\n", a.gpus, a.device);
         std::printf("frames: %u at %ux%u, %u spp, %u segments: %.3f ms/frame, %.1f fps, %.1f spp/s, %.1f Mrays/s -> %s\n", a.frames, w, h,
                     a.num_samples, a.num_bounces, 1e3 * render_s / a.frames, a.frames / render_s, a.num_samples * a.frames / render_s,
                     rays / render_s / 1e6, a.output.c_str());
     }
-    pt_destroy(r);                                                                // RaytracingPass.deinit, main.zig:206
+    for (PtRenderer* q : rs) pt_destroy(q);                                       // RaytracingPass.deinit, main.zig:206
     return 0;
 }

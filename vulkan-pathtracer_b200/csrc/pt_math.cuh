@@ -7,6 +7,7 @@
 // in double and rounded to float; min/max follow GLSL 8.3 (min(x,y) = y<x ? y : x).
 #pragma once
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
 
 namespace pt {

@@ -445,7 +445,8 @@ __global__ void k_upscale(const float4* __restrict__ src, uint32_t sw, uint32_t 
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= dw * dh) return;
     const uint32_t x = i % dw, y = i / dw;
-    const uint32_t sx = min(sw - 1u, (uint32_t)(((uint64_t)x * sw) / dw)), sy = min(sh - 1u, (uint32_t)(((uint64_t)y * sh) / dh));
+    // vkCmdBlitImage with VK_FILTER_NEAREST samples the source at the destination texel's centre: floor((x + 0.5) * sw / dw)
+    const uint32_t sx = min(sw - 1u, (uint32_t)(((2ull * x + 1ull) * sw) / (2ull * dw))), sy = min(sh - 1u, (uint32_t)(((2ull * y + 1ull) * sh) / (2ull * dh)));
     dst[i] = src[(size_t)sy * sw + sx];
 }
 
@@ -511,12 +512,23 @@ int persistent_blocks(K kernel, int threads, int num_sms) {
 
 }  // namespace
 
-// tuning knobs; see pt_set_option
-static uint32_t g_chunk = 32;
+// tuning knob (pt_set_option): default fetch granularity of renderers created afterwards
+static uint32_t g_default_chunk = 32;
 int set_option(const char* key, int value) {
-    if (!strcmp(key, "chunk")) { g_chunk = (uint32_t)(value < 1 ? 1 : value); return 0; }   // K-trace: rays per queue atomic
-    if (!strcmp(key, "postpone")) return 0;   // retired knob (triangle postponing was removed from K-trace); accepted, no effect
+    if (!strcmp(key, "chunk")) { g_default_chunk = (uint32_t)(value < 1 ? 1 : value); return 0; }   // K-trace: rays per queue atomic
     return -1;
+}
+
+LaunchDims compute_launch_dims(int num_sms) {
+    LaunchDims d;
+    d.trace_walker = persistent_blocks(k_trace<TRACE_BVH8>, kTraceThreads, num_sms);
+    d.trace_bvh2 = persistent_blocks(k_trace<TRACE_BVH2>, kTraceThreads, num_sms);
+    d.trace_count = persistent_blocks(k_trace<TRACE_BVH8_COUNT>, kTraceThreads, num_sms);
+    d.trace_persistent = persistent_blocks(k_trace_persistent, kTraceBlock, num_sms);
+    d.shade_single = persistent_blocks(k_shade<false>, kShadeThreads, num_sms);
+    d.shade_multi = persistent_blocks(k_shade<true>, kShadeThreads, num_sms);
+    d.chunk = g_default_chunk;
+    return d;
 }
 
 void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st) {
@@ -525,25 +537,18 @@ void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams&
 }
 
 void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
-                  const uint32_t* tlas2_leaf_instance, int num_sms, cudaStream_t st) {
-    static int blocks[4] = {0, 0, 0, 0};
-    if (!blocks[0]) {
-        blocks[0] = persistent_blocks(k_trace<TRACE_BVH8>, kTraceThreads, num_sms);
-        blocks[1] = persistent_blocks(k_trace<TRACE_BVH2>, kTraceThreads, num_sms);
-        blocks[2] = persistent_blocks(k_trace<TRACE_BVH8_COUNT>, kTraceThreads, num_sms);
-        blocks[3] = persistent_blocks(k_trace_persistent, kTraceBlock, num_sms);
-    }
+                  const uint32_t* tlas2_leaf_instance, const LaunchDims& dims, cudaStream_t st) {
     if (mode == TRACE_BVH8) {
         TraceIO io;
         io.queue = pb.queue[iter & 1u]; io.count_ptr = pb.qcount + iter; io.count = 0; io.cursor = pb.trace_next + iter;
         io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.ray_e = pb.ray_e; io.ray_s = pb.ray_s; io.ray_m = pb.ray_m; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
-        io.hit_a_stride = 1; io.hit_b_stride = 1; io.bias_word = 0x4B000000u; io.chunk = g_chunk;
-        k_trace_persistent<<<blocks[3], kTraceBlock, 0, st>>>(sc, io);
+        io.hit_a_stride = 1; io.hit_b_stride = 1; io.bias_word = 0x4B000000u; io.chunk = dims.chunk;
+        k_trace_persistent<<<dims.trace_persistent, kTraceBlock, 0, st>>>(sc, io);
         return;
     }
-    if (mode == TRACE_BVH2) k_trace<TRACE_BVH2><<<blocks[1], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
-    else if (mode == TRACE_BVH8_COUNT) k_trace<TRACE_BVH8_COUNT><<<blocks[2], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
-    else k_trace<TRACE_BVH8><<<blocks[0], kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
+    if (mode == TRACE_BVH2) k_trace<TRACE_BVH2><<<dims.trace_bvh2, kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
+    else if (mode == TRACE_BVH8_COUNT) k_trace<TRACE_BVH8_COUNT><<<dims.trace_count, kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
+    else k_trace<TRACE_BVH8><<<dims.trace_walker, kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
 }
 
 void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, int num_sms, cudaStream_t st) {
@@ -555,16 +560,14 @@ void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t
 }
 
 void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
-                  int num_sms, cudaStream_t st) {
-    static int blocks[2] = {0, 0};
-    if (!blocks[0]) { blocks[0] = persistent_blocks(k_shade<false>, kShadeThreads, num_sms); blocks[1] = persistent_blocks(k_shade<true>, kShadeThreads, num_sms); }
-    if (fp.num_samples > 1u) k_shade<true><<<blocks[1], kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
-    else k_shade<false><<<blocks[0], kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+                  const LaunchDims& dims, cudaStream_t st) {
+    if (fp.num_samples > 1u) k_shade<true><<<dims.shade_multi, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+    else k_shade<false><<<dims.shade_single, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
 }
 
 void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
                        uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, float4* setup, int num_sms,
-                       cudaStream_t st) {
+                       const LaunchDims& dims, cudaStream_t st) {
     const int blocks = num_sms * 4;
     if (mode == TRACE_BVH8) {
         static_assert(sizeof(RayRec) == 32 && sizeof(HitRec) == 32, "AoS strides");
@@ -575,7 +578,7 @@ void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, Hi
         io.ray_o = so; io.ray_d = sd; io.ray_e = se; io.ray_s = ss; io.ray_m = sm;
         io.hit_a = reinterpret_cast<float4*>(hits); io.hit_a_stride = 2;
         io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4;
-        io.bias_word = 0x4B000000u; io.chunk = g_chunk;
+        io.bias_word = 0x4B000000u; io.chunk = dims.chunk;
         k_trace_persistent<<<blocks, kTraceBlock, 0, st>>>(sc, io);
         return;
     }

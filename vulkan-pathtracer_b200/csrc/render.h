@@ -52,17 +52,26 @@ struct FrameParams {
 // TRACE_BVH2: walker over the LBVH binary trees.
 enum TraceMode { TRACE_BVH8 = 0, TRACE_BVH2 = 1, TRACE_BVH8_COUNT = 2, TRACE_BVH8_WALKER = 3 };
 
+// Persistent grid sizes (resident CTAs per SM x SM count of the renderer's device) and the K-trace fetch granularity;
+// computed once per renderer in pt_create, after cudaSetDevice (renderers on different devices do not share them).
+struct LaunchDims {
+    int trace_persistent = 0, trace_walker = 0, trace_bvh2 = 0, trace_count = 0;
+    int shade_single = 0, shade_multi = 0;
+    uint32_t chunk = 32;          // rays a K-trace warp takes from the queue per global atomic
+};
+LaunchDims compute_launch_dims(int num_sms);
+
 void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st);
 void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
-                  const uint32_t* tlas2_leaf_instance, int num_sms, cudaStream_t st);
+                  const uint32_t* tlas2_leaf_instance, const LaunchDims& dims, cudaStream_t st);
 // PT_FLAG_SORT_BY_MATERIAL: counting sort of queue `iter` by the material of each path's hit (misses last)
 void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, int num_sms, cudaStream_t st);
 void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
-                  int num_sms, cudaStream_t st);
+                  const LaunchDims& dims, cudaStream_t st);
 // standalone closest-hit queries (pt_trace_rays)
 void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
                        uint32_t tlas2_count, const uint32_t* tlas2_leaf_instance, uint32_t* cursor, float4* setup /* 5*n */,
-                       int num_sms, cudaStream_t st);
+                       int num_sms, const LaunchDims& dims, cudaStream_t st);
 // material texture interleave (MatRec::atlas): out[i] = (t0[i], t1[i], t2[i], t3[i]); absent maps read as 0xFFFFFFFF
 void launch_interleave_textures(const uint32_t* t0, const uint32_t* t1, const uint32_t* t2, const uint32_t* t3, size_t n, uint4* out,
                                 cudaStream_t st);
