@@ -119,15 +119,16 @@ def lib():
         L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
         L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.pt_write_exr.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
-        L.pt_comm_available.argtypes = [C.POINTER(C.c_int)]
-        L.pt_comm_unique_id.argtypes = [C.c_void_p]
-        L.pt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
-        L.pt_comm_init_all.argtypes = [C.POINTER(C.c_void_p), C.c_int]
-        L.pt_comm_rank.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
-        L.pt_reduce_image.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
-        L.pt_reduce_accum.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
-        L.pt_comm_destroy.argtypes = [C.c_void_p]
-        L.pt_add_accum.argtypes = [C.c_void_p, C.c_void_p]
+        if hasattr(L, "pt_comm_init"):      # absent only from A/B variant builds that predate the multi-GPU surface (B200PT_LIB)
+            L.pt_comm_available.argtypes = [C.POINTER(C.c_int)]
+            L.pt_comm_unique_id.argtypes = [C.c_void_p]
+            L.pt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+            L.pt_comm_init_all.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+            L.pt_comm_rank.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+            L.pt_reduce_image.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+            L.pt_reduce_accum.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+            L.pt_comm_destroy.argtypes = [C.c_void_p]
+            L.pt_add_accum.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_scene_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
         L.pt_scene_desc.argtypes = [C.c_void_p, C.POINTER(PtSceneDesc)]
         L.pt_scene_free.argtypes = [C.c_void_p]
