@@ -45,7 +45,10 @@ typedef enum PtStatus {
     PT_ERR_TOO_MANY_SCENES = -22,         /* error.TooManyScenes           Scene.zig:496 */
     PT_ERR_IMAGE_DECODE = -23,            /* stb_image failure             stb_image.zig:11-18 */
     PT_ERR_INVALID_INDEX_TYPE = -24,      /* `unreachable` at Scene.zig:252-256 (u8 indices) */
-    PT_ERR_NCCL = -30
+    PT_ERR_NCCL = -30,                    /* NCCL missing or a communicator error (multi-GPU combine) */
+    PT_ERR_TRAVERSAL_STACK = -31          /* a ray needed more traversal stack than the kernels have (64 entries): the
+                                             hierarchy is pathologically deep; reported by pt_sync / pt_get_stats instead
+                                             of an image with missed hits */
 } PtStatus;
 
 /* ------------------------------------------------------------------ scene data contract
@@ -138,8 +141,14 @@ enum {
                                              the Morton radix tree (LBVH): slower build, better trees for irregular meshes */
     PT_FLAG_BVH_SAH = 1u << 6,            /* build the binary hierarchy top-down by binned SAH on the GPU (32 bins x 3 axes
                                              per segment, level-synchronous; csrc/bvh_sah.cuh).  Takes precedence over PLOC */
-    PT_FLAG_BVH_OPTIMAL_COLLAPSE = 1u << 7 /* BVH2 -> BVH8 by the cost-optimal collapse (dynamic programme of Ylitie et al.
+    PT_FLAG_BVH_OPTIMAL_COLLAPSE = 1u << 7, /* BVH2 -> BVH8 by the cost-optimal collapse (dynamic programme of Ylitie et al.
                                              2017) instead of the greedy surface-area expansion; LBVH and SAH hierarchies */
+    PT_FLAG_RUSSIAN_ROULETTE = 1u << 8    /* EXTENSION, off by default and outside every parity claim against the reference
+                                             (which has none, ray_gen.rgen:49-97): after the throughput update of a bounce
+                                             (:95), from the second bounce on, the path survives with probability
+                                             p = clamp(max(atten.rgb), 0.05, 1) decided by one more pcg2d draw (xi.x < p) and
+                                             atten /= p — unbiased, fewer deep low-throughput segments.  The oracle implements
+                                             the same rule (same flag), so GPU == oracle still holds bit for bit. */
 };
 
 typedef struct PtRenderConfig {
@@ -185,7 +194,7 @@ typedef struct PtRay {
 
 typedef struct PtStats {
     uint64_t rays_traced;        /* closest-hit queries executed by the last pt_render */
-    uint64_t rays_hit;
+    uint64_t rays_hit;           /* ... of which hit geometry (the rest ended in the sky) */
     uint32_t wavefront_iterations;
     uint32_t kernel_launches;    /* kernels launched by the last pt_render */
     float ms_trace;              /* CUDA-event time of the traversal launches of the last frame

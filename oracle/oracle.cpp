@@ -748,7 +748,7 @@ static inline MaterialData get_material_data(const SceneView& sv, const Triangle
 struct PixelOut { V3 color; PtHit primary; uint64_t rays; };
 
 static inline PixelOut shade_pixel(const SceneView& sv, const PtCamera& cam, uint32_t x, uint32_t y, uint32_t W, uint32_t H,
-                                   uint32_t S, uint32_t B, bool use_bvh) {
+                                   uint32_t S, uint32_t B, bool use_bvh, uint32_t flags = 0) {
     PixelOut out; out.rays = 0;
     const float px = (float)x + 0.5f, py = (float)y + 0.5f;                     // :34
     const float u = px / (float)W, v = py / (float)H;                           // :35
@@ -798,6 +798,16 @@ static inline PixelOut shade_pixel(const SceneView& sv, const PtCamera& cam, uin
                 float lambert_in = dot(s.normal, direction);                    // :90
                 if (lambert_in <= 0.0f) break;                                  // :91-93
                 atten = atten * (brdf(s, direction) * lambert_in / density);    // :95
+                // PT_FLAG_RUSSIAN_ROULETTE (extension, not in the reference; include/b200pt.h): from the second bounce on the
+                // path survives with probability p = clamp(max(atten), 0.05, 1), one more pcg2d draw decides
+                if ((flags & PT_FLAG_RUSSIAN_ROULETTE) && j >= 1) {
+                    const float p = gmin(1.0f, gmax(0.05f, gmax(atten.x, gmax(atten.y, atten.z))));
+                    if (p < 1.0f) {
+                        const V2 xr = pcg2d(seed);
+                        if (!(xr.x < p)) break;
+                        atten = atten / p;
+                    }
+                }
                 // statistic for DESIGN.md section 10: last segments about to be traced with a throughput of exactly zero (brdf()
                 // returns 0 when the shading normal faces away from the viewer)
                 if (g_count_dead && j + 2 == B && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) g_dead_rays.fetch_add(1, std::memory_order_relaxed);
@@ -848,7 +858,7 @@ uint64_t orc_render(const OrcScene* s, const PtRenderConfig* cfg, const PtCamera
                     uint32_t tile = (y / 8) * tiles_x + (x / 32);
                     if ((int)(tile % (uint32_t)cfg->world) != cfg->rank) continue;
                 }
-                PixelOut po = shade_pixel(s->sv, *cam, x, y, W, H, cfg->num_samples, cfg->num_bounces, use_bvh != 0);
+                PixelOut po = shade_pixel(s->sv, *cam, x, y, W, H, cfg->num_samples, cfg->num_bounces, use_bvh != 0, cfg->flags);
                 local += po.rays;
                 size_t i = (size_t)y * W + x;
                 if (rgba) { rgba[4 * i + 0] = po.color.x; rgba[4 * i + 1] = po.color.y; rgba[4 * i + 2] = po.color.z; rgba[4 * i + 3] = 1.0f; }
@@ -884,7 +894,7 @@ uint64_t orc_render_rows(const OrcScene* s, const PtRenderConfig* cfg, const PtC
             if (r >= nrows) break;
             uint32_t y = y0 + r * row_step;
             for (uint32_t x = 0; x < W; ++x) {
-                PixelOut po = shade_pixel(s->sv, *cam, x, y, W, H, cfg->num_samples, cfg->num_bounces, use_bvh != 0);
+                PixelOut po = shade_pixel(s->sv, *cam, x, y, W, H, cfg->num_samples, cfg->num_bounces, use_bvh != 0, cfg->flags);
                 local += po.rays;
                 size_t i = (size_t)y * W + x;
                 if (rgba) { rgba[4 * i + 0] = po.color.x; rgba[4 * i + 1] = po.color.y; rgba[4 * i + 2] = po.color.z; rgba[4 * i + 3] = 1.0f; }

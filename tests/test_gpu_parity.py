@@ -324,6 +324,9 @@ def test_ray_counts_and_stats(sponza):
     img, ids, st = render(sponza, 640, 360, 1, 2)
     hit = int((ids[0] != 0xFFFFFFFF).sum())
     assert 640 * 360 <= st.rays_traced <= 640 * 360 + hit
+    assert hit <= st.rays_hit < st.rays_traced
+    _, ids1, st1 = render(sponza, 640, 360, 1, 1)                 # one segment: the hits are the primary hits
+    assert st1.rays_traced == 640 * 360 and st1.rays_hit == int((ids1[0] != 0xFFFFFFFF).sum())
     assert st.kernel_launches == 1 + 2 * 2 and st.bvh_nodes > 0 and st.ms_build > 0
 
 
@@ -337,6 +340,44 @@ def test_bgra8_is_the_reference_storage_format():
     assert np.array_equal(b[..., 0], q[..., 2]) and np.array_equal(b[..., 1], q[..., 1]) and np.array_equal(b[..., 2], q[..., 0])
     assert (b[..., 3] == 255).all()
     r.deinit()
+
+
+def test_divider_blit_samples_texel_centres_on_non_divisible_extents():
+    """vkCmdBlitImage with VK_FILTER_NEAREST (RaytracingPass.zig:599-635) reads the source texel under the destination texel's
+    centre, floor((x + 0.5) * sw / dw); with 1921 / 2 -> 960 that differs from floor(x * sw / dw) from x = 2 on."""
+    ps = S.cornell().pack()
+    r = b200pt.Renderer(ps, 1921, 101, 1, 1, divider=2)
+    assert (r.width, r.height) == (960, 50)
+    r.record(S.camera_default(1921, 101, 0)); r.sync()
+    small, up = r.image(), r.image_upscaled()
+    assert up.shape == (101, 1921, 4)
+    sx = np.minimum(959, ((2 * np.arange(1921) + 1) * 960) // (2 * 1921))
+    sy = np.minimum(49, ((2 * np.arange(101) + 1) * 50) // (2 * 101))
+    assert sx[2] == 1 and (2 * 960) // 1921 == 0                                    # the case the advisor named
+    assert np.array_equal(up, small[sy][:, sx])
+    r.deinit()
+
+
+def test_russian_roulette_extension_matches_the_oracle_and_is_unbiased():
+    """PT_FLAG_RUSSIAN_ROULETTE (north_star (c); SURVEY Q11: opt-in, default off, excluded from parity with the reference).
+    GPU == oracle bit for bit with the flag on both sides; fewer rays; the mean over frames stays within noise."""
+    ps = S.cornell().pack()
+    W, H, spp, seg = 96, 96, 4, 8
+    RR = b200pt.PT_FLAG_RUSSIAN_ROULETTE
+    img, ids, st = render(ps, W, H, spp, seg, 1, flags=RR)
+    cfg = S.render_config(W, H, spp, seg, flags=RR)
+    oimg, oids, orays = orc.OracleScene(ps, True).render(cfg, S.camera_default(W, H, 1), True)
+    assert bits_equal(img, oimg).all() and all((a == b).all() for a, b in zip(ids, oids))
+    plain, _, st0 = render(ps, W, H, spp, seg, 1)
+    assert st.rays_traced < st0.rays_traced and not bits_equal(img, plain).all()
+    acc = {0: np.zeros(3), RR: np.zeros(3)}
+    for flags in acc:
+        r = b200pt.Renderer(ps, W, H, 16, seg, flags=flags)
+        for f in range(8):
+            r.record(S.camera_default(W, H, f)); r.sync()
+            acc[flags] += np.nan_to_num(r.image()[..., :3]).reshape(-1, 3).mean(axis=0)
+        r.deinit()
+    assert np.allclose(acc[RR], acc[0], rtol=0.02)
 
 
 def test_divider_upscale_and_resize():

@@ -71,8 +71,10 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
 #define A(ptr, cnt) if ((rc = dev_alloc(&(ptr), (cnt))) != PT_OK) return rc
     A(b.ray_o, n); A(b.ray_d, n); A(b.ray_e, n); A(b.ray_s, n); A(b.ray_m, n); A(b.hit_a, n); A(b.hit_b, n); { const size_t np = r->cfg.num_samples > 1 ? n : 1; A(b.prim_a, np); A(b.prim_b, np); A(b.prim_c, np); A(b.prim_d, np); }
     A(b.atten_sx, n); A(b.color_sy, n); A(b.final_sb, n); A(b.queue[0], n); A(b.queue[1], n); A(b.queue_sorted, n); A(b.sort_bins, (size_t)r->scene.num_materials + 4);
-    A(b.qcount, 3 * ((size_t)r->max_iters + 2)); A(b.trav_counters, 4);
+    b.frame_words = 3u * (r->max_iters + 2u) + 4u;
+    A(b.qcount, b.frame_words); A(b.trav_counters, 4);
     b.trace_next = b.qcount + ((size_t)r->max_iters + 2); b.shade_next = b.trace_next + ((size_t)r->max_iters + 2);
+    b.hit_count = reinterpret_cast<unsigned long long*>(b.qcount + ((3u * (r->max_iters + 2u) + 1u) & ~1u));   // 8-byte aligned (cudaMalloc base is)
     const size_t px = (size_t)pm.width * pm.height;
     A(r->d_image, px * 4); A(r->d_ids, px * 3);
 #undef A
@@ -219,6 +221,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     sc.triangle_data = r->d_blob; sc.prims = r->d_prims; sc.materials = r->d_materials; sc.textures = r->d_textures;
     sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.node_bits = r->bvh.node_bits8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
     sc.nodes2 = r->bvh.nodes2; sc.tris2 = r->bvh.tris2; sc.tlas2 = r->bvh.tlas2; sc.tlas_root = r->bvh.tlas_root8;
+    PT_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&sc.error_flag), r->h_error, 0));
     sc.num_instances = (uint32_t)inst.size(); sc.num_prims = (uint32_t)prims.size();
     sc.num_materials = (uint32_t)s->num_materials; sc.num_textures = (uint32_t)s->num_textures;
 #ifdef PT_OCCLUSION_LAST
@@ -275,6 +278,7 @@ void destroy_impl(PtRenderer* r) {
         r->bvh.release();
     }
     cudaFree(r->d_cursor);
+    if (r->owns_scene && r->h_error) cudaFreeHost(r->h_error);
     comm_release(r);
     if (r->ev_reduce_done) cudaEventDestroy(r->ev_reduce_done);
     if (r->d_remote_image) cudaIpcCloseMemHandle(r->d_remote_image);
@@ -330,6 +334,7 @@ const char* pt_status_name(int s) {
         case PT_ERR_IMAGE_DECODE: return "ImageDecodeError";
         case PT_ERR_INVALID_INDEX_TYPE: return "InvalidIndexType";
         case PT_ERR_NCCL: return "NcclError";
+        case PT_ERR_TRAVERSAL_STACK: return "TraversalStackOverflow";
         default: return "Unknown";
     }
 }
@@ -359,6 +364,8 @@ int pt_create(const PtSceneDesc* scene, const PtRenderConfig* config, PtRenderer
         r->num_sms = prop.multiProcessorCount;
         r->dims = compute_launch_dims(r->num_sms);
         if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); rc = PT_ERR_CUDA; break; }
+        if (cudaHostAlloc(reinterpret_cast<void**>(&r->h_error), 4, cudaHostAllocMapped) != cudaSuccess) { set_error("cudaHostAlloc failed"); rc = PT_ERR_CUDA; break; }
+        *r->h_error = 0u;
         if ((rc = upload_scene(r, scene)) != PT_OK) break;
         if ((rc = alloc_frame(r, r->cfg.width, r->cfg.height, r->cfg.divider)) != PT_OK) break;
         if ((rc = dev_alloc(&r->d_cursor, 4)) != PT_OK) break;
@@ -413,7 +420,7 @@ static int create_sibling_impl(PtRenderer* parent, const int* part, PtRenderer**
     PtRenderer* r = new PtRenderer();
     r->cfg = parent->cfg;
     if (part) { r->cfg.partition = PT_PARTITION_TILES; r->cfg.rank = part[0]; r->cfg.world = part[1]; }
-    r->device = parent->device; r->num_sms = parent->num_sms; r->dims = parent->dims; r->owns_scene = false; r->parent = parent;
+    r->device = parent->device; r->num_sms = parent->num_sms; r->dims = parent->dims; r->h_error = parent->h_error; r->owns_scene = false; r->parent = parent;
     r->d_blob = parent->d_blob; r->d_prims = parent->d_prims; r->d_materials = parent->d_materials; r->d_textures = parent->d_textures;
     r->d_instances_raw = parent->d_instances_raw; r->d_instances = parent->d_instances;
     r->bvh = parent->bvh; r->scene = parent->scene; r->num_triangles = parent->num_triangles; r->trace_mode = parent->trace_mode;
@@ -439,7 +446,7 @@ static int render_impl(PtRenderer* r, const PtCamera* camera, cudaStream_t st, T
     fp.image = r->d_remote_image ? r->d_remote_image : r->d_image;
     const size_t px = (size_t)r->pm.width * r->pm.height;
     fp.id_inst = r->d_ids; fp.id_prim = r->d_ids + px; fp.id_tri = r->d_ids + 2 * px;
-    PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * 3 * ((size_t)r->max_iters + 2), st));   // counts + both cursor arrays
+    PT_CUDA_CHECK(cudaMemsetAsync(pb.qcount, 0, sizeof(uint32_t) * pb.frame_words, st));   // counts + both cursor arrays + hit counter
     bool waited_copy = !r->copy_pending && !r->reduce_pending;
     auto wait_copy = [&]() {   // a pipelined read-back of the previous frame must finish before the image is written again
         if (!waited_copy) { if (r->copy_pending) cudaStreamWaitEvent(st, r->ev_copy_done, 0); waited_copy = true; r->copy_pending = false; }
@@ -503,6 +510,10 @@ int pt_sync(PtRenderer* r) {
     if (r->last_stream && r->last_stream != r->stream) PT_CUDA_CHECK(cudaStreamSynchronize(r->last_stream));
     PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
     if (r->copy_stream) PT_CUDA_CHECK(cudaStreamSynchronize(r->copy_stream));
+    if (r->h_error && *reinterpret_cast<volatile uint32_t*>(r->h_error)) {
+        set_error("a ray needed more than the 64 traversal stack entries of the kernels: the acceleration structure is too deep");
+        return PT_ERR_TRAVERSAL_STACK;
+    }
     return PT_OK;
 }
 
@@ -675,6 +686,9 @@ int pt_get_stats(PtRenderer* r, PtStats* out) {
     { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     std::vector<uint32_t> q((size_t)r->max_iters + 2, 0);
     PT_CUDA_CHECK(cudaMemcpy(q.data(), r->pb.qcount, q.size() * 4, cudaMemcpyDeviceToHost));
+    unsigned long long hits = 0;
+    PT_CUDA_CHECK(cudaMemcpy(&hits, r->pb.hit_count, 8, cudaMemcpyDeviceToHost));
+    out->rays_hit = hits;
     uint32_t its = 0;
     for (uint32_t i = 0; i < r->last_iters; ++i) { out->rays_traced += q[i]; if (q[i]) its = i + 1; }
     out->wavefront_iterations = its;

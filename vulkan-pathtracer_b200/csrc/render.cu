@@ -252,6 +252,7 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
     for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) s_unorm[i] = (float)i / 255.0f;
     __syncthreads();
     uint32_t* cursor = pb.shade_next + iter;
+    uint32_t n_hit = 0;     // entries of this thread whose traced segment hit geometry (PtStats::rays_hit)
     for (;;) {
         uint32_t base = 0;
         if ((threadIdx.x & 31u) == 0u) base = atomicAdd(cursor, 32u);
@@ -288,6 +289,7 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
             // geometric normal) are cached at iteration 0 and a restarted sample reads them back instead of
             // re-fetching vertices, material and texels: same values, hence the same bits, without the chain of
             // dependent loads (K-shade is latency-bound on multi-sample workloads).
+            n_hit += h.t != kMissT ? 1u : 0u;
             const bool keep_primary = kMulti && iter == 0u && !(fp.flags & PT_FLAG_NO_PRIMARY_REUSE);
             if (iter == 0u) {
                 const size_t pi = (size_t)y * pm.width + x;
@@ -355,6 +357,15 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                             atten = atten * (brdf(si, direction) * lambert_in / density);   // :95
                             ++j;
                             emit = true;
+                            // PT_FLAG_RUSSIAN_ROULETTE (extension, off by default; include/b200pt.h): same rule as the oracle's
+                            if ((fp.flags & PT_FLAG_RUSSIAN_ROULETTE) && j >= 2u) {
+                                const float p = gmin(1.0f, gmax(0.05f, gmax(atten.x, gmax(atten.y, atten.z))));
+                                if (p < 1.0f) {
+                                    const V2 xr = pcg2d(seed);
+                                    if (!(xr.x < p)) { emit = false; end_sample = true; }
+                                    else atten = atten / p;
+                                }
+                            }
 #ifdef PT_SKIP_DEAD_LAST
                             // A/B variant: the last segment draws no random numbers and only adds atten * (emission | sky), both
                             // finite, so with a throughput of exactly zero (brdf() == 0: shading normal facing away from the
@@ -417,6 +428,8 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
         }
         queue_push(qout, qout_count, emit, slot);
     }
+    n_hit = __reduce_add_sync(0xffffffffu, n_hit);
+    if ((threadIdx.x & 31u) == 0u && n_hit) atomicAdd(pb.hit_count, (unsigned long long)n_hit);
 }
 
 __global__ void k_interleave_textures(const uint32_t* __restrict__ t0, const uint32_t* __restrict__ t1, const uint32_t* __restrict__ t2,

@@ -35,6 +35,8 @@ struct PathBuffers {
     uint32_t* trace_next;// [max_iters] dynamic-fetch cursors of the persistent trace kernel
     uint32_t* shade_next;// [max_iters] the same for K-shade (qcount, trace_next and shade_next are one allocation)
     uint32_t* trav_counters;  // [2] nodes, tris (counting walker)
+    unsigned long long* hit_count;   // rays of this frame that hit geometry (PtStats::rays_hit); lives behind shade_next, zeroed per frame
+    uint32_t frame_words;     // size of the qcount allocation in 32-bit words (counts, cursors, hit counter): one memset per frame
 };
 
 struct FrameParams {

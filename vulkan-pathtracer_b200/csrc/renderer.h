@@ -61,6 +61,7 @@ struct PtRenderer {
     bool peer_root = false;   // pt_ipc_export_image was called: other ranks store their tiles into d_image
     bool owns_scene = true;   // false for a sibling (pt_create_sibling): scene + BVH belong to the parent
     PtRenderer* parent = nullptr;   // sibling: where the current DeviceScene is read from (the parent may rebuild its top level)
+    uint32_t* h_error = nullptr;    // host-mapped traversal error flag (DeviceScene::error_flag); a sibling borrows its parent's
     // multi-GPU combine (comm.cpp): owned by the renderer pt_comm_init* was called on; siblings use their parent's
     PtComm* comm = nullptr;
     cudaEvent_t ev_reduce_done = nullptr;   // recorded on the communication stream after this renderer's last reduce

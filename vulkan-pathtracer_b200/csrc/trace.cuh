@@ -232,7 +232,7 @@ PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, 
     constexpr int kStack = 64;
     uint2 stack[kStack];
     int sp = 0;
-#define PT_PUSH(v) do { if (sp < kStack) stack[sp++] = (v); } while (0)
+#define PT_PUSH(v) do { if (sp < kStack) stack[sp++] = (v); else *sc.error_flag = 1u; } while (0)
     const uint2 kSentinel = make_uint2(0xFFFFFFFFu, 0u);
     uint2 G = make_uint2(sc.start_root, 0x80000000u);  // node group: (base, hits<<24 | imask)
     uint2 T = make_uint2(0u, 0u);                      // leaf group: (base, item mask)
@@ -325,6 +325,7 @@ PT_D void trace_bvh2(const DeviceScene& sc, uint32_t tlas2_count, const uint32_t
         if (!(ref & 0x80000000u)) {
             const Bvh2Node n = sc.tlas2[ref];
             if (!box2_hit(n, world, tmin, fminf(tmax, best.t))) continue;
+            if (tsp + 2 > 64) { *sc.error_flag = 1u; continue; }      // a Karras tree over clustered keys can be deeper than the stack
             tstack[tsp++] = n.left; tstack[tsp++] = n.right;
             continue;
         }
@@ -344,6 +345,7 @@ PT_D void trace_bvh2(const DeviceScene& sc, uint32_t tlas2_count, const uint32_t
             if (r & 0x80000000u) { test_triangle(tris, r & 0x7fffffffu, oo, rp, tmin, tmax, inst, best); continue; }
             const Bvh2Node n = nodes[r];
             if (!box2_hit(n, f, tmin, fminf(tmax, best.t))) continue;
+            if (sp + 2 > 64) { *sc.error_flag = 1u; continue; }
             stack[sp++] = n.left; stack[sp++] = n.right;
         }
     }

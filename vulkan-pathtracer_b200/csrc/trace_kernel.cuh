@@ -173,11 +173,11 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     // entries in thread-local memory.  Default: all of it in thread-local memory (L1-resident).
     __shared__ uint2 sstack[PT_TRACE_SMEM_STACK * kTraceBlock];
     uint2 stack[kStackSize - PT_TRACE_SMEM_STACK];
-#define PT_STACK_PUSH(v) do { if (sp < PT_TRACE_SMEM_STACK) sstack[sp * kTraceBlock + threadIdx.x] = (v); else stack[sp - PT_TRACE_SMEM_STACK] = (v); ++sp; } while (0)
+#define PT_STACK_PUSH(v) do { if (sp >= kStackSize) { *sc.error_flag = 1u; break; } if (sp < PT_TRACE_SMEM_STACK) sstack[sp * kTraceBlock + threadIdx.x] = (v); else stack[sp - PT_TRACE_SMEM_STACK] = (v); ++sp; } while (0)
 #define PT_STACK_POP(e) do { --sp; if (sp < PT_TRACE_SMEM_STACK) (e) = sstack[sp * kTraceBlock + threadIdx.x]; else (e) = stack[sp - PT_TRACE_SMEM_STACK]; } while (0)
 #else
     uint2 stack[kStackSize];
-#define PT_STACK_PUSH(v) do { stack[sp++] = (v); } while (0)
+#define PT_STACK_PUSH(v) do { if (sp < kStackSize) stack[sp++] = (v); else *sc.error_flag = 1u; } while (0)
 #define PT_STACK_POP(e) do { (e) = stack[--sp]; } while (0)
 #endif
     int sp = 0;
@@ -256,13 +256,13 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
 #endif
             } else {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
-                if (T.y && sp < kStackSize) PT_STACK_PUSH(T);
-                if ((G.y & 0xFF000000u) && sp < kStackSize) PT_STACK_PUSH(G);
+                if (T.y) PT_STACK_PUSH(T);
+                if (G.y & 0xFF000000u) PT_STACK_PUSH(G);
                 cur_inst = __ldg(sc.tlas_leaf_instance + T.x + b);
                 const uint4 ent = __ldg(reinterpret_cast<const uint4*>(&sc.instances[cur_inst].blas_root));   // blas_root, -, mesh | flags, -
                 const bool identity = (ent.z & kInstIdentity) != 0u;
                 // sentinel: y = 1 when the world frame must be re-loaded on the way out
-                if (sp < kStackSize) PT_STACK_PUSH(make_uint2(0xFFFFFFFFu, identity ? 0u : 1u));
+                PT_STACK_PUSH(make_uint2(0xFFFFFFFFu, identity ? 0u : 1u));
                 if (!identity) {
                     V3 oo, dd;
                     const float4 wd = io.ray_d[slot];      // the world direction is not kept in registers
@@ -300,7 +300,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             G.y &= ~(1u << k);
             const uint32_t s = (k - 24u) ^ f.rs;
             const uint32_t node = G.x + __popc(G.y & 0xffu & ((1u << s) - 1u));
-            if ((G.y & 0xFF000000u) && sp < kStackSize) PT_STACK_PUSH(G);
+            if (G.y & 0xFF000000u) PT_STACK_PUSH(G);
             uint32_t cb, tb, im;
             const uint32_t hits = node_test_fast(sc.nodes, sc.node_bits, node, f, tmin, fminf(tmax, best.t), bias, perm_lut, cb, tb, im);
             G = make_uint2(cb, (hits & 0xFF000000u) | im);
