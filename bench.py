@@ -7,8 +7,12 @@
 A step = one frame of the hot path (raygen -> [trace -> shade]* -> image) of the synthetic
 Sponza-scale scene (config C2: ~260 k triangles, 25 textured PBR materials, 1920x1080, 1 spp,
 2 ray segments) with frame_count = step index.  At N>1 every rank renders its own frame_count
-(sample-range partitioning: rank r renders frames r, r+N, ...) and the per-rank images are combined
-with an NCCL reduce(sum) to rank 0 inside the timed region (weak scaling).
+(sample-range partitioning: rank r renders frames r, r+N, ...) into its own accumulation buffer and
+the per-rank accumulation buffers are combined with ONE NCCL reduce(sum) to rank 0 — the library's
+pt_reduce_accum — inside the timed region, after the last step (weak scaling).  The `strong` object of
+the line is config C3 (3840x2160, 64 spp, 8 segments) with every frame tile-partitioned over the N
+ranks and reduced per frame (pt_reduce_image).  torch.distributed is used for the launch plumbing only
+(barrier, max-over-ranks of the timings, shipping the 128-byte NCCL id).
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -62,7 +66,9 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """nvidia-smi clocks / throttle reasons.  The process is started before the warm-up (it needs ~0.2 s to print its first
+    row) and every row is time-stamped on arrival; stop(t0, t1) keeps the rows that fall inside the timed region, or — when
+    the region is shorter than the 20 ms sampling period allows — the rows nearest to it, and says which."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -82,18 +88,27 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.time(), line.strip()))
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
+        rows, where = self.rows, "whole run"
+        if t0 is not None:
+            inside = [r for r in self.rows if t0 <= r[0] <= t1 + 0.03]
+            if inside:
+                rows, where = inside, "timed region"
+            else:
+                near = sorted(self.rows, key=lambda r: min(abs(r[0] - t0), abs(r[0] - t1)))[:3]
+                rows, where = near, "nearest to the timed region (region shorter than the sampling period)"
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        for _, r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 9:
                 continue
@@ -105,7 +120,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": where}
 
 
 def run_reference(args, rank, world):
@@ -168,6 +183,8 @@ def main():
                     help="tiles partitions only: contexts per GPU, each rendering a share of the rank's tiles on its own stream "
                          "(pt_create_sibling_part), so that the tail of one share's wavefronts overlaps the others' work")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (C3, tiles + reduce per frame)")
+    ap.add_argument("--strong-steps", type=int, default=3)
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--single-frame-in-flight", action="store_true", help="e2e leg without the sibling frame context")
     args = ap.parse_args()
@@ -217,6 +234,19 @@ def main():
             hb = (C.c_uint8 * 64)(*handle.cpu().tolist())
             b200pt.check(b200pt.lib().pt_ipc_open_root_image(r.handle, hb))
         fence = torch.zeros(1, dtype=torch.int32, device="cuda")
+    def comm_bootstrap(renderer):
+        """pt_comm_init on every rank: rank 0 makes the NCCL id, torch.distributed ships its 128 bytes."""
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.tensor(list(b200pt.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, src=0)
+        renderer.comm_init(rank, world, bytes(idt.cpu().tolist()))
+
+    if world > 1 and not peer:
+        comm_bootstrap(r)
+    frames_mode = world > 1 and not tiles
+    if frames_mode:
+        r.set_accumulate(True)      # every rank sums its own frames; one reduce of the accumulation buffers at the end
     st0 = r.stats()
     # a non-default torch stream: its handle is passed to pt_render so that torch.cuda.Event timing and
     # NCCL ordering see the renderer's kernels (the NULL handle would mean "the renderer's own stream")
@@ -239,12 +269,12 @@ def main():
         return i if tiles else i * world + rank
 
     def combine():
-        if world == 1:
+        if world == 1 or frames_mode:
             return
         if peer:
             dist.all_reduce(fence)      # stream-ordered fence: every rank's kernels (and their peer stores) precede it
         else:
-            dist.reduce(img_t, dst=0, op=dist.ReduceOp.SUM)
+            r.reduce_image(0, sp)       # ncclReduce(sum) to rank 0 inside libb200pt, on the timed stream
 
     def render_frame(cam):
         for p, ps_ in zip(parts, part_streams):     # the other shares start with this one and join before the reduce
@@ -260,12 +290,16 @@ def main():
         render_frame(S.camera_default(W, H, frame_of(i)))
 
     # ---------------- device-timed region: inputs resident, per-step CUDA events, L2 flushed between steps
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     r.set_profiling(True)
     for i in range(args.warmup):
         step(i)
+    if frames_mode:
+        r.reduce_accum(0, sp)           # warm-up of the collective too
+        r.reset_accum()
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    t_region0 = time.time()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     trace_ms = shade_ms = other_ms = 0.0
     launches = 0
@@ -285,9 +319,20 @@ def main():
             sp_ = p.stats()
             launches += sp_.kernel_launches + 1     # + the add of its image
             rays_local += sp_.rays_traced
+    reduce_ms = 0.0
+    if frames_mode:
+        # the combine of the sample-range split: per-rank accumulation buffers -> rank 0, once, inside the timed region
+        ra, rb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ra.record(stream)
+        r.reduce_accum(0, sp)
+        rb.record(stream)
+        launches += 1
     barrier()
-    clocks = sampler.stop()
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    t_region1 = time.time()
+    clocks = sampler.stop(t_region0, t_region1)
+    if frames_mode:
+        reduce_ms = ra.elapsed_time(rb)
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev) + reduce_ms
     t = torch.tensor([dev_ms, float(rays_local)], dtype=torch.float64, device="cuda")
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -305,14 +350,21 @@ def main():
     # One GPU: two frames in flight, like the reference's one command buffer + fence per swapchain image
     # (main.zig:209-217,255-259): a sibling context shares the device scene and has its own stream, path state,
     # image and pinned destination, so the tail of frame k overlaps ray generation + primary traversal of frame k+1.
-    in_flight = 2 if (world == 1 and not parts and not args.single_frame_in_flight) else 1
+    # N > 1, frame shares: the same on every rank (no per-step collective), both contexts accumulate; after the last step the
+    # sibling's accumulation is folded into the parent's, the parents' are reduced to rank 0 and rank 0 reads the mean.
+    in_flight = 2 if ((world == 1 or frames_mode) and not parts and not args.single_frame_in_flight) else 1
     if in_flight == 2:
         ctx = [r, r.sibling()]
+        if frames_mode:
+            ctx[1].set_accumulate(True)
         hosts = [host_img, torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)]
         for k in range(2):      # untimed: the sibling creates its copy stream and events on first use
             ctx[1].record(S.camera_default(W, H, k))
             b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(ctx[1].handle, hosts[1].data_ptr()))
         ctx[1].sync()
+    if frames_mode:
+        for c in (ctx if in_flight == 2 else [r]):
+            c.reset_accum()
     barrier()
     t0 = time.perf_counter()
     e2e_rays = 0
@@ -323,7 +375,7 @@ def main():
         b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(c.handle, hosts[k & 1].data_ptr()))
     if in_flight == 2:
         ctx[0].sync(); ctx[1].sync()
-    for k in range(args.steps if in_flight == 1 else 0):
+    for k in range(args.steps if (in_flight == 1 and not frames_mode) else 0):
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
         render_frame(cam)
         if rank == 0:
@@ -333,6 +385,15 @@ def main():
                 b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, host_img.data_ptr()))
         if peer:
             dist.all_reduce(fence)      # the next frame's peer stores must not overtake rank 0's read-back
+    for k in range(args.steps if (in_flight == 1 and frames_mode) else 0):
+        r.record(S.camera_default(W, H, frame_of(args.warmup + k)))
+        b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, host_img.data_ptr()))
+    if frames_mode:
+        if in_flight == 2:
+            r.add_accum(ctx[1])
+        r.reduce_accum(0)               # on the library's communication stream, behind this rank's last frame
+        if rank == 0:
+            b200pt.check(b200pt.lib().pt_read_accum_mean(r.handle, host_img.data_ptr(), args.steps * world))   # synchronises
     r.sync()            # the last pipelined read-back
     barrier()
     e2e_s = time.perf_counter() - t0
@@ -351,14 +412,24 @@ def main():
         n_trace_launches = args.steps * seg if spp == 1 else None
         achieved = bytes_per_ray * rays_local / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else 0.0
         # DRAM bytes per K-trace launch from the committed `ncu --set full` capture of this workload (None if absent)
-        traffic = None
+        traffic = warp_inst = lanes = None
         try:
             with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
                 tj = json.load(f)
-            if tj.get("workload") == args.workload:
-                traffic = tj["k_trace_persistent"]["dram_bytes_per_launch"]
+            if tj.get("workload") == args.workload and tj.get("flags", 0) == args.flags:
+                kt = tj["k_trace_persistent"]
+                traffic = kt["dram_bytes_per_launch"]
+                warp_inst = kt.get("warp_inst_per_frame")           # smsp__inst_executed.sum over the frame's K-trace launches
+                lanes = kt.get("lanes_per_inst")                    # smsp__thread_inst_executed_per_inst_executed, instruction-weighted
         except (OSError, KeyError, ValueError):
             pass
+        # the bounds K-trace actually sits under (SURVEY 8(d) "which roofline"): the traversal working set is L2-resident, so
+        # the memory bound is the L2 read bandwidth, measured here and now (32 MiB buffer read 100 times through __ldcg);
+        # and the kernel is instruction-issue-bound, so the issue rate (4 warp instructions per SM per clock) is stated too
+        l2_gbs, n_sms = b200pt.read_bandwidth(32 << 20, 100, local_rank)
+        sm_mhz = clocks.get("sm_mhz") or pk.get("sm_max_mhz", 1965.0)
+        issue_peak = n_sms * 4 * sm_mhz * 1e6                       # warp instructions per second
+        issue_frac = (warp_inst * args.steps / (trace_ms * 1e-3)) / issue_peak if (warp_inst and trace_ms > 0) else None
         # bloat guard: one root-to-leaf descent of a perfect 8-ary tree with 3 triangles per leaf
         per_mesh = [sum(ps.primitives[p].triangle_count for p in range(m.start, m.end)) for m in ps.meshes]
         t_blas, n_inst = max(per_mesh + [1]), max(1, len(ps.instances))
@@ -369,7 +440,11 @@ def main():
                 "algorithmic_bytes_per_ray": bytes_per_ray, "a_floor_bytes_per_ray": a_floor, "a_trav_over_floor": bytes_per_ray / a_floor, "nodes_per_ray": nodes / max(1, crays), "tris_per_ray": tris / max(1, crays),
                 "trace_ms_per_step": trace_ms / args.steps, "shade_ms_per_step": shade_ms / args.steps, "other_ms_per_step": other_ms / args.steps,
                 "trace_mrays_per_s": rays_local / (trace_ms * 1e-3) / 1e6 if trace_ms > 0 else 0.0,
-                "note": "BVH (nodes+triangles) is L2-resident on B200; the HBM peak is the contract's denominator, see DESIGN.md"}
+                "l2_peak_gbs": l2_gbs, "l2_frac": achieved / l2_gbs if l2_gbs > 0 else None, "l2_peak_source": "measured in this run (pt_debug_read_bandwidth, 32 MiB x 100 passes)",
+                "issue_frac": issue_frac, "lanes_per_inst": lanes, "useful_issue_frac": issue_frac * lanes / 32.0 if (issue_frac and lanes) else None,
+                "issue_peak_gwarp_inst_s": issue_peak * 1e-9, "issue_source": "warp instructions per frame from the committed ncu capture (profiles/ncu_traffic.json) / K-trace time of this run",
+                "note": "BVH (nodes+triangles) is L2-resident on B200: frac is against the HBM copy peak (the contract's denominator), l2_frac against the measured L2 read "
+                        "bandwidth, issue_frac against the issue rate -- the binding one (see DESIGN.md section 5)"}
         if not args.no_cpu_baseline and world == 1:
             from oracle import orc
             osc = orc.OracleScene(ps, True)
@@ -387,11 +462,48 @@ def main():
                     break
             cpu = {"value": crays2 / dt / 1e6, "unit": "Mrays/s", "cores": nt, "kind": "port",
                    "sample": f"{frames_cpu} frames x {rows} of {H} scanlines (every {row_step}th) at 1 spp, CPU oracle (C++ restatement, binned-SAH BVH2), {nt} threads, {dt:.2f} s"}
+    # ---------------- strong scaling (north_star: ">= 7x at 8 GPUs", BASELINE config 3): C3 = the same scene at 3840x2160,
+    # 64 spp, 8 segments; every frame is split into interleaved 32x8 tiles over the N ranks and reduced to rank 0 per frame
+    # (pt_reduce_image) inside the timed region.  Total work is fixed: value(N) / value(1) is the strong-scaling curve.
+    strong = None
+    if name == "c2" and not args.no_strong and args.flags == 0 and not parts:
+        _, W3, H3, spp3, seg3 = WORKLOADS["c3"]
+        r3 = b200pt.Renderer(ps, W3, H3, spp3, seg3, device=local_rank, rank=rank, world=world,
+                             partition=b200pt.PT_PARTITION_TILES if world > 1 else b200pt.PT_PARTITION_NONE)
+        if world > 1:
+            comm_bootstrap(r3)
+        ev3 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.strong_steps)]
+        rays3 = 0
+        for i in range(1 + args.strong_steps):
+            if i == 1:
+                barrier()
+            k = i - 1
+            if k >= 0:
+                ev3[k][0].record(stream)
+            r3.record(S.camera_default(W3, H3, i), sp)
+            if world > 1:
+                r3.reduce_image(0, sp)
+            if k >= 0:
+                ev3[k][1].record(stream)
+                rays3 += r3.stats().rays_traced          # synchronises, outside the bracket
+        barrier()
+        t3 = torch.tensor([sum(a.elapsed_time(b) for a, b in ev3), float(rays3)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            t3m = t3.clone(); dist.all_reduce(t3m, op=dist.ReduceOp.MAX)
+            t3s = t3.clone(); dist.all_reduce(t3s, op=dist.ReduceOp.SUM)
+            ms3, rays3 = float(t3m[0]), float(t3s[1])
+        else:
+            ms3 = float(t3[0])
+        strong = {"workload": WORKLOAD_DESC["c3"], "partition": "none" if world == 1 else "interleaved 32x8 tiles of every frame + NCCL reduce(sum) to rank 0 per frame (pt_reduce_image)",
+                  "scaling": "strong", "n_gpus": world, "steps": args.strong_steps, "warmup": 1, "ms_per_step": ms3 / args.strong_steps,
+                  "value": rays3 / (ms3 * 1e-3) / 1e6, "unit": "Mrays/s", "rays_per_step": rays3 / args.strong_steps,
+                  "spp_per_s": spp3 * args.strong_steps / (ms3 * 1e-3)}
+        r3.deinit()
     if rank == 0:
         line = {"metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
-                "config": {"workload": WORKLOAD_DESC[name], "partition": ("none" if (world == 1 and not tiles) else "frames (rank r renders frame_count r, r+N, ...) + NCCL reduce(sum) to rank 0" if not tiles
+                "config": {"workload": WORKLOAD_DESC[name], "partition": ("none" if (world == 1 and not tiles) else "frames (rank r renders frame_count r, r+N, ... into its own accumulation buffer) + one NCCL reduce(sum) of the accumulation buffers to rank 0 after the last step (pt_reduce_accum), inside the timed region" if not tiles
                                          else "interleaved 32x8 tiles of one frame, peer stores into rank 0 over NVLink + 4-byte NCCL fence" if peer
                                          else "interleaved 32x8 tiles of one frame + NCCL reduce(sum) to rank 0") + (f", {shares} tile shares per GPU on own streams" if shares > 1 else ""),
                            "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed; per-step path state (365 MB) exceeds L2",
@@ -400,7 +512,7 @@ def main():
                 "spp_per_s": spp_s, "rays_per_step": rays_total / args.steps / (1 if tiles else world),
                 "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(S.PtCamera), "d2h_bytes_per_step": W * H * 16,
                         "ms_per_step": 1e3 * e2e_s / args.steps, "spp_per_s": spp * frames_done / e2e_s, "frames_in_flight": in_flight},
-                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "strong": strong}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     if in_flight == 2:
