@@ -123,39 +123,60 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "window": where}
 
 
+def cpu_arm(ps, name, seconds=None, steps=None, warmup=0):
+    """The CPU arm of the comparison on all host threads, on a bounded sample of the workload: every `share`-th interleaved
+    32x8 tile of full-size frames at 1 spp (Mrays/s is a rate).  kind "reference": the reference's OWN shader sources
+    (ray_gen.rgen, closest_hit.rchit, miss.rmiss, triangle/material/brdf/rand.glsl) compiled as C++ into oracle/_ref
+    (oracle/ref_glsl/), one raygen invocation per pixel, with the oracle's BVH2 closest-hit query standing in for the part
+    the Vulkan driver owns (acceleration-structure traversal has no source).  kind "port": the oracle's restatement, when
+    oracle/_ref was never built.  Returns (Mrays/s, dict for the JSON line, ms per full frame)."""
+    from oracle import orc
+    _, W, H, spp, seg = WORKLOADS[name]
+    osc = orc.OracleScene(ps, True)
+    nt = orc.lib().orc_hardware_threads()
+    ref = orc.ref_lib()
+    use_ref = ref is not None and hasattr(ref, "ref_render")
+    share = max(1, int(round((W * H * seg / 2.0e6) / max(1, nt) / 3.0)))
+    rays_total, t_total, frames = 0, 0.0, 0
+    i = 0
+    while True:
+        cfg = S.render_config(W, H, 1, seg, rank=0, world=share, partition=1 if share > 1 else 0)
+        cam = S.camera_default(W, H, i)
+        t0 = time.perf_counter()
+        if use_ref:
+            _, rays = osc.ref_render(cfg, cam, True, nt)
+        else:
+            _, _, rays = osc.render(cfg, cam, True, nt, ids=False)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            rays_total += rays; t_total += dt; frames += 1
+        i += 1
+        if (steps is not None and frames >= steps) or (seconds is not None and t_total >= seconds) or frames >= 4096:
+            break
+    mrays = rays_total / t_total / 1e6
+    sample = (f"{frames} frames x 1/{share} of the interleaved 32x8 tiles of {WORKLOAD_DESC[name]} at 1 spp, {nt} threads, {t_total:.2f} s; "
+              + ("the reference's own GLSL (ray_gen.rgen + includes) compiled as C++ (oracle/_ref), oracle BVH2 closest-hit behind traceRayEXT"
+                 if use_ref else "CPU oracle (C++ restatement, binned-SAH BVH2)"))
+    info = {"value": mrays, "unit": "Mrays/s", "cores": nt, "kind": "reference" if use_ref else "port", "sample": sample}
+    return mrays, info, 1e3 * t_total / frames * share
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU implementation of the path is unavailable (Zig +
-    Vulkan) so the CPU oracle (kind "port") is timed on all host threads."""
+    """--impl reference: the reference's Vulkan pipeline cannot run here (no Zig, no Vulkan: SURVEY.md 8c); its shader code
+    can — see cpu_arm()."""
     if rank != 0:
         return 0
-    from oracle import orc
     name = args.workload
     ps, _ = build_scene(name)
     _, W, H, spp, seg = WORKLOADS[name]
-    osc = orc.OracleScene(ps, True)
-    cfg = S.render_config(W, H, 1, seg)   # 1 spp per step (Mrays/s is a rate)
-    nt = orc.lib().orc_hardware_threads()
-    # bounded sample: every `row_step`-th scanline so that one step stays around a few CPU-seconds per thread
-    row_step = max(1, int(round((W * H * seg / 2.0e6) / max(1, nt) / 2.0)))
-    rays_total, t_total = 0, 0.0
-    for i in range(args.warmup + args.steps):
-        cam = S.camera_default(W, H, i)
-        t0 = time.perf_counter()
-        _, rays = osc.render_rows(cfg, cam, 0, H, row_step, nt)
-        dt = time.perf_counter() - t0
-        if i >= args.warmup:
-            rays_total += rays; t_total += dt
-    mrays = rays_total / t_total / 1e6
-    rows = len(range(0, H, row_step))
-    frac = rows / H
-    sample = f"{rows} of {H} scanlines (every {row_step}th) of {WORKLOAD_DESC[name]} at 1 spp per step, {nt} threads"
+    mrays, info, ms_frame = cpu_arm(ps, name, steps=args.steps, warmup=args.warmup)
     line = {"impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps / frac, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms_frame, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_DESC[name], "note": "reference Vulkan/lavapipe path unavailable on this box; CPU oracle (C++ restatement of the shaders + binned-SAH BVH2) timed instead; ms_per_step extrapolated to the full frame"},
-            "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": nt, "kind": "port", "sample": sample},
+            "config": {"workload": WORKLOAD_DESC[name], "note": "the reference's Vulkan/lavapipe path is unavailable on this box; its shader sources compiled as C++ are timed on the host cores instead (see cpu_baseline.sample); ms_per_step extrapolated to the full frame"},
+            "cpu_baseline": info,
             "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "spp_per_s": (args.steps * frac) / t_total}
+            "spp_per_s": 1e3 / ms_frame}
     print(json.dumps(line))
     return 0
 
@@ -179,9 +200,6 @@ def main():
                     help="N>1: frames = rank r renders frame_count r, r+N, ... (weak scaling, default); tiles = every rank renders "
                          "its interleaved 32x8 tiles of the SAME frame + NCCL reduce (strong scaling); tiles-peer = same, but owned "
                          "pixels are stored straight into rank 0's image over NVLink (CUDA IPC), one 4-byte NCCL all-reduce as fence")
-    ap.add_argument("--tile-shares", type=int, default=1,
-                    help="tiles partitions only: contexts per GPU, each rendering a share of the rank's tiles on its own stream "
-                         "(pt_create_sibling_part), so that the tail of one share's wavefronts overlaps the others' work")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (C3, tiles + reduce per frame)")
     ap.add_argument("--strong-steps", type=int, default=3)
@@ -214,13 +232,10 @@ def main():
     _, W, H, spp, seg = WORKLOADS[name]
     ps, t_gen = build_scene(name)
     t0 = time.time()
-    tiles = (world > 1 or args.tile_shares > 1) and args.partition != "frames"
+    tiles = world > 1 and args.partition != "frames"
     peer = world > 1 and args.partition == "tiles-peer"
-    shares = max(1, args.tile_shares) if (tiles and args.partition == "tiles") else 1
-    r = b200pt.Renderer(ps, W, H, spp, seg, device=local_rank, flags=args.flags, rank=rank if tiles else 0, world=world * shares if tiles else 1,
+    r = b200pt.Renderer(ps, W, H, spp, seg, device=local_rank, flags=args.flags, rank=rank if tiles else 0, world=world if tiles else 1,
                         partition=b200pt.PT_PARTITION_TILES if tiles else b200pt.PT_PARTITION_NONE)
-    # further shares of this rank's tiles: share k of rank r owns the tiles `tile % (K * world) == k * world + r`
-    parts = [r.sibling_part(k * world + rank, world * shares) for k in range(1, shares)]
     t_create = time.time() - t0
     if peer:
         # rank 0 exports its image buffer; the others map it and their K-shade writes owned pixels into it
@@ -255,8 +270,6 @@ def main():
     sp = C.c_void_p(stream.cuda_stream)
     assert sp.value, "expected a non-default CUDA stream"
     img_t = torch.as_tensor(DevArray(r.device_image_ptr(), (H, W, 4)), device=f"cuda:{local_rank}")
-    part_img = [torch.as_tensor(DevArray(p.device_image_ptr(), (H, W, 4)), device=f"cuda:{local_rank}") for p in parts]
-    part_streams = [torch.cuda.Stream() for _ in parts]
     flush = None if args.no_l2_flush else torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")
     total_steps = args.warmup + args.steps
 
@@ -277,13 +290,7 @@ def main():
             r.reduce_image(0, sp)       # ncclReduce(sum) to rank 0 inside libb200pt, on the timed stream
 
     def render_frame(cam):
-        for p, ps_ in zip(parts, part_streams):     # the other shares start with this one and join before the reduce
-            ps_.wait_stream(stream)
-            p.record(cam, C.c_void_p(ps_.cuda_stream))
         r.record(cam, sp)
-        for ps_, im in zip(part_streams, part_img):
-            stream.wait_stream(ps_)
-            img_t.add_(im)                           # disjoint tiles, zero elsewhere
         combine()
 
     def step(i):
@@ -315,10 +322,6 @@ def main():
         trace_ms += s.ms_trace; shade_ms += s.ms_shade; other_ms += s.ms_other
         launches += s.kernel_launches
         rays_local += s.rays_traced
-        for p in parts:
-            sp_ = p.stats()
-            launches += sp_.kernel_launches + 1     # + the add of its image
-            rays_local += sp_.rays_traced
     reduce_ms = 0.0
     if frames_mode:
         # the combine of the sample-range split: per-rank accumulation buffers -> rank 0, once, inside the timed region
@@ -352,7 +355,7 @@ def main():
     # image and pinned destination, so the tail of frame k overlaps ray generation + primary traversal of frame k+1.
     # N > 1, frame shares: the same on every rank (no per-step collective), both contexts accumulate; after the last step the
     # sibling's accumulation is folded into the parent's, the parents' are reduced to rank 0 and rank 0 reads the mean.
-    in_flight = 2 if ((world == 1 or frames_mode) and not parts and not args.single_frame_in_flight) else 1
+    in_flight = 2 if ((world == 1 or frames_mode) and not args.single_frame_in_flight) else 1
     if in_flight == 2:
         ctx = [r, r.sibling()]
         if frames_mode:
@@ -379,7 +382,7 @@ def main():
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
         render_frame(cam)
         if rank == 0:
-            if peer or parts:    # the fence below / the sum of the tile shares is ordered on `sp`, so the copy has to be too
+            if peer:    # the fence below is ordered on `sp`, so the copy has to be too
                 b200pt.check(b200pt.lib().pt_read_rgba32f_async(r.handle, host_img.data_ptr(), sp))
             else:       # copy of frame k overlaps ray generation + primary traversal of frame k+1
                 b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, host_img.data_ptr()))
@@ -446,27 +449,12 @@ def main():
                 "note": "BVH (nodes+triangles) is L2-resident on B200: frac is against the HBM copy peak (the contract's denominator), l2_frac against the measured L2 read "
                         "bandwidth, issue_frac against the issue rate -- the binding one (see DESIGN.md section 5)"}
         if not args.no_cpu_baseline and world == 1:
-            from oracle import orc
-            osc = orc.OracleScene(ps, True)
-            nt = orc.lib().orc_hardware_threads()
-            cfg = S.render_config(W, H, 1, seg)
-            row_step = max(1, int(round((W * H * seg / 2.0e6) / max(1, nt) / 4.0)))
-            rows = len(range(0, H, row_step))
-            # bounded sample: whole frames (frame_count 0, 1, ...) of the same workload until ~12 s of wall time
-            crays2, frames_cpu, t1 = 0, 0, time.perf_counter()
-            while True:
-                _, cr = osc.render_rows(cfg, S.camera_default(W, H, frames_cpu), 0, H, row_step, nt)
-                crays2 += cr; frames_cpu += 1
-                dt = time.perf_counter() - t1
-                if dt >= 12.0 or frames_cpu >= 4096:
-                    break
-            cpu = {"value": crays2 / dt / 1e6, "unit": "Mrays/s", "cores": nt, "kind": "port",
-                   "sample": f"{frames_cpu} frames x {rows} of {H} scanlines (every {row_step}th) at 1 spp, CPU oracle (C++ restatement, binned-SAH BVH2), {nt} threads, {dt:.2f} s"}
+            _, cpu, _ = cpu_arm(ps, name, seconds=12.0)
     # ---------------- strong scaling (north_star: ">= 7x at 8 GPUs", BASELINE config 3): C3 = the same scene at 3840x2160,
     # 64 spp, 8 segments; every frame is split into interleaved 32x8 tiles over the N ranks and reduced to rank 0 per frame
     # (pt_reduce_image) inside the timed region.  Total work is fixed: value(N) / value(1) is the strong-scaling curve.
     strong = None
-    if name == "c2" and not args.no_strong and args.flags == 0 and not parts:
+    if name == "c2" and not args.no_strong and args.flags == 0:
         _, W3, H3, spp3, seg3 = WORKLOADS["c3"]
         r3 = b200pt.Renderer(ps, W3, H3, spp3, seg3, device=local_rank, rank=rank, world=world,
                              partition=b200pt.PT_PARTITION_TILES if world > 1 else b200pt.PT_PARTITION_NONE)
@@ -505,7 +493,7 @@ def main():
                 "data": "synthetic",
                 "config": {"workload": WORKLOAD_DESC[name], "partition": ("none" if (world == 1 and not tiles) else "frames (rank r renders frame_count r, r+N, ... into its own accumulation buffer) + one NCCL reduce(sum) of the accumulation buffers to rank 0 after the last step (pt_reduce_accum), inside the timed region" if not tiles
                                          else "interleaved 32x8 tiles of one frame, peer stores into rank 0 over NVLink + 4-byte NCCL fence" if peer
-                                         else "interleaved 32x8 tiles of one frame + NCCL reduce(sum) to rank 0") + (f", {shares} tile shares per GPU on own streams" if shares > 1 else ""),
+                                         else "interleaved 32x8 tiles of one frame + NCCL reduce(sum) to rank 0"),
                            "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed; per-step path state (365 MB) exceeds L2",
                            "triangles": int(st0.num_triangles), "bvh8_nodes": int(st0.bvh_nodes), "bvh_build_ms": st0.ms_build,
                            "scene_gen_s": t_gen, "create_s": t_create},
@@ -517,8 +505,6 @@ def main():
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     if in_flight == 2:
         ctx[1].deinit()     # the sibling goes first: the scene belongs to r
-    for p in parts:
-        p.deinit()
     r.deinit()
     if world > 1:
         dist.destroy_process_group()

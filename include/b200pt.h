@@ -139,10 +139,19 @@ enum {
                                              material that share one extent are interleaved per texel on the device */
     PT_FLAG_BVH_PLOC = 1u << 4,           /* build the binary hierarchy by locally-ordered clustering (PLOC) instead of
                                              the Morton radix tree (LBVH): slower build, better trees for irregular meshes */
-    PT_FLAG_BVH_SAH = 1u << 6,            /* build the binary hierarchy top-down by binned SAH on the GPU (32 bins x 3 axes
+    PT_FLAG_BVH_SAH = 1u << 6,            /* (default when no PT_FLAG_BVH_* is given: SAH | OPTIMAL_COLLAPSE)
+                                             build the binary hierarchy top-down by binned SAH on the GPU (32 bins x 3 axes
                                              per segment, level-synchronous; csrc/bvh_sah.cuh).  Takes precedence over PLOC */
     PT_FLAG_BVH_OPTIMAL_COLLAPSE = 1u << 7, /* BVH2 -> BVH8 by the cost-optimal collapse (dynamic programme of Ylitie et al.
                                              2017) instead of the greedy surface-area expansion; LBVH and SAH hierarchies */
+    PT_FLAG_BVH_LBVH = 1u << 9,           /* fast build: Morton radix tree (Karras 2012) + greedy collapse, 3-4x quicker to
+                                             build and ~10 % slower to trace than the default (binned SAH + cost-optimal
+                                             collapse, the reference's prefer_fast_trace: RaytracingPass.zig:353-358); with
+                                             PT_FLAG_BVH_OPTIMAL_COLLAPSE: radix tree + optimal collapse */
+    PT_FLAG_SKIP_DEAD_SEGMENTS = 1u << 10, /* do not trace the last segment of a sample whose throughput is exactly (0, 0, 0):
+                                             it draws no random numbers and only adds atten * (emission | sky), i.e. nothing.
+                                             Same image bit for bit, fewer executed queries than the reference's raygen
+                                             issues (C2: -5 % rays); off by default so that ray counts stay the reference's */
     PT_FLAG_RUSSIAN_ROULETTE = 1u << 8    /* EXTENSION, off by default and outside every parity claim against the reference
                                              (which has none, ray_gen.rgen:49-97): after the throughput update of a bounce
                                              (:95), from the second bounce on, the path survives with probability
@@ -274,11 +283,6 @@ int pt_create_from_gltf(const char* scene_path, const PtRenderConfig* config, Pt
  * with no frame in flight on either; the sibling picks the new top level up at its next pt_render).  pt_resize
  * applies to one context at a time.  Alternate pt_render between the two to overlap consecutive frames. */
 int pt_create_sibling(PtRenderer* parent, PtRenderer** out);
-/* the same, but the new context renders the interleaved tiles `tile % world == rank` only (PT_PARTITION_TILES with its own
- * rank / world, whatever the parent's): several contexts on ONE GPU, each with a share of the tiles and its own stream, so
- * that the tail of one share's wavefront (its slowest rays, a few per warp) overlaps the other shares' work.  Images of
- * the shares are disjoint and zero elsewhere: their sum is the frame.  With N GPUs use rank = k * N + gpu_rank, world = K * N. */
-int pt_create_sibling_part(PtRenderer* parent, int rank, int world, PtRenderer** out);
 /* deinit  src/RaytracingPass.zig:202-222 */
 void pt_destroy(PtRenderer* r);
 /* record  src/RaytracingPass.zig:520-675: enqueue one frame on `cuda_stream` (a cudaStream_t, or

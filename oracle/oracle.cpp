@@ -21,6 +21,7 @@
 // Each function cites the reference file:line it follows (paths relative to /root/reference).
 
 #include "../include/b200pt.h"
+#include "../include/b200pt_contract.h"
 
 #include <algorithm>
 #include <atomic>
@@ -63,9 +64,9 @@ static inline float mixf(float a, float b, float t) { return a * (1.0f - t) + b 
 static inline V3 mix(V3 a, V3 b, float t) { return V3{mixf(a.x, b.x, t), mixf(a.y, b.y, t), mixf(a.z, b.z, t)}; }
 static inline float idx(V3 a, int k) { return k == 0 ? a.x : (k == 1 ? a.y : a.z); }
 
-// correctly rounded fp32 sin / cos (arithmetic contract)
-static inline float sin_cr(float x) { return (float)std::sin((double)x); }
-static inline float cos_cr(float x) { return (float)std::cos((double)x); }
+// fp32 sin / cos of the arithmetic contract (include/b200pt_contract.h: explicit double arithmetic, no library call)
+static inline float sin_cr(float x) { float s, c; pt_contract_sincos(x, &s, &c); return s; }
+static inline float cos_cr(float x) { float s, c; pt_contract_sincos(x, &s, &c); return c; }
 
 static const float kPi = 3.141592653589793238462643f;  // brdf.glsl:4 (GLSL literal = fp32)
 
@@ -379,7 +380,6 @@ struct SceneView {
     Bvh2 tlas;
     std::vector<Box> inst_boxes;
     bool have_bvh = false;
-    std::vector<std::vector<int>> emissive_refs;   // per mesh: refs whose material has a non-zero emissive factor
 };
 
 static inline void load3(const uint8_t* base, uint64_t off, uint32_t i, float* out) {
@@ -408,9 +408,6 @@ static void build_scene_view(SceneView& sv, const PtSceneDesc& d, bool with_bvh)
                 uint32_t id[3]; tri_indices(d, pr, t, id);
                 float v[9];
                 for (int k = 0; k < 3; ++k) load3(d.triangle_data, pr.positions_offset, id[k], v + 3 * k);
-                if (sv.emissive_refs.size() <= m) sv.emissive_refs.resize(d.num_meshes);
-                const uint32_t mi = pr.info & 0xFFFFFFu;
-                if (mi < d.num_materials && (d.materials[mi].emissive_factor & 0xFFFFFFu) != 0u) sv.emissive_refs[m].push_back((int)ma.refs.size());
                 ma.refs.push_back(TriRef{p, t});
                 ma.verts.insert(ma.verts.end(), v, v + 9);
                 for (int k = 0; k < 3; ++k) ma.box.grow(v + 3 * k);
@@ -422,7 +419,6 @@ static void build_scene_view(SceneView& sv, const PtSceneDesc& d, bool with_bvh)
             ma.bvh.build(boxes, 4);
         }
     }
-    sv.emissive_refs.resize(d.num_meshes);
     sv.inst.resize(d.num_instances);
     sv.inst_boxes.resize(d.num_instances);
     for (size_t i = 0; i < d.num_instances; ++i) {
@@ -525,10 +521,7 @@ static inline V3 safe_inv(V3 d) {
     return v3(inv(d.x), inv(d.y), inv(d.z));
 }
 
-// stop (optional): set, and the walk abandoned, at the first candidate that beats `best` (first-hit query, see
-// last_segment_hit below)
-static inline void intersect_instance(const SceneView& sv, uint32_t ii, V3 o, V3 d, float tmin, float tmax, bool use_bvh, PtHit& best, uint64_t* tri_tests,
-                                      bool* stop = nullptr, const std::vector<int>* only = nullptr) {
+static inline void intersect_instance(const SceneView& sv, uint32_t ii, V3 o, V3 d, float tmin, float tmax, bool use_bvh, PtHit& best, uint64_t* tri_tests) {
     const InstanceXf& x = sv.inst[ii];
     const MeshAccel& ma = sv.meshes[x.mesh];
     if (ma.refs.empty()) return;
@@ -543,16 +536,11 @@ static inline void intersect_instance(const SceneView& sv, uint32_t ii, V3 o, V3
             const TriRef& tr = ma.refs[ri];
             if (hit_better(t, ii, tr.prim, tr.tri, best)) {
                 best.t = t; best.b1 = b1; best.b2 = b2; best.instance = ii; best.primitive_index = tr.prim; best.triangle_index = tr.tri;
-                if (stop) *stop = true;
             }
         }
     };
-    if (only) {
-        for (int ri : *only) test(ri);
-        return;
-    }
     if (!use_bvh) {
-        for (int i = 0; i < (int)ma.refs.size() && !(stop && *stop); ++i) test(i);
+        for (int i = 0; i < (int)ma.refs.size(); ++i) test(i);
         return;
     }
     const V3 inv_d = safe_inv(dd);
@@ -563,7 +551,6 @@ static inline void intersect_instance(const SceneView& sv, uint32_t ii, V3 o, V3
         if (!hit_box(n.box, oo, inv_d, tmin, std::min(tmax, best.t))) continue;
         if (n.count > 0) {
             for (int i = n.first; i < n.first + n.count; ++i) test(ma.bvh.items[i]);
-            if (stop && *stop) return;
         } else {
             stack[sp++] = n.left; stack[sp++] = n.right;
         }
@@ -592,43 +579,8 @@ static inline PtHit closest_hit(const SceneView& sv, V3 o, V3 d, float tmin, flo
     return best;
 }
 
-// The last segment of a sample consumes nothing of its hit but the emission (ray_gen.rgen:75-77; a miss adds the sky,
-// :65-70).  Proposed saving, restated here so that its claim can be checked on the CPU: take the
-// lexicographically closest hit among the EMISSIVE triangles first, then look for any candidate that beats it and stop at
-// the first one found.  Such a candidate is not emissive (the closest emissive one is already held), so whichever it is the
-// sample adds the same exact zero as the true closest hit would; without one the answer is the emissive hit or a miss.
-// tests/test_oracle_trace.py asserts that images rendered this way are bit-identical to the plain loop.
-static bool g_occlusion_last = false;
-static bool g_skip_dead_last = false;
 static bool g_count_dead = false;
 static std::atomic<uint64_t> g_dead_rays{0};
-
-static inline PtHit last_segment_hit(const SceneView& sv, V3 o, V3 d, float tmin, float tmax, bool use_bvh) {
-    PtHit best; best.t = 1e32f; best.b1 = best.b2 = 0.0f;
-    best.instance = best.primitive_index = best.triangle_index = 0xFFFFFFFFu;
-    for (uint32_t i = 0; i < sv.inst.size(); ++i) {
-        const std::vector<int>& em = sv.emissive_refs[sv.inst[i].mesh];
-        if (!em.empty()) intersect_instance(sv, i, o, d, tmin, tmax, false, best, nullptr, nullptr, &em);
-    }
-    bool stop = false;
-    if (!use_bvh || !sv.have_bvh) {
-        for (uint32_t i = 0; i < sv.inst.size() && !stop; ++i) intersect_instance(sv, i, o, d, tmin, tmax, false, best, nullptr, &stop);
-        return best;
-    }
-    if (sv.tlas.nodes.empty()) return best;
-    const V3 inv_d = safe_inv(d);
-    int stack[128]; int sp = 0; stack[sp++] = 0;
-    while (sp && !stop) {
-        const Bvh2Node& n = sv.tlas.nodes[stack[--sp]];
-        if (!hit_box(n.box, o, inv_d, tmin, std::min(tmax, best.t))) continue;
-        if (n.count > 0) {
-            for (int i = n.first; i < n.first + n.count && !stop; ++i) intersect_instance(sv, (uint32_t)sv.tlas.items[i], o, d, tmin, tmax, true, best, nullptr, &stop);
-        } else {
-            stack[sp++] = n.left; stack[sp++] = n.right;
-        }
-    }
-    return best;
-}
 
 // ------------------------------------------------------------------------------------------
 // Hit attribute fetch — src/shaders/triangle.glsl:46-112
@@ -767,12 +719,10 @@ static inline PixelOut shade_pixel(const SceneView& sv, const PtCamera& cam, uin
         V3 origin = pos;                                                        // :47
         V3 direction = normalize(fwd + hor * dx - ver * dy);                    // :48
         for (uint32_t j = 0; j < B; ++j) {                                      // :49
-            // second proposed saving: the last segment draws no random numbers and only adds atten * (emission or sky), so
-            // with a throughput of exactly zero it adds exactly nothing and need not be traced (both factors are finite)
-            if (g_skip_dead_last && j == B - 1 && j > 0 && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) break;
-            const PtHit h = (g_occlusion_last && j == B - 1 && !(i == 0 && j == 0))
-                                ? last_segment_hit(sv, origin, direction, tmin, tmax, use_bvh)
-                                : closest_hit(sv, origin, direction, tmin, tmax, use_bvh);  // :50-63
+            // PT_FLAG_SKIP_DEAD_SEGMENTS (include/b200pt.h): the last segment draws no random numbers and only adds
+            // atten * (emission or sky), both finite, so with a throughput of exactly zero it adds exactly nothing
+            if ((flags & PT_FLAG_SKIP_DEAD_SEGMENTS) && j == B - 1 && j > 0 && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) break;
+            const PtHit h = closest_hit(sv, origin, direction, tmin, tmax, use_bvh);  // :50-63
             ++out.rays;
             if (i == 0 && j == 0) out.primary = h;
             if (h.t == 1e32f) {                                                 // :65-70
@@ -996,10 +946,6 @@ int orc_intersect_tri(const float o[3], const float d[3], const float v[9], floa
     if (!intersect_tri(v3(o[0], o[1], o[2]), rp, v, tmin, tmax, t, b1, b2)) return 0;
     out[0] = t; out[1] = b1; out[2] = b2; return 1;
 }
-// test-only switch: last segments of a sample as first-hit queries behind the closest emissive hit (see last_segment_hit)
-void orc_set_occlusion_last(int on) { g_occlusion_last = on != 0; }
-
-void orc_set_skip_dead_last(int on) { g_skip_dead_last = on != 0; }
 uint64_t orc_dead_ray_statistic(int enable) { g_count_dead = enable != 0; return g_dead_rays.exchange(0); }
 
 int orc_hardware_threads(void) { return (int)std::thread::hardware_concurrency(); }

@@ -8,13 +8,15 @@
 // matrix, matN(matMxK) takes the upper-left block, swizzles are l-values).  Where the spec leaves the
 // precision or evaluation order open, the arithmetic contract of DESIGN.md §2 is used and marked
 // [contract] below: matrix/vector products sum left to right, normalize(v) = v * (1 / sqrt(dot)),
-// inverse(mat3) by cofactors with one division, sin/cos correctly rounded, texture() = the Vulkan
+// inverse(mat3) by cofactors with one division, sin/cos = include/b200pt_contract.h, texture() = the Vulkan
 // bilinear formula in fp32.  What the Vulkan *driver* does behind traceRayEXT (acceleration-structure
 // traversal, ray/triangle intersection) is not shader source: it is supplied by a callback.
 #pragma once
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+
+#include "../../include/b200pt_contract.h"
 
 namespace glsl {
 typedef uint32_t uint;
@@ -118,8 +120,8 @@ inline float sqrt(float x) { return std::sqrt(x); }
 inline float sin(float x) { return std::sin(x); }
 inline float cos(float x) { return std::cos(x); }
 #else
-inline float sin(float x) { return (float)std::sin((double)x); }   // [contract] correctly rounded
-inline float cos(float x) { return (float)std::cos((double)x); }
+inline float sin(float x) { float s, c; pt_contract_sincos(x, &s, &c); return s; }   // [contract] include/b200pt_contract.h
+inline float cos(float x) { float s, c; pt_contract_sincos(x, &s, &c); return c; }
 #endif
 inline float min(float x, float y) { return (y < x) ? y : x; }     // 8.3
 inline float max(float x, float y) { return (x < y) ? y : x; }

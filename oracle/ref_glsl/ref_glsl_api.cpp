@@ -61,6 +61,7 @@ struct Pipeline {
     std::atomic<uint64_t> rays{0};
 };
 static Pipeline g_pipe;
+static thread_local uint64_t t_rays = 0;      // traceRayEXT calls of this thread (summed into g_pipe.rays per worker)
 static std::vector<Primitive> g_primitives;
 static std::vector<Material> g_materials;
 static std::vector<sampler2D> g_textures;
@@ -83,7 +84,7 @@ static void set_hit_builtins(const PtHit& h) {
 void traceRayEXT(accelerationStructureEXT, uint, uint, uint, uint, uint, vec3 origin, float tmin, vec3 direction, float tmax, int) {
     const float o[3] = {origin.x, origin.y, origin.z}, d[3] = {direction.x, direction.y, direction.z};
     PtHit h;
-    g_pipe.rays.fetch_add(1, std::memory_order_relaxed);
+    ++t_rays;
     if (g_pipe.trace(g_pipe.trace_ctx, o, tmin, d, tmax, g_pipe.use_bvh, &h)) {
         set_hit_builtins(h);
         rchit::attribs = vec2(h.b1, h.b2);
@@ -145,9 +146,10 @@ uint64_t ref_render(const PtSceneDesc* scene, const PtRenderConfig* cfg, const P
     std::atomic<uint32_t> next_row{0};
     const uint32_t tiles_x = (W + 31) / 32;
     auto worker = [&]() {
+        t_rays = 0;
         for (;;) {
             const uint32_t y = next_row.fetch_add(1);
-            if (y >= H) break;
+            if (y >= H) { g_pipe.rays.fetch_add(t_rays); break; }
             for (uint32_t x = 0; x < W; ++x) {
                 if (cfg->partition == PT_PARTITION_TILES && cfg->world > 1) {
                     const uint32_t tile = (y / 8) * tiles_x + (x / 32);

@@ -121,7 +121,9 @@ def test_new_round_one_entry_points_reject_null_arguments():
     assert L.pt_debug_bvh_digest(None, None) == -1
     assert L.pt_read_rgba32f_overlapped(None, None) == -1
     assert L.pt_create_sibling(None, None) == -1
-    assert L.pt_create_sibling_part(None, 0, 2, None) == -1
+    assert L.pt_comm_init(None, 0, 1, None) == -1 and L.pt_comm_init_all(None, 0) == -1
+    assert L.pt_reduce_image(None, 0, None) == -1 and L.pt_reduce_accum(None, 0, None) == -1
+    assert L.pt_add_accum(None, None) == -1 and L.pt_comm_unique_id(None) == -1
     assert L.pt_debug_read_bandwidth(0, C.c_size_t(1 << 20), 1, None, None) == -1
     assert C.sizeof(b200pt.PtCameraState) == 26 * 4 and C.sizeof(b200pt.PtInput) == 20
 

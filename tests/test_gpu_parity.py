@@ -95,8 +95,12 @@ def test_unorm8_conversion_is_exact():
 
 
 # ------------------------------------------------------------------ traversal kernel vs brute force
-@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2, b200pt.PT_FLAG_BVH_PLOC,
-                                   b200pt.PT_FLAG_BVH_PLOC | b200pt.PT_FLAG_TRACE_BVH2])
+# builder stages: default = binned SAH + cost-optimal collapse; LBVH = Morton radix tree + greedy collapse (fast build)
+LBVH, OPT, SAH, PLOC = b200pt.PT_FLAG_BVH_LBVH, b200pt.PT_FLAG_BVH_OPTIMAL_COLLAPSE, b200pt.PT_FLAG_BVH_SAH, b200pt.PT_FLAG_BVH_PLOC
+
+
+@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2, LBVH, LBVH | OPT, SAH, LBVH | b200pt.PT_FLAG_TRACE_WALKER,
+                                   LBVH | b200pt.PT_FLAG_TRACE_BVH2, PLOC, PLOC | b200pt.PT_FLAG_TRACE_BVH2])
 @pytest.mark.parametrize("seed,ntri,nmesh,ninst", [(3, 3000, 3, 7), (5, 3, 3, 4), (11, 20000, 2, 40), (12, 64, 5, 1)])
 def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
     ps = S.random_soup(seed, ntri, nmesh, ninst).pack()
@@ -112,7 +116,7 @@ def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
     r.deinit()
 
 
-@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_BVH_PLOC])
+@pytest.mark.parametrize("flags", [0, LBVH, SAH, PLOC])
 def test_duplicated_geometry_builds_and_keeps_the_tie_break(flags):
     """6000 coincident triangles (two primitives, three instances at the same place): the builders must
     terminate on runs of identical boxes, and the closest hit is the lexicographically smallest
@@ -591,18 +595,46 @@ def test_single_instance_scene_skips_the_top_level_only_when_identity():
     assert bits_equal(fresh_img, oimg).all() and all((a == b).all() for a, b in zip(fresh_ids, oids))
 
 
-def test_builder_is_deterministic_across_builds():
-    """Same scene, repeated builds with other work in between: identical digests of every builder stage."""
+@pytest.mark.parametrize("builder", [0, LBVH])
+def test_builder_is_deterministic_across_builds(builder):
+    """Same scene, repeated builds with other work in between: identical digests of every builder stage (the SAH stage
+    derives node ids from split positions and partitions stably, so it does not depend on atomic order either)."""
     ps = S.random_soup(3, 3000, 3, 7).pack()
     pc = S.cornell().pack()
     seen = set()
     for k in range(12):
         if k % 3 == 0:
             rc = b200pt.Renderer(pc, 96, 64, 1 + k % 2, 2); rc.record(S.camera_default(96, 64, k)); rc.sync(); rc.deinit()
-        r = b200pt.Renderer(ps, 100, 60, 1, 2, flags=(0, b200pt.PT_FLAG_TRACE_BVH2)[k & 1])
+        r = b200pt.Renderer(ps, 100, 60, 1, 2, flags=builder | (0, b200pt.PT_FLAG_TRACE_BVH2)[k & 1])
         seen.add(r.bvh_digest())
         r.deinit()
     assert len(seen) == 1, f"{len(seen)} different acceleration structures from the same input"
+
+
+def test_image_does_not_depend_on_the_hierarchy():
+    """The closest-hit rule is order-independent, so every builder gives the same image, ids and ray count."""
+    ps = S.atrium(1234, 20000, 6, 64).pack()
+    ref = None
+    for flags in (0, LBVH, LBVH | OPT, SAH, PLOC):
+        img, ids, st = render(ps, 256, 144, 2, 3, 1, flags=flags)
+        if ref is None:
+            ref = (img, ids, st.rays_traced)
+        assert bits_equal(img, ref[0]).all() and all((a == b).all() for a, b in zip(ids, ref[1])) and st.rays_traced == ref[2]
+
+
+def test_zero_throughput_last_segments_are_skipped_without_changing_a_bit():
+    """PT_FLAG_SKIP_DEAD_SEGMENTS: same image and ids, fewer executed queries — and exactly as many as the oracle under the
+    same flag (the saving is proven in the restatement too, tests/test_oracle_trace.py)."""
+    SK = b200pt.PT_FLAG_SKIP_DEAD_SEGMENTS
+    for ps, W, H, spp, seg in ((S.atrium(1234, 20000, 6, 64).pack(), 320, 180, 2, 3), (S.cornell().pack(), 128, 128, 3, 2)):
+        a, ia, sa = render(ps, W, H, spp, seg, 2)
+        b, ib, sb_ = render(ps, W, H, spp, seg, 2, flags=SK)
+        assert bits_equal(a, b).all() and all((x == y).all() for x, y in zip(ia, ib))
+        assert sb_.rays_traced <= sa.rays_traced
+        c, _, sc = render(ps, W, H, spp, seg, 2, flags=SK | b200pt.PT_FLAG_NO_PRIMARY_REUSE)
+        _, _, orays = orc.OracleScene(ps, True).render(S.render_config(W, H, spp, seg, flags=SK), S.camera_default(W, H, 2), True)
+        assert bits_equal(a, c).all() and sc.rays_traced == orays
+    assert sb_.rays_traced <= sa.rays_traced
 
 
 def test_sibling_context_shares_the_scene_and_keeps_two_frames_in_flight():

@@ -50,33 +50,3 @@ def test_tile_and_frame_partition_world2(tmp_path):
     assert (g["owned"] == 1).all()                                              # every pixel owned exactly once
     assert np.array_equal(g["reduced"].view(np.uint32), g["full"].view(np.uint32))   # bit-exact vs 1 rank
     assert np.array_equal(g["fsum"].view(np.uint32), g["fref"].view(np.uint32))
-
-
-def test_tile_shares_partition_the_image():
-    """bench.py --tile-shares K: share k of rank r renders the tiles `tile % (K * world) == k * world + r`
-    (pt_create_sibling_part).  Checked with the oracle's tile partition: for world 2 x 3 shares every pixel is owned exactly
-    once, a rank's shares together are exactly the rank's own tiles of the plain 2-rank partition, and the sum is the frame."""
-    sys.path.insert(0, ROOT)
-    from oracle import orc
-    from tools import scene as S
-    ps = S.cornell().pack()
-    osc = orc.OracleScene(ps, True)
-    W, H = 160, 48
-    cam = S.camera_default(W, H, 1)
-    world, K = 2, 3
-    full, _, _ = osc.render(S.render_config(W, H, 1, 2), cam, True)
-    total = np.zeros_like(full)
-    owned = np.zeros((H, W), np.int32)
-    for r in range(world):
-        plain, _, _ = osc.render(S.render_config(W, H, 1, 2, rank=r, world=world, partition=1), cam, True)
-        mine = np.zeros((H, W), bool)
-        for k in range(K):
-            img, _, _ = osc.render(S.render_config(W, H, 1, 2, rank=k * world + r, world=K * world, partition=1), cam, True)
-            own = img[..., 3] != 0
-            assert not (mine & own).any()
-            mine |= own
-            owned += own
-            total += img
-        assert (mine == (plain[..., 3] != 0)).all()     # the shares of rank r are rank r's tiles
-    assert (owned == 1).all()
-    assert np.array_equal(total.view(np.uint32), full.view(np.uint32))

@@ -154,45 +154,11 @@ def test_bounce_count_is_segment_count():
     assert np.allclose(img[~miss][:, :3].max(), 10.0) or (img[~miss][:, :3] <= 10.0).all()
 
 
-@pytest.mark.parametrize("scene,W,H,spp,seg", [("cornell", 96, 96, 3, 2), ("cornell", 64, 64, 2, 4), ("soup", 96, 64, 2, 2),
-                                               ("soup", 64, 64, 3, 3), ("atrium", 160, 90, 1, 2)])
-def test_last_segment_as_occlusion_query_is_bit_identical(oracle_lib, scene, W, H, spp, seg):
-    """DESIGN.md section 10 proposes to trace the last segment of a sample as a first-hit query behind the closest EMISSIVE hit
-    (it only adds the emission of what it hits, ray_gen.rgen:75-77).  The claim that this changes no bit of the image is
-    checked here in the CPU restatement (orc_set_occlusion_last) before any kernel is written: emissive quads (Cornell,
-    atrium), random soups with emissive materials on rotated / scaled instances, several samples and segment counts."""
-    if scene == "cornell":
-        ps = S.cornell().pack()
-    elif scene == "soup":
-        ps = S.random_soup(17, 1500, 3, 6).pack()
-    else:
-        ps = S.atrium(1234, 20_000, 6, 64, (0.1, 1.0), 0.2, True).pack()
-    osc = orc.OracleScene(ps, True)
-    cfg = S.render_config(W, H, spp, seg)
-    try:
-        for frame in (0, 1):
-            cam = S.camera_default(W, H, frame)
-            oracle_lib.orc_set_occlusion_last(0)
-            a, ids_a, rays_a = osc.render(cfg, cam, True)
-            oracle_lib.orc_set_occlusion_last(1)
-            b, ids_b, rays_b = osc.render(cfg, cam, True)
-            assert bits_equal(a, b).all(), f"{int((~bits_equal(a, b).all(axis=2)).sum())} pixels differ"
-            assert rays_a == rays_b
-            for x, y in zip(ids_a, ids_b):
-                assert (x == y).all()
-            oracle_lib.orc_set_occlusion_last(1)
-            c, _, _ = osc.render(cfg, cam, False)      # brute force under the same rule
-            assert bits_equal(a, c).all()
-    finally:
-        oracle_lib.orc_set_occlusion_last(0)
-
-
 @pytest.mark.parametrize("scene,W,H,spp,seg", [("cornell", 96, 96, 3, 2), ("soup", 96, 64, 2, 3), ("atrium", 160, 90, 2, 2)])
 def test_zero_throughput_last_segments_need_no_trace(oracle_lib, scene, W, H, spp, seg):
     """The last segment of a sample draws no random numbers and only adds atten * (emission | sky), both finite: when atten is
     exactly (0, 0, 0) -- brdf() returns 0 for a shading normal that faces away from the viewer -- it adds exactly nothing.
-    Skipping those rays (orc_set_skip_dead_last) leaves every bit of the image alone and traces fewer rays; combined with the
-    occlusion-query rule as well."""
+    Skipping those rays (PT_FLAG_SKIP_DEAD_SEGMENTS) leaves every bit of the image alone and traces fewer rays."""
     if scene == "cornell":
         ps = S.cornell().pack()
     elif scene == "soup":
@@ -200,16 +166,7 @@ def test_zero_throughput_last_segments_need_no_trace(oracle_lib, scene, W, H, sp
     else:
         ps = S.atrium(1234, 20_000, 6, 64, (0.1, 1.0), 0.2, True).pack()
     osc = orc.OracleScene(ps, True)
-    cfg = S.render_config(W, H, spp, seg)
     cam = S.camera_default(W, H, 0)
-    try:
-        a, _, rays_a = osc.render(cfg, cam, True)
-        oracle_lib.orc_set_skip_dead_last(1)
-        b, _, rays_b = osc.render(cfg, cam, True)
-        oracle_lib.orc_set_occlusion_last(1)
-        c, _, rays_c = osc.render(cfg, cam, True)
-        assert bits_equal(a, b).all() and bits_equal(a, c).all()
-        assert rays_b <= rays_a and rays_c == rays_b
-    finally:
-        oracle_lib.orc_set_skip_dead_last(0)
-        oracle_lib.orc_set_occlusion_last(0)
+    a, _, rays_a = osc.render(S.render_config(W, H, spp, seg), cam, True)
+    b, _, rays_b = osc.render(S.render_config(W, H, spp, seg, flags=1 << 10), cam, True)
+    assert bits_equal(a, b).all() and rays_b <= rays_a

@@ -1,4 +1,4 @@
-"""Turns the raw outputs of tools/final_evidence.sh (gpurun_out/<tag>_*) into the tracked summaries under profiles/:
+"""Turns the raw outputs of tools/evidence.sh (gpurun_out/<tag>_*) into the tracked summaries under profiles/:
 bench lines, launch shares, the `ncu --set full` summary, per-line attribution of K-trace and the DRAM traffic file
 that bench.py reads for `roofline.traffic`.   usage: python tools/collect_evidence.py <tag>"""
 import csv
@@ -55,12 +55,17 @@ def main():
         hdr, units = rr[0], rr[1]
         ni, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
         scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
-        tot = [float(r[ri]) * scale[units[ri]] + float(r[wi]) * scale[units[wi]] for r in rr[2:] if "k_trace_persistent" in r[ni]]
-        last = tot[-2:]
-        json.dump({"workload": "c2", "source": f"profiles/{tag}_ncu_full_summary.txt (ncu --set full --clock-control none, bench.py --steps 1 --warmup 3)",
-                   "k_trace_persistent": {"dram_bytes_per_launch": sum(last) / len(last), "launches": last}},
+        kt = [r for r in rr[2:] if "k_trace_persistent" in r[ni]][-2:]      # the last captured frame: primary + bounce wavefront
+        last = [float(r[ri]) * scale[units[ri]] + float(r[wi]) * scale[units[wi]] for r in kt]
+        ii, li = hdr.index("smsp__inst_executed.sum"), hdr.index("smsp__thread_inst_executed_per_inst_executed.ratio")
+        inst = [float(r[ii]) for r in kt]
+        lanes = sum(float(r[li]) * n for r, n in zip(kt, inst)) / sum(inst)
+        json.dump({"workload": "c2", "flags": 0,
+                   "source": f"profiles/{tag}_ncu_full_summary.txt (ncu --set full --clock-control none, bench.py --steps 1 --warmup 3)",
+                   "k_trace_persistent": {"dram_bytes_per_launch": sum(last) / len(last), "launches": last,
+                                          "warp_inst_per_frame": sum(inst), "warp_inst_per_launch": inst, "lanes_per_inst": lanes}},
                   open(os.path.join(PROF, "ncu_traffic.json"), "w"), indent=1)
-        print("traffic per K-trace launch (bytes):", last)
+        print("traffic per K-trace launch (bytes):", last, "warp instructions per frame:", sum(inst), "lanes per instruction:", lanes)
 
 
 if __name__ == "__main__":

@@ -20,25 +20,14 @@ def main():
     name = sys.argv[2] if len(sys.argv) > 2 else "c2"
     builder, W, H, spp, seg = S.CONFIGS[name]
     ps = builder(1234).pack()
-    if what == "postpone":   # retired knob (profiles/r1_experiments.md); the option is a no-op now
-        r = b200pt.Renderer(ps, W, H, spp, seg)
-        ref = None
-        for v in (0, 2, 4, 6, 8, 12, 16, 20, 24, 33):
-            b200pt.set_option("postpone", v)
-            tr, sh, ot, rays = measure(r, W, H)
-            img = r.image()
-            if ref is None: ref = img
-            same = np.array_equal(ref.view(np.uint32), img.view(np.uint32))
-            print(f"postpone<{v:2d}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  {rays/1e6:.2f} Mrays  {rays/(tr*1e3):.0f} Mrays/s(trace)  same_image={same}")
-        r.deinit()
-    elif what == "chunk":
-        r = b200pt.Renderer(ps, W, H, spp, seg)
-        for v in (8, 16, 32, 64, 128):
+    if what == "chunk":
+        for v in (8, 16, 32, 64, 128):       # the knob applies to renderers created afterwards
             b200pt.set_option("chunk", v)
+            r = b200pt.Renderer(ps, W, H, spp, seg)
             tr, sh, ot, rays = measure(r, W, H)
             print(f"chunk {v:4d}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}")
+            r.deinit()
         b200pt.set_option("chunk", 32)
-        r.deinit()
     elif what == "one":
         r = b200pt.Renderer(ps, W, H, spp, seg)
         tr, sh, ot, rays = measure(r, W, H)
@@ -51,12 +40,12 @@ def main():
         # A/B of the binary-hierarchy stages and collapses: per-ray counts (pt_count_traversal), kernel times, and the image
         # must be bit-identical to the default build (the closest-hit rule does not depend on the hierarchy)
         ref = None
-        for flags, label in ((0, "LBVH + greedy (default)"), (128, "LBVH + optimal collapse"), (64, "SAH + greedy"), (192, "SAH + optimal collapse"),
+        for flags, label in ((0, "SAH + optimal collapse (default)"), (512, "LBVH + greedy"), (512 | 128, "LBVH + optimal collapse"), (64, "SAH + greedy"),
                              (16, "PLOC + greedy")):
             try:
                 r = b200pt.Renderer(ps, W, H, spp, seg, flags=flags)
             except Exception as e:   # an opt-in stage that fails must not hide the others
-                print(f"{label:26s}: build failed: {e}")
+                print(f"{label:34s}: build failed: {e}")
                 continue
             tr, sh, ot, rays = measure(r, W, H)
             st = r.stats()
@@ -65,7 +54,7 @@ def main():
             img = r.image()
             if ref is None: ref = img
             same = np.array_equal(ref.view(np.uint32), img.view(np.uint32))
-            print(f"{label:26s}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  bvh8 nodes {st.bvh_nodes}  "
+            print(f"{label:34s}: trace {tr:.3f} ms  shade {sh:.3f}  other {ot:.3f}  total {tr+sh+ot:.3f}  bvh8 nodes {st.bvh_nodes}  "
                   f"per ray: {nn/max(nr,1):.2f} nodes {nt/max(nr,1):.2f} tris  build {st.ms_build:.2f} ms  same_image={same}")
             r.deinit()
     elif what == "modes":

@@ -29,7 +29,7 @@ LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(_HERE, "libb200pt.so")
 
 PT_PARTITION_NONE, PT_PARTITION_TILES = 0, 1
 PT_FLAG_SORT_BY_MATERIAL, PT_FLAG_TRACE_BVH2, PT_FLAG_NO_PRIMARY_REUSE, PT_FLAG_TRACE_WALKER, PT_FLAG_BVH_PLOC, PT_FLAG_NO_TEXTURE_INTERLEAVE = 1, 2, 4, 8, 16, 32
-PT_FLAG_BVH_SAH, PT_FLAG_BVH_OPTIMAL_COLLAPSE, PT_FLAG_RUSSIAN_ROULETTE = 64, 128, 256
+PT_FLAG_BVH_SAH, PT_FLAG_BVH_OPTIMAL_COLLAPSE, PT_FLAG_RUSSIAN_ROULETTE, PT_FLAG_BVH_LBVH, PT_FLAG_SKIP_DEAD_SEGMENTS = 64, 128, 256, 512, 1024
 
 PtHit_dtype = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("instance", "<u4"), ("primitive_index", "<u4"),
                         ("triangle_index", "<u4")])
@@ -114,7 +114,6 @@ def lib():
         L.pt_camera_pack.argtypes = [C.POINTER(PtCameraState), C.c_uint32, C.POINTER(PtCamera)]
         L.pt_create_from_gltf.argtypes = [C.c_char_p, C.POINTER(PtRenderConfig), C.POINTER(C.c_void_p)]
         L.pt_create_sibling.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
-        L.pt_create_sibling_part.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.pt_debug_bvh_digest.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 6)]
         L.pt_set_instance_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_float)]
         L.pt_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
@@ -268,16 +267,6 @@ class Renderer:
         other.handle = C.c_void_p()
         other.cfg = self.cfg
         check(lib().pt_create_sibling(self.handle, C.byref(other.handle)))
-        other.width, other.height = self.width, self.height
-        return other
-
-    def sibling_part(self, rank, world):
-        """A further context on the same GPU that renders the interleaved tiles `tile % world == rank` only (own stream, path
-        state, zero-initialised image); the images of all shares sum to the frame.  Deinit it before this renderer."""
-        other = Renderer.__new__(Renderer)
-        other.handle = C.c_void_p()
-        other.cfg = self.cfg
-        check(lib().pt_create_sibling_part(self.handle, rank, world, C.byref(other.handle)))
         other.width, other.height = self.width, self.height
         return other
 

@@ -213,7 +213,13 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     if ((rc = dev_alloc(&r->d_instances_raw, inst.size())) != PT_OK) return rc;
     if (!inst.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_instances_raw, inst.data(), inst.size() * sizeof(PtInstance), cudaMemcpyHostToDevice, r->stream));
     // acceleration structures (createBlases + Tlas.init)
-    if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, r->cfg.flags & (PT_FLAG_BVH_PLOC | PT_FLAG_BVH_SAH | PT_FLAG_BVH_OPTIMAL_COLLAPSE), r->stream, &r->bvh)) != PT_OK) return rc;
+    // builder stages: binned SAH + cost-optimal collapse unless the caller picks (measured on B200, profiles/r2a_builders.txt:
+    // C2 trace 1.328 -> 1.202 ms, C5 52.8 -> 46.4 ms, C4 14.97 -> 14.41 ms against the radix tree + greedy collapse; the build
+    // is 3-4x slower — 24 ms for 259 k triangles — and, like the reference's prefer_fast_trace build, off the frame path)
+    uint32_t builder = r->cfg.flags & (PT_FLAG_BVH_PLOC | PT_FLAG_BVH_SAH | PT_FLAG_BVH_OPTIMAL_COLLAPSE | PT_FLAG_BVH_LBVH);
+    if (builder == 0u) builder = PT_FLAG_BVH_SAH | PT_FLAG_BVH_OPTIMAL_COLLAPSE;
+    builder &= ~(uint32_t)PT_FLAG_BVH_LBVH;
+    if ((rc = build_scene_bvh(r->d_blob, r->d_prims, prims, meshes, r->d_instances_raw, inst, builder, r->stream, &r->bvh)) != PT_OK) return rc;
     r->h_instances = inst;
     if ((rc = dev_alloc(&r->d_instances, inst.size())) != PT_OK) return rc;
     if ((rc = upload_instance_records(r)) != PT_OK) return rc;
@@ -224,42 +230,6 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     PT_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&sc.error_flag), r->h_error, 0));
     sc.num_instances = (uint32_t)inst.size(); sc.num_prims = (uint32_t)prims.size();
     sc.num_materials = (uint32_t)s->num_materials; sc.num_textures = (uint32_t)s->num_textures;
-#ifdef PT_OCCLUSION_LAST
-    {
-        // every (instance, triangle) with a non-zero emissive factor (material.glsl:50-53: factor 0 makes the emission exactly 0
-        // whatever the texture says); more than 32 of them and the variant stays off for this scene
-        std::vector<Bvh8Tri> em;
-        bool too_many = false;
-        auto bits = [](uint32_t v) { float f; std::memcpy(&f, &v, 4); return f; };
-        for (size_t i = 0; i < inst.size() && !too_many; ++i) {
-            const PtMesh& m = meshes[inst[i].mesh_index];
-            for (uint32_t p = m.start; p < m.end && !too_many; ++p) {
-                const PtPrimitive& pr = s->primitives[p];
-                if ((s->materials[pr.info & PT_MATERIAL_INDEX_MASK].emissive_factor & 0xFFFFFFu) == 0u) continue;
-                for (uint32_t t = 0; t < pr.triangle_count; ++t) {
-                    if (em.size() >= 32) { too_many = true; break; }
-                    uint32_t id[3];
-                    for (int k = 0; k < 3; ++k)
-                        id[k] = (pr.info & PT_UINT32_INDICES_MASK) ? reinterpret_cast<const uint32_t*>(s->triangle_data + pr.indices_offset)[3 * (size_t)t + k]
-                                                                   : reinterpret_cast<const uint16_t*>(s->triangle_data + pr.indices_offset)[3 * (size_t)t + k];
-                    const float* pos = reinterpret_cast<const float*>(s->triangle_data + pr.positions_offset);
-                    Bvh8Tri tr;
-                    tr.v0 = make_float4(pos[3 * (size_t)id[0]], pos[3 * (size_t)id[0] + 1], pos[3 * (size_t)id[0] + 2], bits(p));
-                    tr.v1 = make_float4(pos[3 * (size_t)id[1]], pos[3 * (size_t)id[1] + 1], pos[3 * (size_t)id[1] + 2], bits(t));
-                    tr.v2 = make_float4(pos[3 * (size_t)id[2]], pos[3 * (size_t)id[2] + 1], pos[3 * (size_t)id[2] + 2], bits((uint32_t)i));
-                    em.push_back(tr);
-                }
-            }
-        }
-        if ((rc = dev_alloc(&r->d_emissive, std::max<size_t>(em.size(), 1))) != PT_OK) return rc;
-        if (!too_many && !em.empty()) {
-            PT_CUDA_CHECK(cudaMemcpyAsync(r->d_emissive, em.data(), em.size() * sizeof(Bvh8Tri), cudaMemcpyHostToDevice, r->stream));
-            PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));     // em is a stack temporary
-        }
-        sc.emissive_tris = r->d_emissive;
-        sc.num_emissive = too_many ? kInvalidId : (uint32_t)em.size();
-    }
-#endif
     return PT_OK;
 }
 
@@ -272,7 +242,6 @@ void destroy_impl(PtRenderer* r) {
     if (r->owns_scene) {
         for (auto p : r->d_texels) cudaFree(p);
         for (auto p : r->d_atlases) cudaFree(p);
-        cudaFree(r->d_emissive);
         cudaFree(r->d_blob); cudaFree(r->d_prims); cudaFree(r->d_materials); cudaFree(r->d_textures);
         cudaFree(r->d_instances_raw); cudaFree(r->d_instances);
         r->bvh.release();
@@ -398,28 +367,19 @@ int pt_create_from_gltf(const char* scene_path, const PtRenderConfig* config, Pt
 // between a renderer and its sibling keeps two frames in flight -- the reference does the same with one command
 // buffer and fence per swapchain image (main.zig:209-217,255-259) -- so the tail of one frame's last wavefront
 // overlaps the next frame's ray generation and primary traversal.
-static int create_sibling_impl(PtRenderer* parent, const int* part, PtRenderer** out);
+static int create_sibling_impl(PtRenderer* parent, PtRenderer** out);
 
 int pt_create_sibling(PtRenderer* parent, PtRenderer** out) {
     PT_REQUIRE(parent && out, "pt_create_sibling: null argument");
-    return create_sibling_impl(parent, nullptr, out);
+    return create_sibling_impl(parent, out);
 }
 
-int pt_create_sibling_part(PtRenderer* parent, int rank, int world, PtRenderer** out) {
-    PT_REQUIRE(parent && out, "pt_create_sibling_part: null argument");
-    *out = nullptr;
-    PT_REQUIRE(world >= 1 && rank >= 0 && rank < world, "pt_create_sibling_part: invalid rank/world");
-    const int part[2] = {rank, world};
-    return create_sibling_impl(parent, part, out);
-}
-
-static int create_sibling_impl(PtRenderer* parent, const int* part, PtRenderer** out) {
+static int create_sibling_impl(PtRenderer* parent, PtRenderer** out) {
     *out = nullptr;
     PT_REQUIRE(parent->owns_scene, "pt_create_sibling: the parent must be a renderer made by pt_create");
     PT_CUDA_CHECK(cudaSetDevice(parent->device));
     PtRenderer* r = new PtRenderer();
     r->cfg = parent->cfg;
-    if (part) { r->cfg.partition = PT_PARTITION_TILES; r->cfg.rank = part[0]; r->cfg.world = part[1]; }
     r->device = parent->device; r->num_sms = parent->num_sms; r->dims = parent->dims; r->h_error = parent->h_error; r->owns_scene = false; r->parent = parent;
     r->d_blob = parent->d_blob; r->d_prims = parent->d_prims; r->d_materials = parent->d_materials; r->d_textures = parent->d_textures;
     r->d_instances_raw = parent->d_instances_raw; r->d_instances = parent->d_instances;

@@ -436,8 +436,6 @@ struct CollapseArgs {
     const float* leaf_hi;
     uint32_t max_leaf;          // 3 for a BLAS (triangles per leaf slot), 1 for the TLAS
     const uint8_t* dp;          // decisions of k_collapse_dp (8 per binary node), or nullptr: greedy surface-area expansion
-    uint32_t pack_below;        // subtrees with at most this many leaves become ONE leaf-only node (0 = off; needs
-                                // contiguous leaf ranges, i.e. the Morton radix tree)
     // outputs
     Bvh8Node* nodes8;           // global node array
     uint4* node_bits8;          // 2 per node
@@ -510,29 +508,6 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
         const uint32_t l = n.left, r = n.right;
         ch[best] = load_child(a, l);
         ch[cnt++] = load_child(a, r);
-    }
-    // Bottom of the tree: when the greedy expansion ran out of slots although the whole subtree would fit into
-    // one node (<= 8 slots of <= max_leaf leaves), the leftover inner children would become tiny nodes with two
-    // or three slots each -- a full node test per ray for very little culling.  Pack the subtree instead: its
-    // leaves are a contiguous run of the Morton order, cut into consecutive groups of max_leaf.
-    if (a.pack_below && !optimal) {
-        bool leftover = false;
-        for (int c = 0; c < cnt; ++c) leftover = leftover || !ch[c].leaf;
-        const uint2 rg = a.range[b2];
-        const uint32_t total = rg.y - rg.x + 1u;
-        if (leftover && total <= a.pack_below) {
-            cnt = 0;
-            for (uint32_t j0 = rg.x; j0 <= rg.y; j0 += a.max_leaf) {
-                CChild c;
-                c.first = j0; c.count = min(a.max_leaf, rg.y - j0 + 1u); c.ref = 0x80000000u | j0; c.leaf = true;
-                for (int k = 0; k < 3; ++k) { c.lo[k] = 3.0e38f; c.hi[k] = -3.0e38f; }
-                for (uint32_t t = 0; t < c.count; ++t) {
-                    const size_t src = a.order[j0 + t];
-                    for (int k = 0; k < 3; ++k) { c.lo[k] = fminf(c.lo[k], a.leaf_lo[3 * src + k]); c.hi[k] = fmaxf(c.hi[k], a.leaf_hi[3 * src + k]); }
-                }
-                ch[cnt++] = c;
-            }
-        }
     }
     // node frame
     float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
@@ -687,7 +662,6 @@ struct Scratch {
     uint32_t* cur_parent = nullptr;   // parent links of the tree just built (Karras layout), for k_collapse_dp
     uint32_t sah_levels = 0;
     uint32_t capacity = 0;        // entries of wq2 / wq8
-    uint32_t pack_below = 0;      // CollapseArgs::pack_below for BLASes (measured slower on C2 / C4: off)
     uint32_t max_leaf = 2;        // triangles per BLAS leaf slot (format limit 3; measured 1 / 2 / 3 on C2: 1.438 / 1.406 /
                                   // 1.429 ms, on C4: 19.4 / 19.5 / 20.3 ms -- a triangle test costs ~0.7 node tests here)
     uint32_t refit_repairs = 0;   // nodes the verification pass had to correct (expected 0)
@@ -825,18 +799,9 @@ int alloc_scratch(Scratch& s, uint32_t L, size_t max_prims, uint32_t builder_fla
         s.cub_bytes = std::max(s.cub_bytes, scan_bytes);
     }
     PT_CU(cudaMalloc(&s.cub_temp, std::max<size_t>(s.cub_bytes, 16)));
-    {
-        const char* e = std::getenv("PT_BVH_PLOC");     // A/B switch for tools/; the API switch is PT_FLAG_BVH_PLOC
-        s.lbvh = !(use_ploc || (e && e[0] == '1'));
-        const char* pk = std::getenv("PT_BVH_PACK");    // A/B switch for tools/
-        if (pk) s.pack_below = (uint32_t)std::atoi(pk);
-        const char* sh = std::getenv("PT_BVH_SAH");     // A/B switches for tools/; the API switches are PT_FLAG_BVH_SAH / _OPTIMAL_COLLAPSE
-        s.sah = (builder_flags & PT_FLAG_BVH_SAH) != 0 || (sh && sh[0] == '1');
-        const char* oc = std::getenv("PT_BVH_OPTCOLLAPSE");
-        s.optimal = (builder_flags & PT_FLAG_BVH_OPTIMAL_COLLAPSE) != 0 || (oc && oc[0] == '1');
-        const char* ml = std::getenv("PT_BVH_MAXLEAF");
-        if (ml) s.max_leaf = (uint32_t)std::max(1, std::min(3, std::atoi(ml)));
-    }
+    s.lbvh = !use_ploc;
+    s.sah = (builder_flags & PT_FLAG_BVH_SAH) != 0;
+    s.optimal = (builder_flags & PT_FLAG_BVH_OPTIMAL_COLLAPSE) != 0;
     if (s.sah) {
         const size_t S = (size_t)L / 2 + 1;
         for (int k = 0; k < 2; ++k) {
@@ -977,7 +942,7 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
         k_reorder_tris<<<blocks_for(n), kThreads, 0, st>>>(s.tmp_tris, s.vals_out, n, out->tris2 + out->tri_off[m]);
         CollapseArgs a{};
         a.nodes2 = n2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
-        a.max_leaf = s.max_leaf; a.pack_below = s.lbvh ? s.pack_below : 0u; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tri_counter;
+        a.max_leaf = s.max_leaf; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tri_counter;
         a.tris_sorted = out->tris2 + out->tri_off[m]; a.tris8 = out->tris8; a.leaf_ids = nullptr; a.leaf_out = nullptr;
         a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = tail; a.capacity = L + 8; a.overflow = overflow;
         PT_TRY(collapse_tree(s, a, n, &out->blas_root8[m], st));
@@ -991,9 +956,8 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
         PT_CU(cudaMalloc(&out->mesh_tri_range, sizeof(uint2) * rg.size()));
         PT_CU(cudaMemcpyAsync(out->mesh_tri_range, rg.data(), sizeof(uint2) * rg.size(), cudaMemcpyHostToDevice, st));
         PT_CU(cudaStreamSynchronize(st));
-        const char* e = std::getenv("PT_TLAS_CORNER_BOXES");   // A/B switch for tools/
         // exact boxes touch every instanced triangle once per (re)build: bounded so that it stays well under a millisecond
-        out->exact_instance_boxes = !(e && e[0] == '1') && instanced <= (64ull << 20);
+        out->exact_instance_boxes = instanced <= (64ull << 20);
     }
     PT_CU(cudaMemcpyAsync(&out->tlas_node_base, node_counter, 4, cudaMemcpyDeviceToHost, st));
     PT_CU(cudaStreamSynchronize(st));

@@ -113,13 +113,6 @@ struct DeviceScene {
     // set to 1 by a walker that had to drop a stack push (hierarchy deeper than the fixed traversal stack): host-mapped, so
     // pt_sync / pt_get_stats can report PT_ERR_TRAVERSAL_STACK instead of returning an image with missed hits
     uint32_t* error_flag;
-#ifdef PT_OCCLUSION_LAST
-    // A/B variant ("last segments as occlusion queries"): every (instance, triangle) whose material has a
-    // non-zero emissive factor, object-space vertices, ids in the w lanes (v0.w primitive, v1.w triangle, v2.w instance).
-    // num_emissive == kInvalidId: too many of them, the variant is off for this scene.
-    const Bvh8Tri* emissive_tris;
-    uint32_t num_emissive;
-#endif
 };
 
 // Hit record in HBM: 32 bytes (2 x 16 B)

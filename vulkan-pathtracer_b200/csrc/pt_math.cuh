@@ -3,12 +3,14 @@
 // Arithmetic contract: IEEE binary32; this translation unit is compiled with
 // --fmad=false so a*b+c is never contracted (FMAs are written explicitly with __fmaf_rn where they
 // are wanted: the conservative box tests); expressions are evaluated left to right as written;
-// sqrtf and / are the correctly rounded CUDA defaults (-prec-sqrt/-prec-div); sin/cos are computed
-// in double and rounded to float; min/max follow GLSL 8.3 (min(x,y) = y<x ? y : x).
+// sqrtf and / are the correctly rounded CUDA defaults (-prec-sqrt/-prec-div); sin/cos are the
+// explicit double-precision evaluation of include/b200pt_contract.h, rounded to float; min/max follow GLSL 8.3 (min(x,y) = y<x ? y : x).
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+
+#include "../../include/b200pt_contract.h"
 
 namespace pt {
 
@@ -39,19 +41,9 @@ PT_HD float mixf(float a, float b, float t) { return a * (1.0f - t) + b * t; }
 PT_HD V3 mix(V3 a, V3 b, float t) { return v3(mixf(a.x, b.x, t), mixf(a.y, b.y, t), mixf(a.z, b.z, t)); }
 PT_HD float comp(V3 a, int k) { return k == 0 ? a.x : (k == 1 ? a.y : a.z); }
 
-// correctly rounded fp32 sin / cos: evaluated in double, rounded once
-PT_D float sin_cr(float x) { return (float)sin((double)x); }
-PT_D float cos_cr(float x) { return (float)cos((double)x); }
-#ifdef PT_SHADE_SINCOS
-// A/B variant: one double-precision sincos() (one argument reduction) instead of sin() + cos().  Its double results may
-// differ from sin() / cos() in the last place, which changes the rounded float only when the double lands within that
-// distance of a float rounding boundary -- the parity tests decide whether it ships.
-PT_D void sincos_cr(float x, float& s, float& c) {
-    double sd, cd;
-    sincos((double)x, &sd, &cd);
-    s = (float)sd; c = (float)cd;
-}
-#endif
+// sin / cos of the arithmetic contract (include/b200pt_contract.h): explicit IEEE double arithmetic, the same bits here, in
+// the CPU oracle and in the reference shaders compiled as C++ — no library call on any side
+PT_HD void sincos_cr(float x, float& s, float& c) { pt_contract_sincos(x, &s, &c); }
 
 // row-major 3x3
 struct M3 { float m[3][3]; };

@@ -100,21 +100,9 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace(DeviceScene sc, PathBuf
             const float4 ro = pb.ray_o[slot], rd = pb.ray_d[slot];
             Hit h;
             if (MODE == TRACE_BVH2) trace_bvh2(sc, tlas2_count, tlas2_leaf_instance, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h);
-#ifdef PT_OCCLUSION_LAST
-            else if (MODE == TRACE_BVH8_COUNT) {
-                // the algorithmic-byte counter follows the same rule as K-trace: flagged rays are first-hit queries
-                Hit init;
-                const bool occl = (__float_as_uint(pb.ray_e[slot].w) & 32u) != 0u;
-                if (occl) {
-                    const float4 ha = pb.hit_a[slot]; const uint2 hb = pb.hit_b[slot];
-                    init.t = ha.x; init.b1 = ha.y; init.b2 = ha.z; init.inst = __float_as_uint(ha.w); init.prim = hb.x; init.tri = hb.y;
-                }
-                trace_bvh8<true>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, &cnt_nodes, &cnt_tris, occl ? &init : nullptr);
-            }
-#else
             else if (MODE == TRACE_BVH8_COUNT) trace_bvh8<true>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, &cnt_nodes, &cnt_tris);
-#endif
             else trace_bvh8<false>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, nullptr, nullptr);
+            hit_finish(h);
             pb.hit_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.inst));
             pb.hit_b[slot] = make_uint2(h.prim, h.tri);
         }
@@ -141,6 +129,7 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_rays(DeviceScene sc, co
             Hit h;
             if (MODE == TRACE_BVH2) trace_bvh2(sc, tlas2_count, tlas2_leaf_instance, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax, h);
             else trace_bvh8<false>(sc, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax, h, nullptr, nullptr);
+            hit_finish(h);
             HitRec o;
             o.t = h.t; o.b1 = h.b1; o.b2 = h.b2; o.instance = h.inst; o.primitive_index = h.prim; o.triangle_index = h.tri;
             o._pad0 = 0; o._pad1 = 0;
@@ -366,13 +355,10 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                                     else atten = atten / p;
                                 }
                             }
-#ifdef PT_SKIP_DEAD_LAST
-                            // A/B variant: the last segment draws no random numbers and only adds atten * (emission | sky), both
-                            // finite, so with a throughput of exactly zero (brdf() == 0: shading normal facing away from the
-                            // viewer) it adds exactly nothing and is not traced.  11 % of C2's bounce rays; bit-identity checked
-                            // in the CPU restatement (tests/test_oracle_trace.py).
-                            if (j + 1u >= B && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) { emit = false; end_sample = true; }
-#endif
+                            // PT_FLAG_SKIP_DEAD_SEGMENTS: the last segment draws no random numbers and only adds
+                            // atten * (emission | sky), both finite, so with a throughput of exactly zero (brdf() == 0: shading normal
+                            // facing away from the viewer) it adds exactly nothing and is not traced (C2: 5 % of all rays)
+                            if ((fp.flags & PT_FLAG_SKIP_DEAD_SEGMENTS) && emit && j + 1u >= B && atten.x == 0.0f && atten.y == 0.0f && atten.z == 0.0f) { emit = false; end_sample = true; }
                         }
                     } else {
                         end_sample = true;   // last segment: loop bound reached (:49)
@@ -390,37 +376,7 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                 from_cache = true;
             }
             if (emit) {
-#ifdef PT_OCCLUSION_LAST
-                // The ray just sampled is the last segment of its sample: it only adds the emission of what it hits, or the
-                // sky.  Take the lexicographically closest hit among the scene's few emissive triangles here (same
-                // intersect_tri and object-space frames as K-trace, all lanes busy), hand it to K-trace as the slot's
-                // initial hit and flag the ray: K-trace stops it at the first candidate that beats that hit -- a non-emissive
-                // blocker by construction, so the sample adds the same exact zero as its true closest hit would.
-                uint32_t occl = 0u;
-                if (sc.num_emissive != kInvalidId && j > 0u && j + 1u >= B && !(fp.flags & (PT_FLAG_TRACE_BVH2 | PT_FLAG_TRACE_WALKER))) {
-                    Hit cand;
-                    hit_init(cand);
-                    for (uint32_t e = 0; e < sc.num_emissive; ++e) {
-                        const float4* q = reinterpret_cast<const float4*>(sc.emissive_tris + e);
-                        const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
-                        const uint32_t inst = __float_as_uint(p2.w);
-                        V3 oo = origin, dd = direction;
-                        if (!(__ldg(&sc.instances[inst].mesh) & kInstIdentity)) to_object(sc.instances, inst, origin, direction, oo, dd);
-                        const RayPre rp = ray_precompute(dd);
-                        float t, b1, b2;
-                        if (intersect_tri(oo, rp, p0, p1, p2, 0.001f, 10000.0f, t, b1, b2)) {
-                            const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
-                            if (hit_better(t, inst, prim, tri, cand)) { cand.t = t; cand.b1 = b1; cand.b2 = b2; cand.inst = inst; cand.prim = prim; cand.tri = tri; }
-                        }
-                    }
-                    pb.hit_a[slot] = make_float4(cand.t, cand.b1, cand.b2, __uint_as_float(cand.inst));
-                    pb.hit_b[slot] = make_uint2(cand.prim, cand.tri);
-                    occl = 32u;
-                }
-                store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, origin, direction, 0.001f, 10000.0f, occl);
-#else
                 store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, origin, direction, 0.001f, 10000.0f);
-#endif
                 pb.atten_sx[slot] = make_float4(atten.x, atten.y, atten.z, __uint_as_float(seed.x));
                 pb.color_sy[slot] = make_float4(color.x, color.y, color.z, __uint_as_float(seed.y));
                 pb.final_sb[slot] = make_float4(final_color.x, final_color.y, final_color.z, __uint_as_float(s | (j << 16)));

@@ -22,7 +22,6 @@ struct PtRenderer {
     cudaEvent_t ev_frame_done = nullptr, ev_copy_done = nullptr;
     bool copy_pending = false;
     // scene on the device
-    pt::Bvh8Tri* d_emissive = nullptr;       // PT_OCCLUSION_LAST variant: the scene's emissive triangles (DeviceScene::emissive_tris)
     uint8_t* d_blob = nullptr;
     pt::PrimRec* d_prims = nullptr;
     pt::MatRec* d_materials = nullptr;

@@ -83,13 +83,9 @@ PT_D V3 sample_ggx_vndf(V3 view_dir, float rx, float ry, V2 rs) {
     float phi = (2.0f * kPi) * rs.x;
     float z = 1.0f - rs.y * (1.0f + transformed_view.z);
     float sin_theta = sqrtf(gmax(0.0f, 1.0f - z * z));
-#ifdef PT_SHADE_SINCOS
     float sp, cp;
     sincos_cr(phi, sp, cp);
     V3 hemisphere_sample = v3(sin_theta * cp, sin_theta * sp, z);
-#else
-    V3 hemisphere_sample = v3(sin_theta * cos_cr(phi), sin_theta * sin_cr(phi), z);
-#endif
     V3 sum = hemisphere_sample + transformed_view;
     return normalize(v3(sum.x * rx, sum.y * ry, sum.z));
 }
@@ -141,13 +137,9 @@ PT_D V3 sample_hemisphere_psa(V2 rs) {
     float phi = (2.0f * kPi) * rs.x;
     float radius = sqrtf(rs.y);
     float z = sqrtf(1.0f - radius * radius);
-#ifdef PT_SHADE_SINCOS
     float sp, cp;
     sincos_cr(phi, sp, cp);
     return v3(radius * cp, radius * sp, z);
-#else
-    return v3(radius * cos_cr(phi), radius * sin_cr(phi), z);
-#endif
 }
 // brdf.glsl:115-117
 PT_D float get_hemisphere_psa_density(float sampled_z) { return gmax(0.0f, sampled_z) / kPi; }

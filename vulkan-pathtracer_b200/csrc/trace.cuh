@@ -73,9 +73,21 @@ PT_D bool intersect_tri(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2,
     return true;
 }
 
+#ifdef PT_TRACE_FINAL_BARY
+// A/B variant: the closest hit keeps the unnormalised barycentrics (V, W in b1, b2) and the determinant; the two IEEE
+// divisions b1 = V / det, b2 = W / det are done once, when the ray's result is stored (same operands, same bits)
+struct Hit { float t, b1, b2, det; uint32_t inst, prim, tri; };
+#else
 struct Hit { float t, b1, b2; uint32_t inst, prim, tri; };
+#endif
 
+#ifdef PT_TRACE_FINAL_BARY
+PT_D void hit_init(Hit& h) { h.t = kMissT; h.b1 = 0.0f; h.b2 = 0.0f; h.det = 1.0f; h.inst = h.prim = h.tri = kInvalidId; }
+PT_D void hit_finish(Hit& h) { h.b1 = h.b1 / h.det; h.b2 = h.b2 / h.det; }
+#else
 PT_D void hit_init(Hit& h) { h.t = kMissT; h.b1 = 0.0f; h.b2 = 0.0f; h.inst = h.prim = h.tri = kInvalidId; }
+PT_D void hit_finish(Hit&) {}
+#endif
 
 PT_D bool hit_better(float t, uint32_t inst, uint32_t prim, uint32_t tri, const Hit& h) {
     if (t < h.t) return true;
@@ -90,18 +102,19 @@ PT_D void test_triangle(const Bvh8Tri* __restrict__ tris, uint32_t idx, V3 o, co
     const float4* q = reinterpret_cast<const float4*>(tris + idx);
     const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
     // tmax stays the ray's tmax: candidates with t == best.t must reach the tie-break
-#ifdef PT_TRACE_LATE_BARY
-    // A/B variant: the two barycentric divisions only for candidates that replace the closest hit (same operands, same bits)
+#ifdef PT_TRACE_FINAL_BARY
+    float t, V, W, det;
+    if (intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t, V, W, det)) {
+        const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
+        if (hit_better(t, inst, prim, tri, best)) { best.t = t; best.b1 = V; best.b2 = W; best.det = det; best.inst = inst; best.prim = prim; best.tri = tri; }
+    }
+#else
+    // the two barycentric divisions only for candidates that replace the closest hit (same operands, same bits; measured
+    // C2 1.334 -> 1.312 ms, C4 14.98 -> 14.83 ms, profiles/r2a_variants.txt)
     float t, V, W, det;
     if (intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t, V, W, det)) {
         const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
         if (hit_better(t, inst, prim, tri, best)) { best.t = t; best.b1 = V / det; best.b2 = W / det; best.inst = inst; best.prim = prim; best.tri = tri; }
-    }
-#else
-    float t, b1, b2;
-    if (intersect_tri(o, rp, p0, p1, p2, tmin, tmax, t, b1, b2)) {
-        const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
-        if (hit_better(t, inst, prim, tri, best)) { best.t = t; best.b1 = b1; best.b2 = b2; best.inst = inst; best.prim = prim; best.tri = tri; }
     }
 #endif
 }
@@ -131,11 +144,11 @@ PT_D void frame_set(RayFrame& f, V3 o, V3 d) {
 // where rays are born (K-raygen / K-shade / k_ray_setup, all lanes busy) instead of in K-trace,
 // where refilled lanes would do it two at a time (profiles/r1a: 22 % of K-trace's issue slots).
 PT_D void store_ray(float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ ray_e, float4* __restrict__ ray_s,
-                    float4* __restrict__ ray_m, uint32_t slot, V3 o, V3 d, float tmin, float tmax, uint32_t extra_bits = 0u) {
+                    float4* __restrict__ ray_m, uint32_t slot, V3 o, V3 d, float tmin, float tmax) {
     RayFrame f;
     frame_set(f, o, d);
     const RayPre rp = ray_precompute(d);
-    const uint32_t bits = f.rs | ((uint32_t)rp.kz << 3) | extra_bits;     // bit 5: occlusion query (PT_OCCLUSION_LAST variant)
+    const uint32_t bits = f.rs | ((uint32_t)rp.kz << 3);
     ray_o[slot] = make_float4(o.x, o.y, o.z, tmin);
     ray_d[slot] = make_float4(d.x, d.y, d.z, tmax);
     ray_e[slot] = make_float4(f.idir.x, f.idir.y, f.idir.z, __uint_as_float(bits));
@@ -215,14 +228,8 @@ PT_D uint32_t node_test(const Bvh8Node* __restrict__ nodes, uint32_t idx, const 
 // counters (optional): [0] += nodes decoded, [1] += triangles tested.
 template <bool kCount>
 PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, Hit& best, uint32_t* n_nodes, uint32_t* n_tris
-#ifdef PT_OCCLUSION_LAST
-                     , const Hit* init = nullptr      // occlusion query: start from this hit, return at the first candidate that beats it
-#endif
 ) {
     hit_init(best);
-#ifdef PT_OCCLUSION_LAST
-    if (init) best = *init;
-#endif
     if (sc.tlas_root == kInvalidId) return;
     RayFrame world, f;
     frame_set(world, o, d);
@@ -260,9 +267,6 @@ PT_D void trace_bvh8(const DeviceScene& sc, V3 o, V3 d, float tmin, float tmax, 
                 T.y &= T.y - 1u;
                 test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
                 if (kCount) ++*n_tris;
-#ifdef PT_OCCLUSION_LAST
-                if (init && (best.t != init->t || best.inst != init->inst || best.prim != init->prim || best.tri != init->tri)) return;
-#endif
             }
         } else if (T.y) {
             // TLAS leaf item = instance: enter the first, keep the rest for later

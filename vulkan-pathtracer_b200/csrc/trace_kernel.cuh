@@ -111,6 +111,11 @@ struct TraceIO {
 
 constexpr int kTraceBlock = 128;
 constexpr int kStackSize = 64;
+#ifdef PT_TRACE_REFILL_MIN
+constexpr int kRefillMin = PT_TRACE_REFILL_MIN;
+#else
+constexpr int kRefillMin = 4;
+#endif
 
 // world-space ray frame + shear constants of one slot (what store_ray() wrote)
 PT_D void load_ray(const TraceIO& io, uint32_t slot, RayFrame& f, RayPre& rp, float& tmin, float& tmax) {
@@ -145,6 +150,11 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     const uint32_t bias = io.bias_word;
     // octant permutation of the inner-child hit byte: lut[rs * 256 + mask]
     __shared__ uint8_t perm_lut[8 * 256];
+#ifdef PT_TRACE_TRI_SHARE
+    __shared__ uint2 s_item[kTraceBlock / 32][32];       // (owner lane, triangle index) of the warp's pending pairs
+    __shared__ float4 s_res[kTraceBlock / 32][32];       // candidate of pair k: t (kMissT: none), b1, b2, primitive (bits)
+    __shared__ uint32_t s_res_tri[kTraceBlock / 32][32];
+#endif
     for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) perm_lut[i] = (uint8_t)perm8(i & 255u, i >> 8);
     __syncthreads();
     // warp-uniform chunk of the queue: 32 rays per global atomic.  Larger chunks save atomics but leave the last
@@ -162,24 +172,11 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     RayPre rp;
     float tmin = 0.0f, tmax = 0.0f;
     uint32_t cur_inst = kInvalidId;
-#ifdef PT_OCCLUSION_LAST
-    bool occl = false;
-#endif
     Hit best;
     uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
-#ifdef PT_TRACE_SMEM_STACK
-    // A/B variant (tools/build_variant.sh smem8 -DPT_TRACE_SMEM_STACK=8): the bottom PT_TRACE_SMEM_STACK entries of every
-    // lane's stack live in shared memory (entry-major, so a warp's accesses to one level are conflict-free), deeper
-    // entries in thread-local memory.  Default: all of it in thread-local memory (L1-resident).
-    __shared__ uint2 sstack[PT_TRACE_SMEM_STACK * kTraceBlock];
-    uint2 stack[kStackSize - PT_TRACE_SMEM_STACK];
-#define PT_STACK_PUSH(v) do { if (sp >= kStackSize) { *sc.error_flag = 1u; break; } if (sp < PT_TRACE_SMEM_STACK) sstack[sp * kTraceBlock + threadIdx.x] = (v); else stack[sp - PT_TRACE_SMEM_STACK] = (v); ++sp; } while (0)
-#define PT_STACK_POP(e) do { --sp; if (sp < PT_TRACE_SMEM_STACK) (e) = sstack[sp * kTraceBlock + threadIdx.x]; else (e) = stack[sp - PT_TRACE_SMEM_STACK]; } while (0)
-#else
     uint2 stack[kStackSize];
 #define PT_STACK_PUSH(v) do { if (sp < kStackSize) stack[sp++] = (v); else *sc.error_flag = 1u; } while (0)
 #define PT_STACK_POP(e) do { (e) = stack[--sp]; } while (0)
-#endif
     int sp = 0;
     hit_init(best);
     f.o = v3s(0.0f); f.idir = v3s(1.0f); f.rs = 7u;
@@ -188,14 +185,11 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     for (;;) {
         // ---- dynamic fetch: refill idle lanes from the warp's chunk
         const uint32_t idle = __ballot_sync(0xffffffffu, !active);
-#ifdef PT_TRACE_REFILL_MIN
-        // A/B variant (tools/build_variant.sh refill8 -DPT_TRACE_REFILL_MIN=8): refill only once that many lanes are idle.
-        // The fetch path runs at ~3.6 lanes and is 5-7 % of K-trace's warp instructions (profiles/r1g_ncu_lines_trace.txt);
-        // waiting trades it against idle lanes in the node phase.  Results do not depend on it.
-        if (__popc(idle) >= PT_TRACE_REFILL_MIN && !exhausted) {
-#else
-        if (idle != 0u && !exhausted) {
-#endif
+        // refill once kRefillMin lanes are idle: the fetch path runs at a few lanes (5-7 % of K-trace's warp instructions when
+        // every idle lane is refilled at once), waiting trades it against idle lanes in the node phase.  Measured on B200
+        // (profiles/r2a_variants.txt, threshold 1 / 4 / 8 / 16): C2 1.334 / 1.290 / 1.302 / 1.354 ms, C4 14.98 / 14.51 / 14.71 /
+        // 15.60 ms, one rank's share of C3 at 8 GPUs 116.7 / 114.1 / 115.3 / 122.7 ms.  Results do not depend on it.
+        if (__popc(idle) >= kRefillMin && !exhausted) {
             if (w_next == w_end) {
                 uint32_t base = 0;
                 if (lane == 0) base = atomicAdd(io.cursor, chunk);
@@ -214,14 +208,6 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                         load_ray(io, slot, f, rp, tmin, tmax);
                         cur_inst = sc.start_inst;
                         hit_init(best);
-#ifdef PT_OCCLUSION_LAST
-                        occl = (__float_as_uint(io.ray_e[slot].w) & 32u) != 0u;
-                        if (occl) {   // the closest emissive hit found by K-shade (or a miss): anything that beats it ends the ray
-                            const float4 ha = io.hit_a[(size_t)slot * io.hit_a_stride];
-                            const uint2 hb = io.hit_b[(size_t)slot * io.hit_b_stride];
-                            best.t = ha.x; best.b1 = ha.y; best.b2 = ha.z; best.inst = __float_as_uint(ha.w); best.prim = hb.x; best.tri = hb.y;
-                        }
-#endif
                         sp = 0;
                         G = make_uint2(sc.start_root, 0x80000000u);
                         T = make_uint2(0u, 0u);
@@ -238,22 +224,75 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         // ---- phase 1: one leaf item.  (Postponing triangle groups while few lanes hold one — Ylitie et
         // al. 2017 — and repeating the phase while many do were both measured: neither pays here, and the
         // warp votes they need cost 3-4 % each; profiles/r1_experiments.md.)
+#ifdef PT_TRACE_TRI_SHARE
+        // A/B variant: warp-cooperative triangle phase (north_star (b): "warp-level ballot/shuffle work redistribution").
+        // The pending (ray, triangle) pairs of the whole warp — lanes inside a BLAS — are numbered by a warp scan, published
+        // in shared memory and tested one pair per lane, 32 at a time: the worker fetches the owner's ray with shuffles,
+        // runs the same intersect_tri and hands the candidate back through shared memory, where the owner merges it with
+        // hit_better (a total order, so the result does not depend on who tested what).  Lanes at the top level keep the
+        // one-instance-per-iteration path below.
+        {
+            const bool in_blas = active && cur_inst != kInvalidId;
+            const uint32_t cnt = in_blas ? (uint32_t)__popc(T.y) : 0u;
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if ((int)lane >= o) incl += v; }
+            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+            if (total != 0u) {      // warp-uniform
+                const uint32_t wid = threadIdx.x >> 5;
+                const uint32_t excl = incl - cnt;
+                uint32_t m = T.y, published = 0u;
+                if (in_blas) {
+                    for (uint32_t j = excl; m != 0u && j < 32u; ++j) {
+                        const uint32_t b = (uint32_t)__ffs((int)m) - 1u;
+                        m &= m - 1u;
+                        s_item[wid][j] = make_uint2(lane, T.x + b);
+                        ++published;
+                    }
+                    T.y = m;        // pairs beyond the warp's first 32 wait for the next iteration
+                }
+                __syncwarp();
+                const uint32_t n_items = min(total, 32u);
+                const uint2 it = lane < n_items ? s_item[wid][lane] : make_uint2(lane, 0u);
+                const int src = (int)it.x;
+                const V3 so = v3(__shfl_sync(0xffffffffu, f.o.x, src), __shfl_sync(0xffffffffu, f.o.y, src), __shfl_sync(0xffffffffu, f.o.z, src));
+                RayPre srp;
+                srp.m0x = __shfl_sync(0xffffffffu, rp.m0x, src); srp.m0y = __shfl_sync(0xffffffffu, rp.m0y, src); srp.m0z = __shfl_sync(0xffffffffu, rp.m0z, src);
+                srp.m1x = __shfl_sync(0xffffffffu, rp.m1x, src); srp.m1y = __shfl_sync(0xffffffffu, rp.m1y, src); srp.m1z = __shfl_sync(0xffffffffu, rp.m1z, src);
+                srp.Sz = __shfl_sync(0xffffffffu, rp.Sz, src); srp.kz = __shfl_sync(0xffffffffu, rp.kz, src);
+                const float stmin = __shfl_sync(0xffffffffu, tmin, src), stmax = __shfl_sync(0xffffffffu, tmax, src);
+                if (lane < n_items) {
+                    const float4* q = reinterpret_cast<const float4*>(sc.tris + it.y);
+                    const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
+                    float t = kMissT, b1 = 0.0f, b2 = 0.0f;
+                    if (!intersect_tri(so, srp, p0, p1, p2, stmin, stmax, t, b1, b2)) t = kMissT;
+                    s_res[wid][lane] = make_float4(t, b1, b2, p0.w);
+                    s_res_tri[wid][lane] = __float_as_uint(p1.w);
+                }
+                __syncwarp();
+                for (uint32_t j = excl; j < excl + published; ++j) {
+                    const float4 c = s_res[wid][j];
+                    if (c.x != kMissT) {
+                        const uint32_t prim = __float_as_uint(c.w), tri = s_res_tri[wid][j];
+                        if (hit_better(c.x, cur_inst, prim, tri, best)) { best.t = c.x; best.b1 = c.y; best.b2 = c.z; best.inst = cur_inst; best.prim = prim; best.tri = tri; }
+                    }
+                }
+                __syncwarp();       // the arrays are rewritten in the next iteration
+            }
+        }
+        const bool has_t = active && T.y != 0u && cur_inst == kInvalidId;
+#else
         const bool has_t = active && T.y != 0u;
+#endif
         if (has_t) {
             const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
             T.y &= T.y - 1u;
-            if (cur_inst != kInvalidId) {
-#ifdef PT_OCCLUSION_LAST
-                const float t_before = best.t;
-                const uint32_t inst_before = best.inst, prim_before = best.prim, tri_before = best.tri;
-                test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
-                // an accepted candidate is lexicographically smaller, so at least one of the four changed
-                if (occl && (best.t != t_before || best.inst != inst_before || best.prim != prim_before || best.tri != tri_before)) {
-                    sp = 0; T.y = 0u; G.y &= 0x00FFFFFFu;    // blocker found: drop the remaining work, the pop below retires the ray
-                }
+#ifdef PT_TRACE_TRI_SHARE
+            if (false) {
 #else
-                test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
+            if (cur_inst != kInvalidId) {
 #endif
+                test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
             } else {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
                 if (T.y) PT_STACK_PUSH(T);
@@ -278,6 +317,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         if (active && T.y == 0u && (G.y & 0xFF000000u) == 0u) {
             for (;;) {
                 if (sp == 0) {
+                    hit_finish(best);
                     io.hit_a[(size_t)slot * io.hit_a_stride] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.inst));
                     io.hit_b[(size_t)slot * io.hit_b_stride] = make_uint2(best.prim, best.tri);
                     active = false;
@@ -305,18 +345,6 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             const uint32_t hits = node_test_fast(sc.nodes, sc.node_bits, node, f, tmin, fminf(tmax, best.t), bias, perm_lut, cb, tb, im);
             G = make_uint2(cb, (hits & 0xFF000000u) | im);
             T = make_uint2(tb, hits & 0x00FFFFFFu);
-#ifdef PT_TRACE_PREFETCH
-            // A/B variant: while this node's triangles are tested, bring in the inner child that will be visited next
-            // (same slot arithmetic as the top of phase 2).  Aimed at the tail of a launch, where a lone ray per warp pays
-            // a full L2 round trip per step.
-            if (T.y != 0u && (G.y & 0xFF000000u) != 0u) {
-                const uint32_t k2 = 31u - (uint32_t)__clz(G.y);
-                const uint32_t s2 = (k2 - 24u) ^ f.rs;
-                const uint32_t nx = G.x + __popc(G.y & 0xffu & ((1u << s2) - 1u));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.nodes + nx));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.node_bits + 2 * (size_t)nx));
-            }
-#endif
         }
     }
 }
