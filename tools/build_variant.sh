@@ -9,7 +9,8 @@ NV="/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c+
 for f in api render bvh_build; do $NV -c $f.cu -o $OBJ/$f.o -Xptxas -v 2> $OBJ/$f.log & done
 wait
 g++ -O2 -std=c++17 -fPIC -ffp-contract=off -c host.cpp -o $OBJ/host.o
+g++ -O2 -std=c++17 -fPIC -ffp-contract=off -I/usr/local/cuda/include $* -c comm.cpp -o $OBJ/comm.o
 g++ -O2 -std=c++17 -fPIC -ffp-contract=off -c scene_load.cpp -o $OBJ/scene_load.o
 g++ -O2 -std=c++17 -fPIC -ffp-contract=off -c image_decode.cpp -o $OBJ/image_decode.o
-/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libb200pt_$NAME.so $OBJ/*.o -lz
+/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libb200pt_$NAME.so $OBJ/*.o -lz -ldl -Xlinker --no-undefined
 grep -E "k_shade|k_trace_persistent" -A3 $OBJ/render.log | grep -E "Used|spill" | sed "s/ptxas info    ://"
