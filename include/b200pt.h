@@ -152,6 +152,12 @@ enum {
                                              it draws no random numbers and only adds atten * (emission | sky), i.e. nothing.
                                              Same image bit for bit, fewer executed queries than the reference's raygen
                                              issues (C2: -5 % rays); off by default so that ray counts stay the reference's */
+    PT_FLAG_HW_BILINEAR = 1u << 11,       /* A/B switch (north_star (c) "CUDA texture objects"): material maps are
+                                             sampled through cudaTextureObject_t (RGBA8 unorm, linear, wrap, LOD 0 — the
+                                             sampler of RayTracingPipeline.zig:54-70 on the texture units) instead of four
+                                             point fetches + fp32 lerp.  The hardware filter uses 1.8 fixed-point weights, so
+                                             radiance is NOT bit-identical to the reference arithmetic: the stated tolerance is
+                                             in tests/test_gpu_parity.py::test_hw_bilinear_...; off by default */
     PT_FLAG_RUSSIAN_ROULETTE = 1u << 8    /* EXTENSION, off by default and outside every parity claim against the reference
                                              (which has none, ray_gen.rgen:49-97): after the throughput update of a bounce
                                              (:95), from the second bounce on, the path survives with probability

@@ -29,7 +29,7 @@ LIB_PATH = os.environ.get("B200PT_LIB") or os.path.join(_HERE, "libb200pt.so")
 
 PT_PARTITION_NONE, PT_PARTITION_TILES = 0, 1
 PT_FLAG_SORT_BY_MATERIAL, PT_FLAG_TRACE_BVH2, PT_FLAG_NO_PRIMARY_REUSE, PT_FLAG_TRACE_WALKER, PT_FLAG_BVH_PLOC, PT_FLAG_NO_TEXTURE_INTERLEAVE = 1, 2, 4, 8, 16, 32
-PT_FLAG_BVH_SAH, PT_FLAG_BVH_OPTIMAL_COLLAPSE, PT_FLAG_RUSSIAN_ROULETTE, PT_FLAG_BVH_LBVH, PT_FLAG_SKIP_DEAD_SEGMENTS = 64, 128, 256, 512, 1024
+PT_FLAG_BVH_SAH, PT_FLAG_BVH_OPTIMAL_COLLAPSE, PT_FLAG_RUSSIAN_ROULETTE, PT_FLAG_BVH_LBVH, PT_FLAG_SKIP_DEAD_SEGMENTS, PT_FLAG_HW_BILINEAR = 64, 128, 256, 512, 1024, 2048
 
 PtHit_dtype = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("instance", "<u4"), ("primitive_index", "<u4"),
                         ("triangle_index", "<u4")])

@@ -201,6 +201,32 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
         }
     }
     PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    if (r->cfg.flags & PT_FLAG_HW_BILINEAR) {
+        // the reference's sampler on the texture units: r8g8b8a8_unorm, linear mag/min, REPEAT, one mip (RayTracingPipeline.zig:54-70)
+        r->tex_arrays.assign(s->num_textures, nullptr);
+        r->tex_objects.assign(s->num_textures, 0);
+        for (size_t i = 0; i < s->num_textures; ++i) {
+            const PtTexture& t = s->textures[i];
+            const cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+            PT_CUDA_CHECK(cudaMallocArray(&r->tex_arrays[i], &fmt, t.width, t.height));
+            PT_CUDA_CHECK(cudaMemcpy2DToArrayAsync(r->tex_arrays[i], 0, 0, t.rgba, (size_t)t.width * 4, (size_t)t.width * 4, t.height, cudaMemcpyHostToDevice, r->stream));
+            cudaResourceDesc rd; std::memset(&rd, 0, sizeof(rd));
+            rd.resType = cudaResourceTypeArray; rd.res.array.array = r->tex_arrays[i];
+            cudaTextureDesc td; std::memset(&td, 0, sizeof(td));
+            td.addressMode[0] = td.addressMode[1] = cudaAddressModeWrap;
+            td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeNormalizedFloat; td.normalizedCoords = 1;
+            PT_CUDA_CHECK(cudaCreateTextureObject(&r->tex_objects[i], &rd, &td, nullptr));
+        }
+        std::vector<unsigned long long> objs(4 * std::max<size_t>(s->num_materials, 1), 0ull);
+        for (size_t i = 0; i < s->num_materials; ++i) {
+            const PtMaterial& m = s->materials[i];
+            const uint32_t t[4] = {m.albedo_texture_index, m.metal_roughness_texture_index, m.emissive_texture_index, m.normal_texture_index};
+            for (int k = 0; k < 4; ++k) objs[4 * i + k] = t[k] == PT_INVALID_TEXTURE ? 0ull : (unsigned long long)r->tex_objects[t[k]];
+        }
+        if ((rc = dev_alloc(&r->d_mat_tex_objs, objs.size())) != PT_OK) return rc;
+        PT_CUDA_CHECK(cudaMemcpyAsync(r->d_mat_tex_objs, objs.data(), objs.size() * 8, cudaMemcpyHostToDevice, r->stream));
+        PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    }
     if ((rc = dev_alloc(&r->d_materials, mats.size())) != PT_OK) return rc;
     if (!mats.empty()) PT_CUDA_CHECK(cudaMemcpyAsync(r->d_materials, mats.data(), mats.size() * sizeof(MatRec), cudaMemcpyHostToDevice, r->stream));
     // meshes / instances
@@ -228,6 +254,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.node_bits = r->bvh.node_bits8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
     sc.nodes2 = r->bvh.nodes2; sc.tris2 = r->bvh.tris2; sc.tlas2 = r->bvh.tlas2; sc.tlas_root = r->bvh.tlas_root8;
     PT_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&sc.error_flag), r->h_error, 0));
+    sc.mat_tex_objs = r->d_mat_tex_objs;
     sc.num_instances = (uint32_t)inst.size(); sc.num_prims = (uint32_t)prims.size();
     sc.num_materials = (uint32_t)s->num_materials; sc.num_textures = (uint32_t)s->num_textures;
     return PT_OK;
@@ -242,6 +269,9 @@ void destroy_impl(PtRenderer* r) {
     if (r->owns_scene) {
         for (auto p : r->d_texels) cudaFree(p);
         for (auto p : r->d_atlases) cudaFree(p);
+        for (auto t : r->tex_objects) if (t) cudaDestroyTextureObject(t);
+        for (auto a : r->tex_arrays) if (a) cudaFreeArray(a);
+        cudaFree(r->d_mat_tex_objs);
         cudaFree(r->d_blob); cudaFree(r->d_prims); cudaFree(r->d_materials); cudaFree(r->d_textures);
         cudaFree(r->d_instances_raw); cudaFree(r->d_instances);
         r->bvh.release();

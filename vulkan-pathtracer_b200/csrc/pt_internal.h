@@ -113,6 +113,8 @@ struct DeviceScene {
     // set to 1 by a walker that had to drop a stack push (hierarchy deeper than the fixed traversal stack): host-mapped, so
     // pt_sync / pt_get_stats can report PT_ERR_TRAVERSAL_STACK instead of returning an image with missed hits
     uint32_t* error_flag;
+    // PT_FLAG_HW_BILINEAR: 4 texture objects per material (albedo, metal-roughness, emissive, normal; 0 = absent), else null
+    const unsigned long long* mat_tex_objs;
 };
 
 // Hit record in HBM: 32 bytes (2 x 16 B)

@@ -102,7 +102,6 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace(DeviceScene sc, PathBuf
             if (MODE == TRACE_BVH2) trace_bvh2(sc, tlas2_count, tlas2_leaf_instance, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h);
             else if (MODE == TRACE_BVH8_COUNT) trace_bvh8<true>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, &cnt_nodes, &cnt_tris);
             else trace_bvh8<false>(sc, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), ro.w, rd.w, h, nullptr, nullptr);
-            hit_finish(h);
             pb.hit_a[slot] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.inst));
             pb.hit_b[slot] = make_uint2(h.prim, h.tri);
         }
@@ -129,7 +128,6 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_rays(DeviceScene sc, co
             Hit h;
             if (MODE == TRACE_BVH2) trace_bvh2(sc, tlas2_count, tlas2_leaf_instance, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax, h);
             else trace_bvh8<false>(sc, v3(r.ox, r.oy, r.oz), v3(r.dx, r.dy, r.dz), r.tmin, r.tmax, h, nullptr, nullptr);
-            hit_finish(h);
             HitRec o;
             o.t = h.t; o.b1 = h.b1; o.b2 = h.b2; o.instance = h.inst; o.primitive_index = h.prim; o.triangle_index = h.tri;
             o._pad0 = 0; o._pad1 = 0;

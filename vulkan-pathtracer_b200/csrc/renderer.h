@@ -28,6 +28,10 @@ struct PtRenderer {
     pt::TexRec* d_textures = nullptr;
     std::vector<uint32_t*> d_texels;
     std::vector<uint4*> d_atlases;   // interleaved material textures (MatRec::atlas)
+    // PT_FLAG_HW_BILINEAR: one CUDA array + texture object per glTF texture, and the per-material table of objects
+    std::vector<cudaArray_t> tex_arrays;
+    std::vector<cudaTextureObject_t> tex_objects;
+    unsigned long long* d_mat_tex_objs = nullptr;
     PtInstance* d_instances_raw = nullptr;
     pt::InstanceRec* d_instances = nullptr;
     std::vector<PtInstance> h_instances;   // host copy (animated instances: pt_set_instance_transforms)

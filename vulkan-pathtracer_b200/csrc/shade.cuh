@@ -310,6 +310,34 @@ struct MaterialData { V4 albedo; V3 normal, emissive; float roughness, metallic;
 PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& td, const float* lut = nullptr) {
     const MatRec* mp = sc.materials + td.material_index;
     const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));     // factors + presence bits
+    if (sc.mat_tex_objs) {
+        MaterialData md;
+        // PT_FLAG_HW_BILINEAR (A/B): the same material.glsl statements with texture() on the texture units (1.8 fixed-point
+        // filter weights: not bit-identical to the fp32 lerp below)
+        const ulonglong2 o01 = __ldg(reinterpret_cast<const ulonglong2*>(sc.mat_tex_objs + 4u * td.material_index));
+        const ulonglong2 o23 = __ldg(reinterpret_cast<const ulonglong2*>(sc.mat_tex_objs + 4u * td.material_index) + 1);
+        float4 ta = make_float4(1.0f, 1.0f, 1.0f, 1.0f), tm = ta, te = ta, tn = ta;
+        if (o01.x) ta = tex2D<float4>((cudaTextureObject_t)o01.x, td.uv.x, td.uv.y);
+        if (o01.y) tm = tex2D<float4>((cudaTextureObject_t)o01.y, td.uv.x, td.uv.y);
+        if (o23.x) te = tex2D<float4>((cudaTextureObject_t)o23.x, td.uv.x, td.uv.y);
+        if (o23.y) tn = tex2D<float4>((cudaTextureObject_t)o23.y, td.uv.x, td.uv.y);
+        md.albedo = unpack_unorm4x8(fac.x, lut);
+        if (o01.x) { md.albedo.x *= ta.x; md.albedo.y *= ta.y; md.albedo.z *= ta.z; md.albedo.w *= ta.w; }
+        const V4 mr = unpack_unorm4x8(fac.y, lut);
+        md.roughness = mr.y; md.metallic = mr.z;
+        if (o01.y) { md.roughness *= tm.y; md.metallic *= tm.z; }
+        const V4 e = unpack_unorm4x8(fac.z, lut);
+        md.emissive = v3(e.x, e.y, e.z);
+        if (o23.x) md.emissive = md.emissive * v3(te.x, te.y, te.z);
+        md.normal = td.normal;
+        if (o23.y) {
+            const V3 T = v3(td.tangent.x, td.tangent.y, td.tangent.z);
+            const V3 bitangent = cross(td.normal, T) * td.tangent.w;
+            const V3 n = normalize(2.0f * v3(tn.x, tn.y, tn.z) - v3s(1.0f));
+            md.normal = T * n.x + bitangent * n.y + td.normal * n.z;
+        }
+        return md;
+    }
     const uint4 aw = __ldg(reinterpret_cast<const uint4*>(mp) + 5);  // interleaved texels, if any
     const uint4* atlas = reinterpret_cast<const uint4*>(((uint64_t)aw.y << 32) | aw.x);
     TexRec tex[4];
@@ -394,6 +422,11 @@ PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h, const float* lut = 
         V2 uv;
         uv.x = u0 * c.x + u1 * c.y + u2 * c.z;
         uv.y = v0 * c.x + v1 * c.y + v2 * c.z;
+        if (sc.mat_tex_objs) {      // PT_FLAG_HW_BILINEAR
+            const unsigned long long o = __ldg(sc.mat_tex_objs + 4u * (p.info & PT_MATERIAL_INDEX_MASK) + 2u);
+            const float4 te = tex2D<float4>((cudaTextureObject_t)o, uv.x, uv.y);
+            return emissive * v3(te.x, te.y, te.z);
+        }
         const uint4 w = __ldg(reinterpret_cast<const uint4*>(mp) + 3);                   // TexRec of the emissive map
         TexRec tex;
         tex.texels = reinterpret_cast<const uint32_t*>(((uint64_t)w.y << 32) | w.x);

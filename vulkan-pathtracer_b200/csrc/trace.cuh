@@ -38,9 +38,8 @@ PT_D RayPre ray_precompute(V3 d) {
 }
 
 // hit distance + the unnormalised barycentrics (b1 = V / det, b2 = W / det)
-// tbest: the closest hit distance so far (kMissT when none); only used to skip work whose outcome is already known.
 PT_D bool intersect_tri_raw(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2, float tmin, float tmax, float& t_out,
-                            float& V_out, float& W_out, float& det_out, float tbest = kMissT) {
+                            float& V_out, float& W_out, float& det_out) {
     const V3 A = v3(p0.x, p0.y, p0.z) - o, B = v3(p1.x, p1.y, p1.z) - o, C = v3(p2.x, p2.y, p2.z) - o;
     const float Ax = (rp.m0x * A.x + rp.m0y * A.y) + rp.m0z * A.z, Ay = (rp.m1x * A.x + rp.m1y * A.y) + rp.m1z * A.z;
     const float Bx = (rp.m0x * B.x + rp.m0y * B.y) + rp.m0z * B.z, By = (rp.m1x * B.x + rp.m1y * B.y) + rp.m1z * B.z;
@@ -60,14 +59,6 @@ PT_D bool intersect_tri_raw(V3 o, const RayPre& rp, float4 p0, float4 p1, float4
     const float Akz = comp(A, rp.kz), Bkz = comp(B, rp.kz), Ckz = comp(C, rp.kz);
     const float Az = rp.Sz * Akz, Bz = rp.Sz * Bkz, Cz = rp.Sz * Ckz;
     const float T = U * Az + V * Bz + W * Cz;
-#ifdef PT_TRACE_EARLY_REJECT
-    // A/B variant: two division-free rejects with a known outcome (det > 0 here).  T <= 0: the plane is hit at t <= 0 <= tmin,
-    // the range test below fails.  T > min(tmax, tbest) * det * (1 + 2^-20): the rounded quotient surely exceeds min(tmax,
-    // tbest), so either the range test fails or hit_better() is false — no state changes either way.  Most candidates that
-    // reach this point lie behind the origin (bounce rays start on a surface) or behind the closest hit.
-    if (tmin >= 0.0f && T <= 0.0f) return false;
-    if (T > (fminf(tmax, tbest) * det) * 1.00000095367431640625f) return false;
-#endif
     const float t = T / det;
     if (!(t > tmin && t < tmax)) return false;
     t_out = t; V_out = V; W_out = W; det_out = det;
@@ -82,21 +73,9 @@ PT_D bool intersect_tri(V3 o, const RayPre& rp, float4 p0, float4 p1, float4 p2,
     return true;
 }
 
-#ifdef PT_TRACE_FINAL_BARY
-// A/B variant: the closest hit keeps the unnormalised barycentrics (V, W in b1, b2) and the determinant; the two IEEE
-// divisions b1 = V / det, b2 = W / det are done once, when the ray's result is stored (same operands, same bits)
-struct Hit { float t, b1, b2, det; uint32_t inst, prim, tri; };
-#else
 struct Hit { float t, b1, b2; uint32_t inst, prim, tri; };
-#endif
 
-#ifdef PT_TRACE_FINAL_BARY
-PT_D void hit_init(Hit& h) { h.t = kMissT; h.b1 = 0.0f; h.b2 = 0.0f; h.det = 1.0f; h.inst = h.prim = h.tri = kInvalidId; }
-PT_D void hit_finish(Hit& h) { h.b1 = h.b1 / h.det; h.b2 = h.b2 / h.det; }
-#else
 PT_D void hit_init(Hit& h) { h.t = kMissT; h.b1 = 0.0f; h.b2 = 0.0f; h.inst = h.prim = h.tri = kInvalidId; }
-PT_D void hit_finish(Hit&) {}
-#endif
 
 PT_D bool hit_better(float t, uint32_t inst, uint32_t prim, uint32_t tri, const Hit& h) {
     if (t < h.t) return true;
@@ -111,21 +90,13 @@ PT_D void test_triangle(const Bvh8Tri* __restrict__ tris, uint32_t idx, V3 o, co
     const float4* q = reinterpret_cast<const float4*>(tris + idx);
     const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
     // tmax stays the ray's tmax: candidates with t == best.t must reach the tie-break
-#ifdef PT_TRACE_FINAL_BARY
-    float t, V, W, det;
-    if (intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t, V, W, det, best.t)) {
-        const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
-        if (hit_better(t, inst, prim, tri, best)) { best.t = t; best.b1 = V; best.b2 = W; best.det = det; best.inst = inst; best.prim = prim; best.tri = tri; }
-    }
-#else
     // the two barycentric divisions only for candidates that replace the closest hit (same operands, same bits; measured
     // C2 1.334 -> 1.312 ms, C4 14.98 -> 14.83 ms, profiles/r2a_variants.txt)
     float t, V, W, det;
-    if (intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t, V, W, det, best.t)) {
+    if (intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t, V, W, det)) {
         const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
         if (hit_better(t, inst, prim, tri, best)) { best.t = t; best.b1 = V / det; best.b2 = W / det; best.inst = inst; best.prim = prim; best.tri = tri; }
     }
-#endif
 }
 
 // ------------------------------------------------------------------ ray frame for box tests

@@ -150,11 +150,6 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     const uint32_t bias = io.bias_word;
     // octant permutation of the inner-child hit byte: lut[rs * 256 + mask]
     __shared__ uint8_t perm_lut[8 * 256];
-#ifdef PT_TRACE_TRI_SHARE
-    __shared__ uint2 s_item[kTraceBlock / 32][32];       // (owner lane, triangle index) of the warp's pending pairs
-    __shared__ float4 s_res[kTraceBlock / 32][32];       // candidate of pair k: t (kMissT: none), b1, b2, primitive (bits)
-    __shared__ uint32_t s_res_tri[kTraceBlock / 32][32];
-#endif
     for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) perm_lut[i] = (uint8_t)perm8(i & 255u, i >> 8);
     __syncthreads();
     // warp-uniform chunk of the queue: 32 rays per global atomic.  Larger chunks save atomics but leave the last
@@ -224,74 +219,11 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         // ---- phase 1: one leaf item.  (Postponing triangle groups while few lanes hold one — Ylitie et
         // al. 2017 — and repeating the phase while many do were both measured: neither pays here, and the
         // warp votes they need cost 3-4 % each; profiles/r1_experiments.md.)
-#ifdef PT_TRACE_TRI_SHARE
-        // A/B variant: warp-cooperative triangle phase (north_star (b): "warp-level ballot/shuffle work redistribution").
-        // The pending (ray, triangle) pairs of the whole warp — lanes inside a BLAS — are numbered by a warp scan, published
-        // in shared memory and tested one pair per lane, 32 at a time: the worker fetches the owner's ray with shuffles,
-        // runs the same intersect_tri and hands the candidate back through shared memory, where the owner merges it with
-        // hit_better (a total order, so the result does not depend on who tested what).  Lanes at the top level keep the
-        // one-instance-per-iteration path below.
-        {
-            const bool in_blas = active && cur_inst != kInvalidId;
-            const uint32_t cnt = in_blas ? (uint32_t)__popc(T.y) : 0u;
-            uint32_t incl = cnt;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if ((int)lane >= o) incl += v; }
-            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-            if (total != 0u) {      // warp-uniform
-                const uint32_t wid = threadIdx.x >> 5;
-                const uint32_t excl = incl - cnt;
-                uint32_t m = T.y, published = 0u;
-                if (in_blas) {
-                    for (uint32_t j = excl; m != 0u && j < 32u; ++j) {
-                        const uint32_t b = (uint32_t)__ffs((int)m) - 1u;
-                        m &= m - 1u;
-                        s_item[wid][j] = make_uint2(lane, T.x + b);
-                        ++published;
-                    }
-                    T.y = m;        // pairs beyond the warp's first 32 wait for the next iteration
-                }
-                __syncwarp();
-                const uint32_t n_items = min(total, 32u);
-                const uint2 it = lane < n_items ? s_item[wid][lane] : make_uint2(lane, 0u);
-                const int src = (int)it.x;
-                const V3 so = v3(__shfl_sync(0xffffffffu, f.o.x, src), __shfl_sync(0xffffffffu, f.o.y, src), __shfl_sync(0xffffffffu, f.o.z, src));
-                RayPre srp;
-                srp.m0x = __shfl_sync(0xffffffffu, rp.m0x, src); srp.m0y = __shfl_sync(0xffffffffu, rp.m0y, src); srp.m0z = __shfl_sync(0xffffffffu, rp.m0z, src);
-                srp.m1x = __shfl_sync(0xffffffffu, rp.m1x, src); srp.m1y = __shfl_sync(0xffffffffu, rp.m1y, src); srp.m1z = __shfl_sync(0xffffffffu, rp.m1z, src);
-                srp.Sz = __shfl_sync(0xffffffffu, rp.Sz, src); srp.kz = __shfl_sync(0xffffffffu, rp.kz, src);
-                const float stmin = __shfl_sync(0xffffffffu, tmin, src), stmax = __shfl_sync(0xffffffffu, tmax, src);
-                if (lane < n_items) {
-                    const float4* q = reinterpret_cast<const float4*>(sc.tris + it.y);
-                    const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
-                    float t = kMissT, b1 = 0.0f, b2 = 0.0f;
-                    if (!intersect_tri(so, srp, p0, p1, p2, stmin, stmax, t, b1, b2)) t = kMissT;
-                    s_res[wid][lane] = make_float4(t, b1, b2, p0.w);
-                    s_res_tri[wid][lane] = __float_as_uint(p1.w);
-                }
-                __syncwarp();
-                for (uint32_t j = excl; j < excl + published; ++j) {
-                    const float4 c = s_res[wid][j];
-                    if (c.x != kMissT) {
-                        const uint32_t prim = __float_as_uint(c.w), tri = s_res_tri[wid][j];
-                        if (hit_better(c.x, cur_inst, prim, tri, best)) { best.t = c.x; best.b1 = c.y; best.b2 = c.z; best.inst = cur_inst; best.prim = prim; best.tri = tri; }
-                    }
-                }
-                __syncwarp();       // the arrays are rewritten in the next iteration
-            }
-        }
-        const bool has_t = active && T.y != 0u && cur_inst == kInvalidId;
-#else
         const bool has_t = active && T.y != 0u;
-#endif
         if (has_t) {
             const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
             T.y &= T.y - 1u;
-#ifdef PT_TRACE_TRI_SHARE
-            if (false) {
-#else
             if (cur_inst != kInvalidId) {
-#endif
                 test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
             } else {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
@@ -317,7 +249,6 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         if (active && T.y == 0u && (G.y & 0xFF000000u) == 0u) {
             for (;;) {
                 if (sp == 0) {
-                    hit_finish(best);
                     io.hit_a[(size_t)slot * io.hit_a_stride] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.inst));
                     io.hit_b[(size_t)slot * io.hit_b_stride] = make_uint2(best.prim, best.tri);
                     active = false;
