@@ -509,6 +509,7 @@ int pt_sync(PtRenderer* r) {
 
 int pt_resize(PtRenderer* r, uint32_t width, uint32_t height) {
     PT_REQUIRE(r && width > 0 && height > 0, "pt_resize: invalid argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     // Like the reference, the storage image is re-created at the full new extent: the divider is
     // dropped (RaytracingPass.zig:684-697, quirk Q13).
@@ -531,6 +532,7 @@ int pt_device_image(PtRenderer* r, float** device_ptr) {
 
 int pt_read_rgba32f_async(PtRenderer* r, float* dst, void* cuda_stream) {
     PT_REQUIRE(r && dst, "pt_read_rgba32f_async: null argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     cudaStream_t st = follow_stream(r, cuda_stream);
     PT_CUDA_CHECK(cudaMemcpyAsync(dst, r->d_image, (size_t)r->pm.width * r->pm.height * 16, cudaMemcpyDeviceToHost, st));
     return PT_OK;
@@ -567,6 +569,7 @@ int pt_read_rgba32f(PtRenderer* r, float* host_dst) {
 
 int pt_read_bgra8_async(PtRenderer* r, uint8_t* dst, void* cuda_stream) {
     PT_REQUIRE(r && dst, "pt_read_bgra8_async: null argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     cudaStream_t st = follow_stream(r, cuda_stream);
     const size_t px = (size_t)r->pm.width * r->pm.height;
     if (!r->d_bgra) { int rc = dev_alloc(&r->d_bgra, px * 4); if (rc != PT_OK) return rc; }
@@ -583,6 +586,7 @@ int pt_read_bgra8(PtRenderer* r, uint8_t* host_dst) {
 
 int pt_read_ids(PtRenderer* r, uint32_t* instance, uint32_t* primitive, uint32_t* triangle) {
     PT_REQUIRE(r, "pt_read_ids: null renderer");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     const size_t px = (size_t)r->pm.width * r->pm.height;
     { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     if (instance) PT_CUDA_CHECK(cudaMemcpy(instance, r->d_ids, px * 4, cudaMemcpyDeviceToHost));
@@ -593,6 +597,7 @@ int pt_read_ids(PtRenderer* r, uint32_t* instance, uint32_t* primitive, uint32_t
 
 int pt_read_rgba32f_upscaled(PtRenderer* r, float* host_dst) {
     PT_REQUIRE(r && host_dst, "pt_read_rgba32f_upscaled: null argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     if (r->pm.width == r->full_w && r->pm.height == r->full_h) return pt_read_rgba32f(r, host_dst);
     const size_t px = (size_t)r->full_w * r->full_h;
     if (!r->d_upscaled) { int rc = dev_alloc(&r->d_upscaled, px * 4); if (rc != PT_OK) return rc; }
@@ -610,6 +615,7 @@ int pt_set_accumulate(PtRenderer* r, int enabled) {
 
 int pt_reset_accum(PtRenderer* r) {
     PT_REQUIRE(r, "pt_reset_accum: null renderer");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     if (r->d_accum) PT_CUDA_CHECK(cudaMemsetAsync(r->d_accum, 0, (size_t)r->pm.width * r->pm.height * 16, follow_stream(r, nullptr)));
     r->accum_frames = 0;
     return PT_OK;
@@ -617,6 +623,7 @@ int pt_reset_accum(PtRenderer* r) {
 
 int pt_device_accum(PtRenderer* r, float** device_ptr, uint32_t* frames) {
     PT_REQUIRE(r && device_ptr, "pt_device_accum: null argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     if (!r->d_accum) {
         const size_t px = (size_t)r->pm.width * r->pm.height;
         int rc = dev_alloc(&r->d_accum, px * 4);
@@ -630,6 +637,7 @@ int pt_device_accum(PtRenderer* r, float** device_ptr, uint32_t* frames) {
 
 int pt_read_accum_mean(PtRenderer* r, float* host_dst, uint32_t total_frames) {
     PT_REQUIRE(r && host_dst && r->d_accum, "pt_read_accum_mean: accumulation is not enabled");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     const size_t px = (size_t)r->pm.width * r->pm.height;
     const uint32_t frames = total_frames ? total_frames : r->accum_frames;
     PT_REQUIRE(frames > 0, "pt_read_accum_mean: no frames accumulated");
@@ -672,6 +680,7 @@ int pt_set_profiling(PtRenderer* r, int enabled) {
 
 int pt_get_stats(PtRenderer* r, PtStats* out) {
     PT_REQUIRE(r && out, "pt_get_stats: null argument");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     std::memset(out, 0, sizeof(*out));
     { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     std::vector<uint32_t> q((size_t)r->max_iters + 2, 0);
@@ -732,6 +741,7 @@ int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
 
 int pt_count_traversal(PtRenderer* r, uint64_t* nodes, uint64_t* tris, uint64_t* rays) {
     PT_REQUIRE(r && r->have_last_cam, "pt_count_traversal: call pt_render first");
+    PT_CUDA_CHECK(cudaSetDevice(r->device));
     { int rc = pt_sync(r); if (rc != PT_OK) return rc; }
     PT_CUDA_CHECK(cudaMemsetAsync(r->pb.trav_counters, 0, 16, r->stream));
     const bool prof = r->profiling, acc = r->accumulate;

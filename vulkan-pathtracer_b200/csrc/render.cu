@@ -224,7 +224,8 @@ __global__ void __launch_bounds__(256) k_matsort_scatter(DeviceScene sc, PathBuf
 #else
 #define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, kMulti ? 4 : 6)
 #endif
-template <bool kMulti>
+// kHwTex: PT_FLAG_HW_BILINEAR (material maps through texture objects); its own instantiations, so the default kernels carry none of it
+template <bool kMulti, bool kHwTex = false>
 __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers pb, FrameParams fp, uint32_t iter) {
     const uint32_t n = pb.qcount[iter];
     const uint32_t* __restrict__ qin = (fp.flags & PT_FLAG_SORT_BY_MATERIAL) ? pb.queue_sorted : pb.queue[iter & 1u];
@@ -302,10 +303,10 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                     if (t_hit != kMissT) {
                         if (j + 1u >= B && !keep_primary) {
                             // last segment: loop bound reached (:49,:77); only the emission of this hit is consumed (:75)
-                            sf_emissive = get_emissive(sc, h, s_unorm);
+                            sf_emissive = get_emissive<kHwTex>(sc, h, s_unorm);
                         } else {
                             const TriangleData td = get_triangle_data(sc, h);                   // :72
-                            const MaterialData md = get_material_data(sc, td, s_unorm);         // :73
+                            const MaterialData md = get_material_data<kHwTex>(sc, td, s_unorm);         // :73
                             sf_normal = md.normal; sf_roughness = md.roughness;
                             sf_albedo = v3(md.albedo.x, md.albedo.y, md.albedo.z); sf_metallic = md.metallic;
                             sf_emissive = md.emissive; sf_gn = td.geometry_normal;
@@ -528,6 +529,11 @@ void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t
 
 void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
                   const LaunchDims& dims, cudaStream_t st) {
+    if (sc.mat_tex_objs) {      // PT_FLAG_HW_BILINEAR
+        if (fp.num_samples > 1u) k_shade<true, true><<<dims.shade_multi, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+        else k_shade<false, true><<<dims.shade_single, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+        return;
+    }
     if (fp.num_samples > 1u) k_shade<true><<<dims.shade_multi, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
     else k_shade<false><<<dims.shade_single, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
 }

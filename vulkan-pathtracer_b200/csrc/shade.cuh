@@ -307,10 +307,11 @@ PT_D V4 sample_texture(const TexRec& tex, V2 uv, const float* lut = nullptr) { r
 struct MaterialData { V4 albedo; V3 normal, emissive; float roughness, metallic; };
 
 // material.glsl:31-69
+template <bool kHwTex = false>
 PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& td, const float* lut = nullptr) {
     const MatRec* mp = sc.materials + td.material_index;
     const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));     // factors + presence bits
-    if (sc.mat_tex_objs) {
+    if (kHwTex) {
         MaterialData md;
         // PT_FLAG_HW_BILINEAR (A/B): the same material.glsl statements with texture() on the texture units (1.8 fixed-point
         // filter weights: not bit-identical to the fp32 lerp below)
@@ -405,6 +406,7 @@ PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& t
 // of getTriangleData / getMaterialData nothing but `emissive` is consumed, so only the emissive factor and --
 // when the material has an emissive map -- the interpolated uv and that map's four texels are fetched.
 // Same expressions as above for everything that is computed, hence the same bits.
+template <bool kHwTex = false>
 PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h, const float* lut = nullptr) {
     const PrimRec p = sc.prims[h.primitive_index];
     const MatRec* mp = sc.materials + (p.info & PT_MATERIAL_INDEX_MASK);
@@ -422,7 +424,7 @@ PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h, const float* lut = 
         V2 uv;
         uv.x = u0 * c.x + u1 * c.y + u2 * c.z;
         uv.y = v0 * c.x + v1 * c.y + v2 * c.z;
-        if (sc.mat_tex_objs) {      // PT_FLAG_HW_BILINEAR
+        if (kHwTex) {      // PT_FLAG_HW_BILINEAR
             const unsigned long long o = __ldg(sc.mat_tex_objs + 4u * (p.info & PT_MATERIAL_INDEX_MASK) + 2u);
             const float4 te = tex2D<float4>((cudaTextureObject_t)o, uv.x, uv.y);
             return emissive * v3(te.x, te.y, te.z);
