@@ -29,7 +29,7 @@ def main():
             r.deinit()
         b200pt.set_option("chunk", 32)
     elif what == "one":
-        r = b200pt.Renderer(ps, W, H, spp, seg)
+        r = b200pt.Renderer(ps, W, H, spp, seg, flags=int(os.environ.get("SWEEP_FLAGS", "0")))
         tr, sh, ot, rays = measure(r, W, H)
         st = r.stats()
         nn, nt, nr = r.count_traversal()

@@ -201,6 +201,11 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
         }
     }
     PT_CUDA_CHECK(cudaStreamSynchronize(r->stream));
+    r->scene.atlas_only = 1u;
+    for (const MatRec& m : mats) if (m.present != 0u && !m.atlas) r->scene.atlas_only = 0u;
+#ifdef PT_SHADE_NO_ATLAS_ONLY
+    r->scene.atlas_only = 0u;       // A/B variant: always the general K-shade instantiation
+#endif
     if (r->cfg.flags & PT_FLAG_HW_BILINEAR) {
         // the reference's sampler on the texture units: r8g8b8a8_unorm, linear mag/min, REPEAT, one mip (RayTracingPipeline.zig:54-70)
         r->tex_arrays.assign(s->num_textures, nullptr);

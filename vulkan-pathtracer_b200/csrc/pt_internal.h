@@ -115,6 +115,7 @@ struct DeviceScene {
     uint32_t* error_flag;
     // PT_FLAG_HW_BILINEAR: 4 texture objects per material (albedo, metal-roughness, emissive, normal; 0 = absent), else null
     const unsigned long long* mat_tex_objs;
+    uint32_t atlas_only;         // 1 when every material that has maps has them interleaved (MatRec::atlas): K-shade's atlas-only instantiation
 };
 
 // Hit record in HBM: 32 bytes (2 x 16 B)

@@ -222,10 +222,14 @@ __global__ void __launch_bounds__(256) k_matsort_scatter(DeviceScene sc, PathBuf
 #ifdef PT_SHADE_MIN_BLOCKS
 #define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, PT_SHADE_MIN_BLOCKS)
 #else
-#define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, kMulti ? 4 : 6)
+#ifndef PT_SHADE_MULTI_MIN_BLOCKS
+#define PT_SHADE_MULTI_MIN_BLOCKS 4
 #endif
-// kHwTex: PT_FLAG_HW_BILINEAR (material maps through texture objects); its own instantiations, so the default kernels carry none of it
-template <bool kMulti, bool kHwTex = false>
+#define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, kMulti ? PT_SHADE_MULTI_MIN_BLOCKS : 6)
+#endif
+// kTex (shade.cuh): how material maps are fetched — 0 general, 1 texture objects (PT_FLAG_HW_BILINEAR), 2 atlas-only scene.  K-shade is
+// instruction-cache-bound on multi-sample workloads, so each mode is its own instantiation and carries only its own fetch code.
+template <bool kMulti, int kTex = 0>
 __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers pb, FrameParams fp, uint32_t iter) {
     const uint32_t n = pb.qcount[iter];
     const uint32_t* __restrict__ qin = (fp.flags & PT_FLAG_SORT_BY_MATERIAL) ? pb.queue_sorted : pb.queue[iter & 1u];
@@ -303,10 +307,10 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                     if (t_hit != kMissT) {
                         if (j + 1u >= B && !keep_primary) {
                             // last segment: loop bound reached (:49,:77); only the emission of this hit is consumed (:75)
-                            sf_emissive = get_emissive<kHwTex>(sc, h, s_unorm);
+                            sf_emissive = get_emissive<kTex>(sc, h, s_unorm);
                         } else {
                             const TriangleData td = get_triangle_data(sc, h);                   // :72
-                            const MaterialData md = get_material_data<kHwTex>(sc, td, s_unorm);         // :73
+                            const MaterialData md = get_material_data<kTex>(sc, td, s_unorm);         // :73
                             sf_normal = md.normal; sf_roughness = md.roughness;
                             sf_albedo = v3(md.albedo.x, md.albedo.y, md.albedo.z); sf_metallic = md.metallic;
                             sf_emissive = md.emissive; sf_gn = td.geometry_normal;
@@ -492,9 +496,11 @@ LaunchDims compute_launch_dims(int num_sms) {
     d.trace_walker = persistent_blocks(k_trace<TRACE_BVH8>, kTraceThreads, num_sms);
     d.trace_bvh2 = persistent_blocks(k_trace<TRACE_BVH2>, kTraceThreads, num_sms);
     d.trace_count = persistent_blocks(k_trace<TRACE_BVH8_COUNT>, kTraceThreads, num_sms);
-    d.trace_persistent = persistent_blocks(k_trace_persistent, kTraceBlock, num_sms);
-    d.shade_single = persistent_blocks(k_shade<false>, kShadeThreads, num_sms);
-    d.shade_multi = persistent_blocks(k_shade<true>, kShadeThreads, num_sms);
+    d.trace_persistent = persistent_blocks(k_trace_persistent<false>, kTraceBlock, num_sms);
+    d.trace_flat = persistent_blocks(k_trace_persistent<true>, kTraceBlock, num_sms);
+    // the launch bounds fix the residency (6 / 4 CTAs per SM) for every fetch mode
+    d.shade_single = persistent_blocks(k_shade<false, 0>, kShadeThreads, num_sms);
+    d.shade_multi = persistent_blocks(k_shade<true, 0>, kShadeThreads, num_sms);
     d.chunk = g_default_chunk;
     return d;
 }
@@ -511,7 +517,8 @@ void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, T
         io.queue = pb.queue[iter & 1u]; io.count_ptr = pb.qcount + iter; io.count = 0; io.cursor = pb.trace_next + iter;
         io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.ray_e = pb.ray_e; io.ray_s = pb.ray_s; io.ray_m = pb.ray_m; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
         io.hit_a_stride = 1; io.hit_b_stride = 1; io.bias_word = 0x4B000000u; io.chunk = dims.chunk;
-        k_trace_persistent<<<dims.trace_persistent, kTraceBlock, 0, st>>>(sc, io);
+        if (sc.start_inst != kInvalidId) k_trace_persistent<true><<<dims.trace_flat, kTraceBlock, 0, st>>>(sc, io);
+        else k_trace_persistent<false><<<dims.trace_persistent, kTraceBlock, 0, st>>>(sc, io);
         return;
     }
     if (mode == TRACE_BVH2) k_trace<TRACE_BVH2><<<dims.trace_bvh2, kTraceThreads, 0, st>>>(sc, pb, iter, tlas2_count, tlas2_leaf_instance);
@@ -529,13 +536,17 @@ void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t
 
 void launch_shade(const DeviceScene& sc, const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, uint32_t iter,
                   const LaunchDims& dims, cudaStream_t st) {
-    if (sc.mat_tex_objs) {      // PT_FLAG_HW_BILINEAR
-        if (fp.num_samples > 1u) k_shade<true, true><<<dims.shade_multi, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
-        else k_shade<false, true><<<dims.shade_single, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
-        return;
+    const int mode = sc.mat_tex_objs ? 1 : (sc.atlas_only ? 2 : 0);
+    const int blocks = fp.num_samples > 1u ? dims.shade_multi : dims.shade_single;
+    if (fp.num_samples > 1u) {
+        if (mode == 1) k_shade<true, 1><<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+        else if (mode == 2) k_shade<true, 2><<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+        else k_shade<true, 0><<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+    } else {
+        if (mode == 1) k_shade<false, 1><<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+        else if (mode == 2) k_shade<false, 2><<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
+        else k_shade<false, 0><<<blocks, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
     }
-    if (fp.num_samples > 1u) k_shade<true><<<dims.shade_multi, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
-    else k_shade<false><<<dims.shade_single, kShadeThreads, 0, st>>>(sc, pm, pb, fp, iter);
 }
 
 void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, HitRec* hits, TraceMode mode,
@@ -552,7 +563,8 @@ void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, Hi
         io.hit_a = reinterpret_cast<float4*>(hits); io.hit_a_stride = 2;
         io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4;
         io.bias_word = 0x4B000000u; io.chunk = dims.chunk;
-        k_trace_persistent<<<blocks, kTraceBlock, 0, st>>>(sc, io);
+        if (sc.start_inst != kInvalidId) k_trace_persistent<true><<<blocks, kTraceBlock, 0, st>>>(sc, io);
+        else k_trace_persistent<false><<<blocks, kTraceBlock, 0, st>>>(sc, io);
         return;
     }
     if (mode == TRACE_BVH2) k_trace_rays<TRACE_BVH2><<<blocks, kTraceThreads, 0, st>>>(sc, rays, n, hits, tlas2_count, tlas2_leaf_instance, cursor);

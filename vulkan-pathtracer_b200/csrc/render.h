@@ -57,7 +57,7 @@ enum TraceMode { TRACE_BVH8 = 0, TRACE_BVH2 = 1, TRACE_BVH8_COUNT = 2, TRACE_BVH
 // Persistent grid sizes (resident CTAs per SM x SM count of the renderer's device) and the K-trace fetch granularity;
 // computed once per renderer in pt_create, after cudaSetDevice (renderers on different devices do not share them).
 struct LaunchDims {
-    int trace_persistent = 0, trace_walker = 0, trace_bvh2 = 0, trace_count = 0;
+    int trace_persistent = 0, trace_flat = 0, trace_walker = 0, trace_bvh2 = 0, trace_count = 0;
     int shade_single = 0, shade_multi = 0;
     uint32_t chunk = 32;          // rays a K-trace warp takes from the queue per global atomic
 };

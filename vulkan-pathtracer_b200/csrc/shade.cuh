@@ -307,11 +307,13 @@ PT_D V4 sample_texture(const TexRec& tex, V2 uv, const float* lut = nullptr) { r
 struct MaterialData { V4 albedo; V3 normal, emissive; float roughness, metallic; };
 
 // material.glsl:31-69
-template <bool kHwTex = false>
+// kTex: 0 = general (interleaved atlas or separate maps per material), 1 = texture objects (PT_FLAG_HW_BILINEAR), 2 = every
+// textured material of the scene has an atlas (DeviceScene::atlas_only), so the separate-map path is not compiled in
+template <int kTex = 0>
 PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& td, const float* lut = nullptr) {
     const MatRec* mp = sc.materials + td.material_index;
     const uint4 fac = __ldg(reinterpret_cast<const uint4*>(mp));     // factors + presence bits
-    if (kHwTex) {
+    if (kTex == 1) {
         MaterialData md;
         // PT_FLAG_HW_BILINEAR (A/B): the same material.glsl statements with texture() on the texture units (1.8 fixed-point
         // filter weights: not bit-identical to the fp32 lerp below)
@@ -343,7 +345,10 @@ PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& t
     const uint4* atlas = reinterpret_cast<const uint4*>(((uint64_t)aw.y << 32) | aw.x);
     TexRec tex[4];
     Taps taps[4];
-    if (atlas) {
+    if (kTex == 2 && !atlas) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) tex[k].texels = nullptr;       // atlas-only scene: no atlas means no maps
+    } else if (kTex == 2 || atlas) {
         // one set of texel coordinates, four 16-byte fetches: every present map's 2x2 footprint at once
         TexRec at; at.texels = nullptr; at.width = aw.z; at.height = aw.w;
         const float W = (float)at.width, H = (float)at.height;
@@ -406,7 +411,7 @@ PT_D MaterialData get_material_data(const DeviceScene& sc, const TriangleData& t
 // of getTriangleData / getMaterialData nothing but `emissive` is consumed, so only the emissive factor and --
 // when the material has an emissive map -- the interpolated uv and that map's four texels are fetched.
 // Same expressions as above for everything that is computed, hence the same bits.
-template <bool kHwTex = false>
+template <int kTex = 0>
 PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h, const float* lut = nullptr) {
     const PrimRec p = sc.prims[h.primitive_index];
     const MatRec* mp = sc.materials + (p.info & PT_MATERIAL_INDEX_MASK);
@@ -424,10 +429,25 @@ PT_D V3 get_emissive(const DeviceScene& sc, const HitRec& h, const float* lut = 
         V2 uv;
         uv.x = u0 * c.x + u1 * c.y + u2 * c.z;
         uv.y = v0 * c.x + v1 * c.y + v2 * c.z;
-        if (kHwTex) {      // PT_FLAG_HW_BILINEAR
+        if (kTex == 1) {      // PT_FLAG_HW_BILINEAR
             const unsigned long long o = __ldg(sc.mat_tex_objs + 4u * (p.info & PT_MATERIAL_INDEX_MASK) + 2u);
             const float4 te = tex2D<float4>((cudaTextureObject_t)o, uv.x, uv.y);
             return emissive * v3(te.x, te.y, te.z);
+        }
+        if (kTex == 2) {
+            // atlas-only scene: the emissive map is word z of the material's interleaved atlas
+            const uint4 aw = __ldg(reinterpret_cast<const uint4*>(mp) + 5);
+            const uint4* atlas = reinterpret_cast<const uint4*>(((uint64_t)aw.y << 32) | aw.x);
+            const float W = (float)aw.z, H = (float)aw.w;
+            const float u = uv.x * W - 0.5f, v = uv.y * H - 0.5f;
+            const float fu = floorf(u), fv = floorf(v);
+            const uint32_t x0 = wrap_texel(fu, aw.z), x1 = (x0 + 1 == aw.z) ? 0u : x0 + 1;
+            const uint32_t y0 = wrap_texel(fv, aw.w), y1 = (y0 + 1 == aw.w) ? 0u : y0 + 1;
+            const uint4* r0 = atlas + (size_t)y0 * aw.z;
+            const uint4* r1 = atlas + (size_t)y1 * aw.z;
+            const Taps tp{__ldg(&r0[x0].z), __ldg(&r0[x1].z), __ldg(&r1[x0].z), __ldg(&r1[x1].z), u - fu, v - fv};
+            const V4 t = filter_taps(tp, lut);
+            return emissive * v3(t.x, t.y, t.z);
         }
         const uint4 w = __ldg(reinterpret_cast<const uint4*>(mp) + 3);                   // TexRec of the emissive map
         TexRec tex;

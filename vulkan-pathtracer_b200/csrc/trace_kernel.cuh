@@ -134,6 +134,10 @@ PT_D void load_ray(const TraceIO& io, uint32_t slot, RayFrame& f, RayPre& rp, fl
 #else
 #define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock)
 #endif
+// kFlat: the scene is one identity instance (DeviceScene::start_inst is set: C1, C2, C3, C5 and most single-mesh glTF files), so
+// traversal never sees the top level: leaf items are always triangles, the stack holds node groups only and there is no
+// instance entry / exit.  Its own instantiation keeps that code out of the hot loop.
+template <bool kFlat>
 __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     const uint32_t n = io.count_ptr ? *io.count_ptr : io.count;
     const uint32_t lane = threadIdx.x & 31u;
@@ -223,7 +227,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         if (has_t) {
             const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
             T.y &= T.y - 1u;
-            if (cur_inst != kInvalidId) {
+            if (kFlat || cur_inst != kInvalidId) {
                 test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
             } else {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
@@ -256,6 +260,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                 }
                 uint2 e;
                 PT_STACK_POP(e);
+                if (kFlat) { G = e; break; }
                 if (e.x == 0xFFFFFFFFu) {
                     if (e.y) { float t0, t1; load_ray(io, slot, f, rp, t0, t1); }
                     cur_inst = kInvalidId;
