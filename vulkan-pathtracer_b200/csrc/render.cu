@@ -223,8 +223,8 @@ __global__ void __launch_bounds__(256) k_matsort_scatter(DeviceScene sc, PathBuf
 #define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, PT_SHADE_MIN_BLOCKS)
 #else
 #ifndef PT_SHADE_MULTI_MIN_BLOCKS
-#define PT_SHADE_MULTI_MIN_BLOCKS 4
-#endif
+#define PT_SHADE_MULTI_MIN_BLOCKS 5     // 96 registers, no spills in the atlas-only instantiation; 4 -> 5 CTAs per SM measured on B200
+#endif                                  // (profiles/r2e_variants.txt): K-shade C4 3.23 -> 3.13 ms, C3 share 63.7 -> 60.3 ms, C5 25.8 -> 23.7 ms
 #define PT_SHADE_BOUNDS __launch_bounds__(kShadeThreads, kMulti ? PT_SHADE_MULTI_MIN_BLOCKS : 6)
 #endif
 // kTex (shade.cuh): how material maps are fetched — 0 general, 1 texture objects (PT_FLAG_HW_BILINEAR), 2 atlas-only scene.  K-shade is
