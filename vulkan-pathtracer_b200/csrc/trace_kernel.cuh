@@ -281,28 +281,6 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             const uint32_t hits = node_test_fast(sc.nodes, sc.node_bits, node, f, tmin, fminf(tmax, best.t), bias, perm_lut, cb, tb, im);
             G = make_uint2(cb, (hits & 0xFF000000u) | im);
             T = make_uint2(tb, hits & 0x00FFFFFFu);
-#ifdef PT_TRACE_TAIL_PREFETCH
-            // A/B variant: once the queue is exhausted the warp runs its last few rays, each a chain of dependent L2 round
-            // trips (node -> triangles -> next node) with nothing to overlap them.  There — and only there: `exhausted` is
-            // warp-uniform, the steady state pays one predicated branch — the first triangle of the new leaf group and the
-            // inner child that will be visited next are requested together, so the chain pays one round trip per step.
-            if (exhausted) {
-                if (T.y != 0u) {
-                    const char* tp = reinterpret_cast<const char*>(sc.tris + T.x + ((uint32_t)__ffs((int)T.y) - 1u));
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(tp));
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 32));
-                }
-                if (G.y & 0xFF000000u) {
-                    const uint32_t k2 = 31u - (uint32_t)__clz(G.y);
-                    const uint32_t s2 = (k2 - 24u) ^ f.rs;
-                    const uint32_t nx = G.x + __popc(G.y & 0xffu & ((1u << s2) - 1u));
-                    const char* np = reinterpret_cast<const char*>(sc.nodes + nx);
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(np));
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(np + 64));
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.node_bits + 2 * (size_t)nx));
-                }
-            }
-#endif
         }
     }
 }
