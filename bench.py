@@ -204,7 +204,9 @@ def main():
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg (C3, tiles + reduce per frame)")
     ap.add_argument("--strong-steps", type=int, default=3)
     ap.add_argument("--no-l2-flush", action="store_true")
-    ap.add_argument("--single-frame-in-flight", action="store_true", help="e2e leg without the sibling frame context")
+    ap.add_argument("--single-frame-in-flight", action="store_true", help="e2e leg without the sibling frame contexts")
+    ap.add_argument("--frames-in-flight", type=int, default=2, help="e2e leg: frame contexts over one device scene (pt_create_sibling), one per "
+                    "swapchain image in the reference (main.zig:209-217)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
@@ -355,30 +357,33 @@ def main():
     # image and pinned destination, so the tail of frame k overlaps ray generation + primary traversal of frame k+1.
     # N > 1, frame shares: the same on every rank (no per-step collective), both contexts accumulate; after the last step the
     # sibling's accumulation is folded into the parent's, the parents' are reduced to rank 0 and rank 0 reads the mean.
-    in_flight = 2 if ((world == 1 or frames_mode) and not args.single_frame_in_flight) else 1
-    if in_flight == 2:
-        ctx = [r, r.sibling()]
+    in_flight = max(2, args.frames_in_flight) if ((world == 1 or frames_mode) and not args.single_frame_in_flight) else 1
+    ctx, hosts = [r], [host_img]
+    for _ in range(in_flight - 1):
+        c = r.sibling()
         if frames_mode:
-            ctx[1].set_accumulate(True)
-        hosts = [host_img, torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)]
+            c.set_accumulate(True)
+        h = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
         for k in range(2):      # untimed: the sibling creates its copy stream and events on first use
-            ctx[1].record(S.camera_default(W, H, k))
-            b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(ctx[1].handle, hosts[1].data_ptr()))
-        ctx[1].sync()
+            c.record(S.camera_default(W, H, k))
+            b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(c.handle, h.data_ptr()))
+        c.sync()
+        ctx.append(c); hosts.append(h)
     if frames_mode:
-        for c in (ctx if in_flight == 2 else [r]):
+        for c in ctx:
             c.reset_accum()
     barrier()
     t0 = time.perf_counter()
     e2e_rays = 0
-    for k in range(args.steps if in_flight == 2 else 0):
+    for k in range(args.steps if in_flight >= 2 else 0):
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
-        c = ctx[k & 1]
+        c = ctx[k % in_flight]
         c.record(cam)
         if rank == 0:       # the step's result crosses to the host on rank 0 (33.2 MB per step, as d2h_bytes_per_step says)
-            b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(c.handle, hosts[k & 1].data_ptr()))
-    if in_flight == 2:
-        ctx[0].sync(); ctx[1].sync()
+            b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(c.handle, hosts[k % in_flight].data_ptr()))
+    if in_flight >= 2:
+        for c in ctx:
+            c.sync()
     for k in range(args.steps if (in_flight == 1 and not frames_mode) else 0):
         cam = S.camera_default(W, H, frame_of(args.warmup + k))     # host camera struct (68 B) crosses in pt_render
         render_frame(cam)
@@ -394,8 +399,8 @@ def main():
         if rank == 0:
             b200pt.check(b200pt.lib().pt_read_rgba32f_overlapped(r.handle, host_img.data_ptr()))
     if frames_mode:
-        if in_flight == 2:
-            r.add_accum(ctx[1])
+        for c in ctx[1:]:
+            r.add_accum(c)
         r.reduce_accum(0)               # on the library's communication stream, behind this rank's last frame
         if rank == 0:
             b200pt.check(b200pt.lib().pt_read_accum_mean(r.handle, host_img.data_ptr(), args.steps * world))   # synchronises
@@ -505,8 +510,8 @@ def main():
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu, "strong": strong}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
-    if in_flight == 2:
-        ctx[1].deinit()     # the sibling goes first: the scene belongs to r
+    for c in ctx[1:]:
+        c.deinit()          # siblings go first: the scene belongs to r
     r.deinit()
     if world > 1:
         dist.destroy_process_group()
