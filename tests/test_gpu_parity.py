@@ -5,6 +5,7 @@ Bar: primary-hit ids bit-exact; radiance bit-exact too (the arithmetic contract 
 the fp32 expression trees identical: no FMA contraction, IEEE sqrt/div, one shared definition of sin/cos);
 NaNs compare equal to NaNs.  north_star allows <=0.01 % edge-tie pixels and a radiance tolerance; the
 tests hold the stricter bar and say so when they relax it."""
+import functools
 import os
 
 import numpy as np
@@ -98,18 +99,27 @@ def test_unorm8_conversion_is_exact():
 LBVH, OPT, SAH, PLOC = b200pt.PT_FLAG_BVH_LBVH, b200pt.PT_FLAG_BVH_OPTIMAL_COLLAPSE, b200pt.PT_FLAG_BVH_SAH, b200pt.PT_FLAG_BVH_PLOC
 
 
-@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2, LBVH, LBVH | OPT, SAH, LBVH | b200pt.PT_FLAG_TRACE_WALKER,
-                                   LBVH | b200pt.PT_FLAG_TRACE_BVH2, PLOC, PLOC | b200pt.PT_FLAG_TRACE_BVH2])
-@pytest.mark.parametrize("seed,ntri,nmesh,ninst", [(3, 3000, 3, 7), (5, 3, 3, 4), (11, 20000, 2, 40), (12, 64, 5, 1)])
-def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
+@functools.lru_cache(maxsize=None)
+def _brute_force_case(seed, ntri, nmesh, ninst):
+    """Scene, rays and the oracle's brute-force hits (every ray against every triangle, no hierarchy): they do not
+    depend on the builder / kernel flags under test, so they are computed once per scene."""
     ps = S.random_soup(seed, ntri, nmesh, ninst).pack()
-    r = b200pt.Renderer(ps, 32, 32, 1, 1, flags=flags)
     rays = random_rays(seed, 100000, dtype=b200pt.PtRay_dtype)
     # axis-parallel and zero-component directions, rays starting on geometry
     rays["dir"][:300] = np.tile(np.eye(3, dtype=np.float32), (100, 1))
     rays["dir"][300:600] = -np.tile(np.eye(3, dtype=np.float32), (100, 1))
-    hg = r.trace(rays)
     ho = orc.OracleScene(ps, False).trace(rays, use_bvh=False)
+    rays.setflags(write=False); ho.setflags(write=False)
+    return ps, rays, ho
+
+
+@pytest.mark.parametrize("flags", [0, b200pt.PT_FLAG_TRACE_WALKER, b200pt.PT_FLAG_TRACE_BVH2, LBVH, LBVH | OPT, SAH, LBVH | b200pt.PT_FLAG_TRACE_WALKER,
+                                   LBVH | b200pt.PT_FLAG_TRACE_BVH2, PLOC, PLOC | b200pt.PT_FLAG_TRACE_BVH2])
+@pytest.mark.parametrize("seed,ntri,nmesh,ninst", [(3, 3000, 3, 7), (5, 3, 3, 4), (11, 20000, 2, 40), (12, 64, 5, 1)])
+def test_traversal_matches_brute_force(flags, seed, ntri, nmesh, ninst):
+    ps, rays, ho = _brute_force_case(seed, ntri, nmesh, ninst)
+    r = b200pt.Renderer(ps, 32, 32, 1, 1, flags=flags)
+    hg = r.trace(rays)
     bad = hits_mismatch(hg, ho)
     assert not bad.any(), f"{int(bad.sum())} of {len(rays)} rays differ from brute force"
     r.deinit()
