@@ -339,6 +339,20 @@ int pt_get_stats(PtRenderer* r, PtStats* out);
 /* Kernel-level access for parity tests: trace `n` arbitrary world-space rays through the same
  * BVH and traversal kernel pt_render uses (host pointers). */
 int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits);
+/* The same query for callers that cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * `device_rays` / `device_hits` are DEVICE pointers on the renderer's GPU
+ * (n records each, caller-owned); the work is enqueued on `cuda_stream` (NULL = the renderer's own
+ * stream, which pt_sync waits for) and not waited for.  The call makes no cudaMalloc / cudaFree or
+ * other allocating call: the kernel's scratch (per-ray traversal records, hit records, the fetch
+ * cursor) is one fixed 14 MiB __device__ array inside the library (held by every GPU that loads
+ * it, until exit), sized for PT_NOALLOC_MAX_RAYS rays; a larger n returns
+ * PT_ERR_INVALID_ARGUMENT and launches nothing (split the batch, or use pt_trace_rays).  Every call
+ * on a device shares that array: calls on one stream are ordered, calls that overlap on the GPU
+ * (other streams, renderers or threads) race.  Default traversal kernel only (a renderer created
+ * with a PT_FLAG_TRACE_* flag is rejected).  Hits are bit-identical to pt_trace_rays'. */
+#define PT_NOALLOC_MAX_RAYS 131072u
+int pt_trace_rays_noalloc(PtRenderer* r, const PtRay* device_rays, size_t n, PtHit* device_hits, void* cuda_stream);
 /* Independent, unoptimised one-thread-per-ray walker over the shipped BVH8: counts the nodes and
  * triangles an ordered closest-hit traversal must decode (SURVEY.md §8d algorithmic bytes =
  * 80*nodes + 48*tris).  Counts the ray set of the last pt_render. */

@@ -6,7 +6,7 @@ cd "$(dirname "$0")/../vulkan-pathtracer_b200/csrc"
 NAME="$1"; shift
 OBJ=_obj_$NAME; mkdir -p $OBJ ../variants
 NV="/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo --fmad=false -Xcompiler -fPIC,-ffp-contract=off $*"
-for f in api render bvh_build; do $NV -c $f.cu -o $OBJ/$f.o -Xptxas -v 2> $OBJ/$f.log & done
+for f in api render noalloc bvh_build; do $NV -c $f.cu -o $OBJ/$f.o -Xptxas -v 2> $OBJ/$f.log & done
 wait
 g++ -O2 -std=c++17 -fPIC -ffp-contract=off -c host.cpp -o $OBJ/host.o
 g++ -O2 -std=c++17 -fPIC -ffp-contract=off -I/usr/local/cuda/include $* -c comm.cpp -o $OBJ/comm.o

@@ -33,6 +33,7 @@ PT_FLAG_BVH_SAH, PT_FLAG_BVH_OPTIMAL_COLLAPSE, PT_FLAG_RUSSIAN_ROULETTE, PT_FLAG
 
 PtHit_dtype = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("instance", "<u4"), ("primitive_index", "<u4"),
                         ("triangle_index", "<u4")])
+NOALLOC_MAX_RAYS = 131072   # PT_NOALLOC_MAX_RAYS
 PtRay_dtype = np.dtype([("origin", "<f4", 3), ("tmin", "<f4"), ("dir", "<f4", 3), ("tmax", "<f4")])
 
 
@@ -102,6 +103,7 @@ def lib():
         L.pt_set_profiling.argtypes = [C.c_void_p, C.c_int]
         L.pt_get_stats.argtypes = [C.c_void_p, C.POINTER(PtStats)]
         L.pt_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.pt_trace_rays_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.pt_count_traversal.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.pt_read_rgba32f_overlapped.argtypes = [C.c_void_p, C.c_void_p]
         L.pt_ipc_export_image.argtypes = [C.c_void_p, C.c_void_p]
@@ -376,6 +378,11 @@ class Renderer:
         hits = np.empty(len(rays), PtHit_dtype)
         check(lib().pt_trace_rays(self.handle, rays.ctypes.data, len(rays), hits.ctypes.data))
         return hits
+
+    def trace_noalloc(self, device_rays, n, device_hits, stream=None):
+        """pt_trace_rays_noalloc: DEVICE addresses (ints) of n PtRay / n PtHit records; enqueued on `stream` (None = the
+        renderer's own, which sync() waits for).  No allocation; n <= NOALLOC_MAX_RAYS."""
+        check(lib().pt_trace_rays_noalloc(self.handle, device_rays, n, device_hits, stream))
 
     def count_traversal(self):
         n, t, r = C.c_uint64(), C.c_uint64(), C.c_uint64()
