@@ -57,12 +57,16 @@ PT_D uint32_t node_test_fast(const Bvh8Node* __restrict__ nodes, const uint4* __
         const float bx = (__uint_as_float(n0.x) - f.o.x) * f.idir.x, by = (__uint_as_float(n0.y) - f.o.y) * f.idir.y,
                     bz = (__uint_as_float(n0.z) - f.o.z) * f.idir.z;
         const float B23 = 8388608.0f;
-        anx = ax - fabsf(ax) * eps; afx = ax + fabsf(ax) * eps;
-        any = ay - fabsf(ay) * eps; afy = ay + fabsf(ay) * eps;
-        anz = az - fabsf(az) * eps; afz = az + fabsf(az) * eps;
-        bnx = __fsub_rd(bx - fabsf(bx) * eps, B23 * anx); bfx = __fsub_ru(bx + fabsf(bx) * eps, B23 * afx);
-        bny = __fsub_rd(by - fabsf(by) * eps, B23 * any); bfy = __fsub_ru(by + fabsf(by) * eps, B23 * afy);
-        bnz = __fsub_rd(bz - fabsf(bz) * eps, B23 * anz); bfz = __fsub_ru(bz + fabsf(bz) * eps, B23 * afz);
+        // slack of 2^-20 relative on slope and offset, then the 2^23 bias folded into the offset with directed rounding.
+        // Explicit FMAs: |v| * 2^-20 and 2^23 * a are exact products (powers of two), so each FMA rounds once, exactly where
+        // the FMUL + FADD pair of the walker (trace.cuh:node_test) rounds — same planes, 12 instructions fewer per node
+        // (profiles/r2o_variants.txt: trace C2 1.126 -> 1.107 ms, C4 14.22 -> 14.13).
+        anx = __fmaf_rn(-fabsf(ax), eps, ax); afx = __fmaf_rn(fabsf(ax), eps, ax);
+        any = __fmaf_rn(-fabsf(ay), eps, ay); afy = __fmaf_rn(fabsf(ay), eps, ay);
+        anz = __fmaf_rn(-fabsf(az), eps, az); afz = __fmaf_rn(fabsf(az), eps, az);
+        bnx = __fmaf_rd(-B23, anx, __fmaf_rn(-fabsf(bx), eps, bx)); bfx = __fmaf_ru(-B23, afx, __fmaf_rn(fabsf(bx), eps, bx));
+        bny = __fmaf_rd(-B23, any, __fmaf_rn(-fabsf(by), eps, by)); bfy = __fmaf_ru(-B23, afy, __fmaf_rn(fabsf(by), eps, by));
+        bnz = __fmaf_rd(-B23, anz, __fmaf_rn(-fabsf(bz), eps, bz)); bfz = __fmaf_ru(-B23, afz, __fmaf_rn(fabsf(bz), eps, bz));
     }
     const bool px = (f.rs & 1u) != 0, py = (f.rs & 2u) != 0, pz = (f.rs & 4u) != 0;
     uint32_t hits = 0;
