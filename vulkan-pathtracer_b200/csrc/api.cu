@@ -58,6 +58,7 @@ int alloc_frame(PtRenderer* r, uint32_t full_w, uint32_t full_h, uint32_t divide
     pm.world = tiles ? (uint32_t)r->cfg.world : 1u;
     const uint32_t n_tiles = pm.tiles_x * pm.tiles_y;
     const uint32_t owned = n_tiles > pm.rank ? (n_tiles - pm.rank + pm.world - 1u) / pm.world : 0u;
+    if ((uint64_t)owned * 256u >= 0x80000000ull) { set_error("extent too large (K-trace uses bit 31 of the slot index)"); return PT_ERR_INVALID_ARGUMENT; }
     pm.num_slots = owned * 256u;
     const size_t n = pm.num_slots;
     const uint32_t S = r->cfg.num_samples, B = r->cfg.num_bounces;
@@ -715,7 +716,7 @@ int pt_get_stats(PtRenderer* r, PtStats* out) {
 
 int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits) {
     PT_REQUIRE(r && (n == 0 || (rays && hits)), "pt_trace_rays: null argument");
-    PT_REQUIRE(n < 0xFFFFFF00ull, "pt_trace_rays: too many rays");
+    PT_REQUIRE(n < 0x80000000ull, "pt_trace_rays: too many rays (K-trace uses bit 31 of the slot index)");
     if (n == 0) return PT_OK;
     PT_CUDA_CHECK(cudaSetDevice(r->device));
     if (r->parent) r->scene = r->parent->scene;

@@ -8,7 +8,8 @@
 //    one node test, in two warp-wide phases, so lanes in the same phase execute together;
 //  * node test: 80-byte node as 5 x LDG.128, 8-bit planes converted with PRMT + FADD (no I2F on
 //    the quarter-rate pipe), branch-free hit-mask assembly, conservative slabs (explicit FMAs);
-//  * the traversal stack (node / leaf groups, 8 bytes each) lives in thread-local memory.
+//  * the traversal stack (node / leaf groups, 8 bytes each) lives in thread-local memory;
+//  * the closest hit lives in the slot's hit record, only its distance in a register: 64 registers, 8 CTAs per SM.
 // The closest-hit semantics are exactly those of trace_bvh8() in trace.cuh (the simple walker that
 // the tests and the algorithmic-byte counter use).
 #pragma once
@@ -114,6 +115,42 @@ struct TraceIO {
 };
 
 constexpr int kTraceBlock = 128;
+constexpr int kTraceMinBlocks = 8;       // 64 registers: 32 resident warps per SM (see test_triangle_rec)
+
+// Triangle test of K-trace.  The closest hit is kept in the slot's hit record (hit_a / hit_b, global memory) and only its distance
+// in a register; bit 31 of `slot` says that a record has been written.  Five registers less across the loop than a Hit in
+// registers, which is what lets the kernel fit 64 registers without spills (8 CTAs per SM instead of 7): accepted candidates are
+// rare (2-3 per ray, 2-4 lanes at a time), so the extra stores cost less than the occupancy gains.  Measured on B200
+// (profiles/r2t_variants.txt, r2u_variants.txt): K-trace C2 1.105 -> 1.073 ms, C3 606 -> 573 ms, C4 14.13 -> 13.60 ms,
+// C5 43.5 -> 41.6 ms; the record in memory alone, still at 7 CTAs: C2 1.117 ms.
+// Same acceptance rule as test_triangle() / hit_better(): lexicographic (t, instance, primitive, triangle), and the ray's own
+// tmax (not the closest distance) bounds the test so that candidates with t == best_t reach the tie-break.
+PT_D void test_triangle_rec(const Bvh8Tri* __restrict__ tris, uint32_t idx, V3 o, const RayPre& rp, float tmin, float tmax, uint32_t inst,
+                            float& best_t, uint32_t& slot, float4* hit_a, uint2* hit_b) {
+    const float4* q = reinterpret_cast<const float4*>(tris + idx);
+    const float4 p0 = __ldg(q), p1 = __ldg(q + 1), p2 = __ldg(q + 2);
+    float t, V, W, det;
+    if (intersect_tri_raw(o, rp, p0, p1, p2, tmin, tmax, t, V, W, det)) {
+        const uint32_t prim = __float_as_uint(p0.w), tri = __float_as_uint(p1.w);
+        bool better = t < best_t;
+        if (t == best_t) {
+            if (!(slot & 0x80000000u)) better = true;       // nothing recorded yet: the invalid ids of hit_init() lose every tie
+            else {
+                // this thread's own earlier stores (program order); volatile keeps the compiler from using the read-only path
+                const volatile uint32_t* pa = reinterpret_cast<const volatile uint32_t*>(hit_a);
+                const volatile uint32_t* pb = reinterpret_cast<const volatile uint32_t*>(hit_b);
+                const uint32_t binst = pa[3], bprim = pb[0], btri = pb[1];
+                better = inst != binst ? inst < binst : (prim != bprim ? prim < bprim : tri < btri);
+            }
+        }
+        if (better) {
+            // the two barycentric divisions only for candidates that replace the closest hit (trace.cuh:test_triangle)
+            best_t = t; slot |= 0x80000000u;
+            *hit_a = make_float4(t, V / det, W / det, __uint_as_float(inst));
+            *hit_b = make_uint2(prim, tri);
+        }
+    }
+}
 constexpr int kStackSize = 64;
 #ifdef PT_TRACE_REFILL_MIN
 constexpr int kRefillMin = PT_TRACE_REFILL_MIN;
@@ -133,11 +170,7 @@ PT_D void load_ray(const TraceIO& io, uint32_t slot, RayFrame& f, RayPre& rp, fl
     tmin = ro.w; tmax = rd.w;
 }
 
-#ifdef PT_TRACE_MIN_BLOCKS
-#define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock, PT_TRACE_MIN_BLOCKS)
-#else
-#define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock)
-#endif
+#define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock, kTraceMinBlocks)
 // kFlat: the scene is one identity instance (DeviceScene::start_inst is set: C1, C2, C3, C5 and most single-mesh glTF files), so
 // traversal never sees the top level: leaf items are always triangles, the stack holds node groups only and there is no
 // instance entry / exit.  Its own instantiation keeps that code out of the hot loop.
@@ -170,18 +203,18 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     // per-lane ray state: ONE frame (world space at TLAS level, object space inside a transformed
     // instance; the world frame is re-loaded from the slot when such an instance is left)
     bool active = false;
-    uint32_t slot = 0;
+    uint32_t slot = 0;                   // bit 31: a hit record has been written for this ray (slots are < 2^31)
+#define PT_SLOT (slot & 0x7fffffffu)
     RayFrame f;
     RayPre rp;
     float tmin = 0.0f, tmax = 0.0f;
     uint32_t cur_inst = kInvalidId;
-    Hit best;
+    float best_t = kMissT;               // distance of the closest hit; the hit itself is in the slot's record (test_triangle_rec)
     uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
     uint2 stack[kStackSize];
 #define PT_STACK_PUSH(v) do { if (sp < kStackSize) stack[sp++] = (v); else *sc.error_flag = 1u; } while (0)
 #define PT_STACK_POP(e) do { (e) = stack[--sp]; } while (0)
     int sp = 0;
-    hit_init(best);
     f.o = v3s(0.0f); f.idir = v3s(1.0f); f.rs = 7u;
     rp.m0x = 1.0f; rp.m0y = 0.0f; rp.m0z = 0.0f; rp.m1x = 0.0f; rp.m1y = 1.0f; rp.m1z = 0.0f; rp.Sz = 1.0f; rp.kz = 2;
 
@@ -210,7 +243,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                         slot = io.queue ? io.queue[qi] : qi;
                         load_ray(io, slot, f, rp, tmin, tmax);
                         cur_inst = sc.start_inst;
-                        hit_init(best);
+                        best_t = kMissT;
                         sp = 0;
                         G = make_uint2(sc.start_root, 0x80000000u);
                         T = make_uint2(0u, 0u);
@@ -232,7 +265,8 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
             T.y &= T.y - 1u;
             if (kFlat || cur_inst != kInvalidId) {
-                test_triangle(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best);
+                test_triangle_rec(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best_t, slot, io.hit_a + (size_t)PT_SLOT * io.hit_a_stride,
+                                  io.hit_b + (size_t)PT_SLOT * io.hit_b_stride);
             } else {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
                 if (T.y) PT_STACK_PUSH(T);
@@ -244,7 +278,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                 PT_STACK_PUSH(make_uint2(0xFFFFFFFFu, identity ? 0u : 1u));
                 if (!identity) {
                     V3 oo, dd;
-                    const float4 wd = io.ray_d[slot];      // the world direction is not kept in registers
+                    const float4 wd = io.ray_d[PT_SLOT];      // the world direction is not kept in registers
                     to_object(sc.instances, cur_inst, f.o, v3(wd.x, wd.y, wd.z), oo, dd);
                     frame_set(f, oo, dd);
                     rp = ray_precompute(dd);
@@ -257,8 +291,10 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         if (active && T.y == 0u && (G.y & 0xFF000000u) == 0u) {
             for (;;) {
                 if (sp == 0) {
-                    io.hit_a[(size_t)slot * io.hit_a_stride] = make_float4(best.t, best.b1, best.b2, __uint_as_float(best.inst));
-                    io.hit_b[(size_t)slot * io.hit_b_stride] = make_uint2(best.prim, best.tri);
+                    if (!(slot & 0x80000000u)) {         // no hit was recorded: the miss record of hit_init()
+                        io.hit_a[(size_t)slot * io.hit_a_stride] = make_float4(kMissT, 0.0f, 0.0f, __uint_as_float(kInvalidId));
+                        io.hit_b[(size_t)slot * io.hit_b_stride] = make_uint2(kInvalidId, kInvalidId);
+                    }
                     active = false;
                     break;
                 }
@@ -266,7 +302,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                 PT_STACK_POP(e);
                 if (kFlat) { G = e; break; }
                 if (e.x == 0xFFFFFFFFu) {
-                    if (e.y) { float t0, t1; load_ray(io, slot, f, rp, t0, t1); }
+                    if (e.y) { float t0, t1; load_ray(io, PT_SLOT, f, rp, t0, t1); }
                     cur_inst = kInvalidId;
                     continue;
                 }
@@ -282,7 +318,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             const uint32_t node = G.x + __popc(G.y & 0xffu & ((1u << s) - 1u));
             if (G.y & 0xFF000000u) PT_STACK_PUSH(G);
             uint32_t cb, tb, im;
-            const uint32_t hits = node_test_fast(sc.nodes, sc.node_bits, node, f, tmin, fminf(tmax, best.t), bias, perm_lut, cb, tb, im);
+            const uint32_t hits = node_test_fast(sc.nodes, sc.node_bits, node, f, tmin, fminf(tmax, best_t), bias, perm_lut, cb, tb, im);
             G = make_uint2(cb, (hits & 0xFF000000u) | im);
             T = make_uint2(tb, hits & 0x00FFFFFFu);
         }
@@ -291,5 +327,6 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
 
 #undef PT_STACK_PUSH
 #undef PT_STACK_POP
+#undef PT_SLOT
 
 }  // namespace pt
