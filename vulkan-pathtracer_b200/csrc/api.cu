@@ -257,7 +257,7 @@ int upload_scene(PtRenderer* r, const PtSceneDesc* s) {
     if ((rc = upload_instance_records(r)) != PT_OK) return rc;
     DeviceScene& sc = r->scene;
     sc.triangle_data = r->d_blob; sc.prims = r->d_prims; sc.materials = r->d_materials; sc.textures = r->d_textures;
-    sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.node_bits = r->bvh.node_bits8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
+    sc.instances = r->d_instances; sc.nodes = r->bvh.nodes8; sc.tris = r->bvh.tris8; sc.tlas_leaf_instance = r->bvh.tlas_leaf_instance;
     sc.nodes2 = r->bvh.nodes2; sc.tris2 = r->bvh.tris2; sc.tlas2 = r->bvh.tlas2; sc.tlas_root = r->bvh.tlas_root8;
     PT_CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&sc.error_flag), r->h_error, 0));
     sc.mat_tex_objs = r->d_mat_tex_objs;
@@ -804,7 +804,7 @@ int pt_debug_bvh_digest(PtRenderer* r, uint64_t digest[6]) {
     for (uint32_t i = 0; i < b.num_nodes8; ++i) {
         uint64_t h = fnv(seed, &n8[i], 16);                 // frame + exponents + imask
         uint8_t kinds[8];
-        for (int k = 0; k < 8; ++k) kinds[k] = n8[i].meta[k] >> 5;
+        for (int k = 0; k < 8; ++k) kinds[k] = (uint8_t)(((n8[i].valid >> (24 + k)) & 1u) ? 4u : ((n8[i].valid >> (kLeafStride * k)) & 3u));
         h = fnv(h, kinds, 8);
         h = fnv(h, n8[i].qlo_x, 48);
         sum += h;

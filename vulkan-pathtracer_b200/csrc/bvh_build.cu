@@ -434,11 +434,10 @@ struct CollapseArgs {
     const uint32_t* order;      // sorted leaf -> source leaf
     const float* leaf_lo;       // source leaf boxes
     const float* leaf_hi;
-    uint32_t max_leaf;          // 3 for a BLAS (triangles per leaf slot), 1 for the TLAS
+    uint32_t max_leaf;          // <= kLeafStride: 2 for a BLAS (triangles per leaf slot), 1 for the TLAS
     const uint8_t* dp;          // decisions of k_collapse_dp (8 per binary node), or nullptr: greedy surface-area expansion
     // outputs
     Bvh8Node* nodes8;           // global node array
-    uint4* node_bits8;          // 2 per node
     uint32_t* node_counter;     // global
     uint32_t* tri_counter;      // global (BLAS: tris8 entries; TLAS: leaf-instance entries)
     const Bvh8Tri* tris_sorted; // BLAS: Morton-ordered triangles of this mesh
@@ -564,13 +563,11 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
     out.px = p[0]; out.py = p[1]; out.pz = p[2];
     out.ex = (uint8_t)ebits[0]; out.ey = (uint8_t)ebits[1]; out.ez = (uint8_t)ebits[2];
     out.child_base = child_base; out.tri_base = tri_base;
-    uint32_t imask = 0, inner_rank = 0, leaf_off = 0;
-    uint32_t cbits[8];
+    uint32_t imask = 0, inner_rank = 0, leaf_off = 0, valid = 0;
     const float delta = 1.0f / 1024.0f;   // quantisation slack (fraction of a grid step)
     for (int s = 0; s < 8; ++s) {
         int c = child_in_slot[s];
         if (c < 0) {
-            out.meta[s] = 0; cbits[s] = 0u;
             out.qlo_x[s] = out.qlo_y[s] = out.qlo_z[s] = 255;   // inverted box: never hit
             out.qhi_x[s] = out.qhi_y[s] = out.qhi_z[s] = 0;
             continue;
@@ -586,16 +583,14 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
         out.qhi_x[s] = qh[0]; out.qhi_y[s] = qh[1]; out.qhi_z[s] = qh[2];
         if (!ch[c].leaf) {
             imask |= 1u << s;
-            out.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
-            cbits[s] = 1u << (24u + (uint32_t)s);
+            valid |= 1u << (24u + (uint32_t)s);
             a.wq2[q_base + inner_rank] = ch[c].ref;
             a.wq8[q_base + inner_rank] = child_base + inner_rank;
             inner_rank++;
         } else {
             const uint32_t k = ch[c].count;
-            const uint32_t unary = (k == 1) ? 1u : (k == 2 ? 3u : 7u);
-            out.meta[s] = (uint8_t)((unary << 5) | leaf_off);
-            cbits[s] = unary << leaf_off;
+            // unary count in the slot's two bits of `valid`; the items themselves are dense in slot order (leaf_off)
+            valid |= ((k == 1) ? 1u : 3u) << (kLeafStride * (uint32_t)s);
             // the (at most max_leaf) leaves under this child, left to right; any binary topology
             uint32_t st[4]; int sp = 0; uint32_t t = 0;
             if (ch[c].first != 0xFFFFFFFFu) {
@@ -622,18 +617,17 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
         }
     }
     out.imask = (uint8_t)imask;
+    out.valid = valid; out.spare = 0u;
     a.nodes8[b8] = out;
-    a.node_bits8[2 * (size_t)b8] = make_uint4(cbits[0], cbits[1], cbits[2], cbits[3]);
-    a.node_bits8[2 * (size_t)b8 + 1] = make_uint4(cbits[4], cbits[5], cbits[6], cbits[7]);
 }
 
 }  // namespace
 
 // ------------------------------------------------------------------ host orchestration
 void SceneBvh::release() {
-    cudaFree(nodes8); cudaFree(node_bits8); cudaFree(tris8); cudaFree(tlas_leaf_instance); cudaFree(nodes2); cudaFree(tris2);
+    cudaFree(nodes8); cudaFree(tris8); cudaFree(tlas_leaf_instance); cudaFree(nodes2); cudaFree(tris2);
     cudaFree(tlas2); cudaFree(tlas2_leaf_instance); cudaFree(mesh_bounds); cudaFree(mesh_tri_range); mesh_tri_range = nullptr;
-    nodes8 = nullptr; node_bits8 = nullptr; tris8 = nullptr; tlas_leaf_instance = nullptr; nodes2 = nullptr; tris2 = nullptr;
+    nodes8 = nullptr; tris8 = nullptr; tlas_leaf_instance = nullptr; nodes2 = nullptr; tris2 = nullptr;
     tlas2 = nullptr; tlas2_leaf_instance = nullptr; mesh_bounds = nullptr;
 }
 
@@ -662,8 +656,9 @@ struct Scratch {
     uint32_t* cur_parent = nullptr;   // parent links of the tree just built (Karras layout), for k_collapse_dp
     uint32_t sah_levels = 0;
     uint32_t capacity = 0;        // entries of wq2 / wq8
-    uint32_t max_leaf = 2;        // triangles per BLAS leaf slot (format limit 3; measured 1 / 2 / 3 on C2: 1.438 / 1.406 /
-                                  // 1.429 ms, on C4: 19.4 / 19.5 / 20.3 ms -- a triangle test costs ~0.7 node tests here)
+    uint32_t max_leaf = kLeafStride;   // triangles per BLAS leaf slot = the format's limit (two bits of Bvh8Node::valid per slot);
+                                  // 1 / 2 / 3 measured on C2 in round 1: 1.438 / 1.406 / 1.429 ms, C4: 19.4 / 19.5 / 20.3 ms, and 3 again on
+                                  // the round-2 kernel: no better (profiles/r2t_variants.txt) -- a triangle test costs ~0.7 node tests here
     uint32_t refit_repairs = 0;   // nodes the verification pass had to correct (expected 0)
     void release() {
         cudaFree(cid[0]); cudaFree(cid[1]); cudaFree(nn); cudaFree(keep); cudaFree(pos);
@@ -861,7 +856,7 @@ int build_tlas(Scratch& s, SceneBvh* out, const PtInstance* d_instances, cudaStr
         k_gather_u32<<<blocks_for(NI), kThreads, 0, st>>>(ids_unsorted, s.vals_out, NI, out->tlas2_leaf_instance);
         CollapseArgs a{};
         a.nodes2 = out->tlas2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
-        a.max_leaf = 1; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tlas_leaf_counter;
+        a.max_leaf = 1; a.nodes8 = out->nodes8; a.node_counter = node_counter; a.tri_counter = tlas_leaf_counter;
         a.tris_sorted = nullptr; a.tris8 = nullptr; a.leaf_ids = ids_unsorted; a.leaf_out = out->tlas_leaf_instance;
         a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = s.counters + 4; a.capacity = s.capacity; a.overflow = s.counters + 5;
         rc = collapse_tree(s, a, NI, &out->tlas_root8, st);
@@ -910,7 +905,6 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
 
     const size_t cap_nodes = (size_t)total + M + NI + 8;
     PT_CU(cudaMalloc(&out->nodes8, sizeof(Bvh8Node) * cap_nodes));
-    PT_CU(cudaMalloc(&out->node_bits8, sizeof(uint4) * 2 * cap_nodes));
     PT_CU(cudaMalloc(&out->tris8, sizeof(Bvh8Tri) * std::max(total, 1u)));
     PT_CU(cudaMalloc(&out->tris2, sizeof(Bvh8Tri) * std::max(total, 1u)));
     PT_CU(cudaMalloc(&out->nodes2, sizeof(Bvh2Node) * std::max(total, 1u)));
@@ -942,7 +936,7 @@ int build_scene_bvh(const uint8_t* d_blob, const PrimRec* d_prims, const std::ve
         k_reorder_tris<<<blocks_for(n), kThreads, 0, st>>>(s.tmp_tris, s.vals_out, n, out->tris2 + out->tri_off[m]);
         CollapseArgs a{};
         a.nodes2 = n2; a.range = s.range; a.order = s.vals_out; a.leaf_lo = s.leaf_lo; a.leaf_hi = s.leaf_hi;
-        a.max_leaf = s.max_leaf; a.nodes8 = out->nodes8; a.node_bits8 = out->node_bits8; a.node_counter = node_counter; a.tri_counter = tri_counter;
+        a.max_leaf = s.max_leaf; a.nodes8 = out->nodes8; a.node_counter = node_counter; a.tri_counter = tri_counter;
         a.tris_sorted = out->tris2 + out->tri_off[m]; a.tris8 = out->tris8; a.leaf_ids = nullptr; a.leaf_out = nullptr;
         a.wq2 = s.wq2; a.wq8 = s.wq8; a.tail = tail; a.capacity = L + 8; a.overflow = overflow;
         PT_TRY(collapse_tree(s, a, n, &out->blas_root8[m], st));

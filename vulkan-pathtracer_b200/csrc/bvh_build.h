@@ -9,7 +9,6 @@ namespace pt {
 struct SceneBvh {
     // BVH8 (shipped structure)
     Bvh8Node* nodes8 = nullptr;
-    uint4* node_bits8 = nullptr;        // 2 per node: pre-expanded child hit-mask words (see DeviceScene::node_bits)
     uint32_t num_nodes8 = 0;
     Bvh8Tri* tris8 = nullptr;
     uint32_t num_tris = 0;

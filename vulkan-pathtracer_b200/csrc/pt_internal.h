@@ -26,20 +26,24 @@ void set_error(const std::string& msg);
 // 80 bytes = 5 x 16 B, 16-byte aligned (Ylitie, Karras, Laine 2017 layout):
 //   n0: origin p.xyz (3 x f32) | ex, ey, ez (biased exponents, u8) | imask (u8: slots holding inner nodes)
 //   n1: child_base (u32: index of the first inner child) | tri_base (u32: index of the first leaf
-//       triangle / instance) | meta[8] (u8 per slot: 0 = empty; inner: 0b001sssss with sssss = 24+slot;
-//       leaf: high 3 bits = unary triangle count (001,011,111), low 5 bits = offset from tri_base)
+//       triangle / instance) | valid (u32: bit 24 + s = slot s holds an inner node (== imask); bits 2s, 2s + 1 = unary
+//       count (01, 11) of the triangles / instances in leaf slot s; both clear = empty slot) | spare (0).
+//       Leaf items are stored densely in slot order: item k of leaf slot s sits at tri_base + popc(valid & ((1 << 2s) - 1)) + k.
+//       A node test ANDs its candidate hit bits with `valid`, so no per-slot table is loaded (round 2 until r2v kept the eight
+//       pre-expanded hit-mask words of a node in a second array: two more LDG.128 and a second memory round trip per node test).
 //   n2: qlo_x[8] | qlo_y[8]      n3: qlo_z[8] | qhi_x[8]      n4: qhi_y[8] | qhi_z[8]
 // child box = p + q * 2^(e-127)   (lo rounded down, hi rounded up, with slack, see bvh_build.cu)
 struct __align__(16) Bvh8Node {
     float px, py, pz;
     uint8_t ex, ey, ez, imask;
     uint32_t child_base, tri_base;
-    uint8_t meta[8];
+    uint32_t valid, spare;
     uint8_t qlo_x[8], qlo_y[8];
     uint8_t qlo_z[8], qhi_x[8];
     uint8_t qhi_y[8], qhi_z[8];
 };
 static_assert(sizeof(Bvh8Node) == 80, "Bvh8Node must be 80 bytes");
+constexpr uint32_t kLeafStride = 2;      // bits of `valid` per leaf slot = triangles a leaf slot can hold
 
 // Leaf triangle: 48 bytes = 3 x float4; ids ride in the w lanes.
 //   v0.xyz, w = primitive_index (bits) | v1.xyz, w = triangle_index (bits) | v2.xyz, w = unused
@@ -97,8 +101,6 @@ struct DeviceScene {
     const TexRec* textures;
     const InstanceRec* instances;
     const Bvh8Node* nodes;       // all BLASes + TLAS
-    const uint4* node_bits;      // 2 x uint4 per node: per slot the hit-mask word of that child (inner: 1 << (24 + slot),
-                                 // leaf: unary triangle count << offset, empty: 0) — the meta bytes pre-expanded for K-trace
     const Bvh8Tri* tris;         // leaf triangles (BLAS) in collapse order
     const uint32_t* tlas_leaf_instance;  // TLAS leaf slots -> instance index
     const Bvh2Node* nodes2;      // LBVH trees (reference walker)

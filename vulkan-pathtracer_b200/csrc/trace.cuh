@@ -149,8 +149,8 @@ PT_D void to_object(const InstanceRec* __restrict__ inst, uint32_t i, V3 o, V3 d
 
 // ------------------------------------------------------------------ BVH8 node test
 // Returns the hit mask of one 80-byte node: bits 31..24 = inner children in traversal priority
-// (bit 24 + (slot ^ rs): nearest octant first when popped from the top), bits 23..0 = leaf items
-// relative to tri_base.  Child boxes are decoded from 8-bit grids; the slab test is conservative:
+// (bit 24 + (slot ^ rs): nearest octant first when popped from the top), bits 15..0 = leaf items
+// relative to tri_base (dense: bit k = item tri_base + k).  Child boxes are decoded from 8-bit grids; the slab test is conservative:
 // near planes are pushed down and far planes up by 2^-20 relative (explicit FMAs).
 PT_D uint32_t node_test(const Bvh8Node* __restrict__ nodes, uint32_t idx, const RayFrame& f, float tmin, float tmax,
                         uint32_t& child_base, uint32_t& tri_base, uint32_t& imask) {
@@ -177,15 +177,18 @@ PT_D uint32_t node_test(const Bvh8Node* __restrict__ nodes, uint32_t idx, const 
     const uint32_t nx[2] = {px ? n2.x : n3.z, px ? n2.y : n3.w}, fx[2] = {px ? n3.z : n2.x, px ? n3.w : n2.y};
     const uint32_t ny[2] = {py ? n2.z : n4.x, py ? n2.w : n4.y}, fy[2] = {py ? n4.x : n2.z, py ? n4.y : n2.w};
     const uint32_t nz[2] = {pz ? n3.x : n4.z, pz ? n3.y : n4.w}, fz[2] = {pz ? n4.z : n3.x, pz ? n4.w : n3.y};
-    const uint32_t meta[2] = {n1.z, n1.w};
-    uint32_t hits = 0;
+    const uint32_t valid = n1.z;         // Bvh8Node::valid
+    uint32_t hits = 0, leaf_off = 0;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int i = 4 * h + j;
-            const uint32_t m = (meta[h] >> (8 * j)) & 0xffu;
-            if (m == 0u) continue;
+            const bool inner = ((valid >> (24 + i)) & 1u) != 0u;
+            const uint32_t unary = (valid >> (kLeafStride * (uint32_t)i)) & 3u;     // leaf slot: 01 or 11
+            const uint32_t off = leaf_off;
+            leaf_off += __popc(unary);
+            if (!inner && unary == 0u) continue;
             const float t0x = __fmaf_rn((float)((nx[h] >> (8 * j)) & 0xffu), an[0], bn[0]);
             const float t0y = __fmaf_rn((float)((ny[h] >> (8 * j)) & 0xffu), an[1], bn[1]);
             const float t0z = __fmaf_rn((float)((nz[h] >> (8 * j)) & 0xffu), an[2], bn[2]);
@@ -195,8 +198,8 @@ PT_D uint32_t node_test(const Bvh8Node* __restrict__ nodes, uint32_t idx, const 
             const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             if (tn <= tf) {
-                if ((imask >> i) & 1u) hits |= 1u << (24u + ((uint32_t)i ^ f.rs));
-                else hits |= (m >> 5) << (m & 31u);
+                if (inner) hits |= 1u << (24u + ((uint32_t)i ^ f.rs));
+                else hits |= unary << off;
             }
         }
     }

@@ -37,18 +37,19 @@ PT_HD uint32_t perm8(uint32_t x, uint32_t rs) {
     return x;
 }
 
-// Node test of K-trace.  Hit-mask assembly: every child contributes its pre-expanded word from
-// node_bits (inner children at the fixed bit 24 + slot) under one FSETP + SEL, and the inner byte is
-// brought into traversal priority order (bit 24 + (slot ^ rs)) by one shared-memory lookup — instead
-// of two byte extracts, a shift and a select per child plus the octant XOR (84 -> ~27 instructions
-// per node, profiles/r1b).
-PT_D uint32_t node_test_fast(const Bvh8Node* __restrict__ nodes, const uint4* __restrict__ node_bits, uint32_t idx, const RayFrame& f,
+// Node test of K-trace.  Hit-mask assembly: a child that passes the slab test contributes a compile-time word — its inner bit
+// 24 + slot and both bits of its leaf slot — under one FSETP + SEL, and one AND with the node's `valid` word keeps what the slot
+// really holds; the inner byte is brought into traversal priority order (bit 24 + (slot ^ rs)) by one shared-memory lookup.
+// (Rounds 1-2 loaded the eight words per node from a second array, `node_bits`: two more LDG.128 that ptxas sank below the plane
+// arithmetic — a second memory round trip per node test — and 32 of the 112 bytes a node test fetched.)
+// Returns bits 31..24 = inner hits in priority order, bits 15..0 = leaf hits in the slot-strided positions of `valid`; `valid`
+// itself is returned for the triangle phase, which turns a bit position into a dense item index with one POPC.
+PT_D uint32_t node_test_fast(const Bvh8Node* __restrict__ nodes, uint32_t idx, const RayFrame& f,
                              float tmin, float tmax, uint32_t bias, const uint8_t* __restrict__ perm_lut, uint32_t& child_base,
-                             uint32_t& tri_base, uint32_t& imask) {
+                             uint32_t& tri_base, uint32_t& imask, uint32_t& valid) {
     const uint4* q = reinterpret_cast<const uint4*>(nodes + idx);
     const uint4 n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2), n3 = __ldg(q + 3), n4 = __ldg(q + 4);
-    const uint4 c0 = __ldg(node_bits + 2 * (size_t)idx), c1 = __ldg(node_bits + 2 * (size_t)idx + 1);
-    child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24;
+    child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24; valid = n1.z;
     const float eps = 9.5367431640625e-7f;  // 2^-20
     float anx, any, anz, afx, afy, afz, bnx, bny, bnz, bfx, bfy, bfz;
     {
@@ -79,19 +80,19 @@ PT_D uint32_t node_test_fast(const Bvh8Node* __restrict__ nodes, const uint4* __
         const uint32_t nxw = px ? lox : hix, fxw = px ? hix : lox;
         const uint32_t nyw = py ? loy : hiy, fyw = py ? hiy : loy;
         const uint32_t nzw = pz ? loz : hiz, fzw = pz ? hiz : loz;
-        const uint4 cw = h ? c1 : c0;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const float t0x = __fmaf_rn(q2f(nxw, j, bias), anx, bnx), t0y = __fmaf_rn(q2f(nyw, j, bias), any, bny), t0z = __fmaf_rn(q2f(nzw, j, bias), anz, bnz);
             const float t1x = __fmaf_rn(q2f(fxw, j, bias), afx, bfx), t1y = __fmaf_rn(q2f(fyw, j, bias), afy, bfy), t1z = __fmaf_rn(q2f(fzw, j, bias), afz, bfz);
             const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-            const uint32_t bits = j == 0 ? cw.x : (j == 1 ? cw.y : (j == 2 ? cw.z : cw.w));
-            hits |= (tn <= tf) ? bits : 0u;
+            const uint32_t slot_bits = (1u << (24 + 4 * h + j)) | (3u << (kLeafStride * (4 * h + j)));     // immediate
+            hits |= (tn <= tf) ? slot_bits : 0u;
         }
     }
+    hits &= valid;
     const uint32_t top = perm_lut[(f.rs << 8) | (hits >> 24)];
-    return (top << 24) | (hits & 0x00FFFFFFu);
+    return (top << 24) | (hits & 0x0000FFFFu);
 }
 
 struct TraceIO {
@@ -115,7 +116,10 @@ struct TraceIO {
 };
 
 constexpr int kTraceBlock = 128;
-constexpr int kTraceMinBlocks = 8;       // 64 registers: 32 resident warps per SM (see test_triangle_rec)
+#ifndef PT_TRACE_MIN_BLOCKS
+#define PT_TRACE_MIN_BLOCKS 8
+#endif
+constexpr int kTraceMinBlocks = PT_TRACE_MIN_BLOCKS;       // 8: 64 registers, 32 resident warps per SM (see test_triangle_rec)
 
 // Triangle test of K-trace.  The closest hit is kept in the slot's hit record (hit_a / hit_b, global memory) and only its distance
 // in a register; bit 31 of `slot` says that a record has been written.  Five registers less across the loop than a Hit in
@@ -210,6 +214,9 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
     float tmin = 0.0f, tmax = 0.0f;
     uint32_t cur_inst = kInvalidId;
     float best_t = kMissT;               // distance of the closest hit; the hit itself is in the slot's record (test_triangle_rec)
+    // G = node group: (child_base, inner hits << 24 | imask).  T = leaf group: (tri_base, pending << 16 | valid16): the pending
+    // items as slot-strided bits (Bvh8Node::valid positions) above the node's valid bits, which turn a position into the dense
+    // item index.  "Items pending" is T.y >= 0x10000; a stacked T always has a bit in 8..23 set, a stacked G never.
     uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
     uint2 stack[kStackSize];
 #define PT_STACK_PUSH(v) do { if (sp < kStackSize) stack[sp++] = (v); else *sc.error_flag = 1u; } while (0)
@@ -260,18 +267,23 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
         // ---- phase 1: one leaf item.  (Postponing triangle groups while few lanes hold one — Ylitie et
         // al. 2017 — and repeating the phase while many do were both measured: neither pays here, and the
         // warp votes they need cost 3-4 % each; profiles/r1_experiments.md.)
-        const bool has_t = active && T.y != 0u;
+        const bool has_t = active && T.y >= 0x10000u;
         if (has_t) {
-            const uint32_t b = (uint32_t)__ffs((int)T.y) - 1u;
-            T.y &= T.y - 1u;
+            // next pending item = lowest pending bit, at position b < 16 of the strided layout; its dense index is the number of
+            // valid bits below b.  Decrementing the pending half flips bit 16 + b and the pending zeros below it, so
+            // (T.y ^ (T.y - 0x10000)) >> 17 == (1 << b) - 1 without a find-first-set (one POPC is the only slow-pipe instruction
+            // ahead of the triangle loads; FLO + POPC measured C2 +0.6 %, profiles/r2w_variants.txt)
+            const uint32_t dec = T.y - 0x10000u;
+            const uint32_t item = T.x + (uint32_t)__popc(T.y & ((T.y ^ dec) >> 17));
+            T.y &= dec;                                                         // clears the lowest pending bit
             if (kFlat || cur_inst != kInvalidId) {
-                test_triangle_rec(sc.tris, T.x + b, f.o, rp, tmin, tmax, cur_inst, best_t, slot, io.hit_a + (size_t)PT_SLOT * io.hit_a_stride,
+                test_triangle_rec(sc.tris, item, f.o, rp, tmin, tmax, cur_inst, best_t, slot, io.hit_a + (size_t)PT_SLOT * io.hit_a_stride,
                                   io.hit_b + (size_t)PT_SLOT * io.hit_b_stride);
             } else {
                 // TLAS leaf item = instance: keep the remaining work for later and enter the BLAS
-                if (T.y) PT_STACK_PUSH(T);
+                if (T.y >= 0x10000u) PT_STACK_PUSH(T);
                 if (G.y & 0xFF000000u) PT_STACK_PUSH(G);
-                cur_inst = __ldg(sc.tlas_leaf_instance + T.x + b);
+                cur_inst = __ldg(sc.tlas_leaf_instance + item);
                 const uint4 ent = __ldg(reinterpret_cast<const uint4*>(&sc.instances[cur_inst].blas_root));   // blas_root, -, mesh | flags, -
                 const bool identity = (ent.z & kInstIdentity) != 0u;
                 // sentinel: y = 1 when the world frame must be re-loaded on the way out
@@ -288,7 +300,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
             }
         }
         // ---- pop when there is nothing else to do
-        if (active && T.y == 0u && (G.y & 0xFF000000u) == 0u) {
+        if (active && T.y < 0x10000u && (G.y & 0xFF000000u) == 0u) {
             for (;;) {
                 if (sp == 0) {
                     if (!(slot & 0x80000000u)) {         // no hit was recorded: the miss record of hit_init()
@@ -306,21 +318,21 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                     cur_inst = kInvalidId;
                     continue;
                 }
-                if (e.y & 0xFF000000u) { G = e; } else { T = e; }
+                if (e.y & 0x00FFFF00u) { T = e; } else { G = e; }
                 break;
             }
         }
         // ---- phase 2: one node test
-        if (active && T.y == 0u && (G.y & 0xFF000000u) != 0u) {
+        if (active && T.y < 0x10000u && (G.y & 0xFF000000u) != 0u) {
             const uint32_t k = 31u - (uint32_t)__clz(G.y);
             G.y &= ~(1u << k);
             const uint32_t s = (k - 24u) ^ f.rs;
             const uint32_t node = G.x + __popc(G.y & 0xffu & ((1u << s) - 1u));
             if (G.y & 0xFF000000u) PT_STACK_PUSH(G);
-            uint32_t cb, tb, im;
-            const uint32_t hits = node_test_fast(sc.nodes, sc.node_bits, node, f, tmin, fminf(tmax, best_t), bias, perm_lut, cb, tb, im);
+            uint32_t cb, tb, im, valid;
+            const uint32_t hits = node_test_fast(sc.nodes, node, f, tmin, fminf(tmax, best_t), bias, perm_lut, cb, tb, im, valid);
             G = make_uint2(cb, (hits & 0xFF000000u) | im);
-            T = make_uint2(tb, hits & 0x00FFFFFFu);
+            T = make_uint2(tb, __byte_perm(valid, hits, 0x5410u));      // leaf hits << 16 | valid16
         }
     }
 }
