@@ -263,13 +263,32 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
             if (iter == 0u) {
                 seed = prng_seed(x, y, fp.cam.frame_count);                                  // :41
             } else {
-                const float4 a4 = pb.atten_sx[slot], c4 = pb.color_sy[slot], f4 = pb.final_sb[slot];
-                atten = v3(a4.x, a4.y, a4.z); color = v3(c4.x, c4.y, c4.z); final_color = v3(f4.x, f4.y, f4.z);
+                const float4 a4 = pb.atten_sx[slot], c4 = pb.color_sy[slot];
+                atten = v3(a4.x, a4.y, a4.z); color = v3(c4.x, c4.y, c4.z);
                 seed.x = __float_as_uint(a4.w); seed.y = __float_as_uint(c4.w);
-                s = __float_as_uint(f4.w) & 0xffffu; j = __float_as_uint(f4.w) >> 16;
+                if (kMulti) {
+                    const float4 f4 = pb.final_sb[slot];
+                    final_color = v3(f4.x, f4.y, f4.z);
+                    s = __float_as_uint(f4.w) & 0xffffu; j = __float_as_uint(f4.w) >> 16;
+                } else {
+                    j = iter;        // S == 1: no restarts, so iteration k shades segment k of sample 0 and the sum over samples is still 0:
+                }                    // the third state record is neither written nor read (16 B per path and iteration each way)
             }
-            const float4 ro = pb.ray_o[slot], rd = pb.ray_d[slot];
-            V3 origin = v3(ro.x, ro.y, ro.z), direction = v3(rd.x, rd.y, rd.z);
+            // S == 1, iteration 0 shades the primary hit: the ray is K-raygen's, restated here from the pixel (same function, same
+            // bits — restarted samples rely on that already) instead of read back: 32 B per pixel less to fetch (C2 K-shade
+            // 0.295 -> 0.281 ms together with the two-record path state; in the S > 1 kernel, where it touches one iteration of
+            // hundreds, the extra code measured +1.5 % on C3 and is left out: profiles/r2y_variants.txt)
+            V3 origin, direction;
+            if (!kMulti && iter == 0u) {
+                origin = v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]);
+                direction = primary_direction(fp.cam, x, y, pm.width, pm.height);
+            } else {
+                const float4 rd = pb.ray_d[slot];
+                direction = v3(rd.x, rd.y, rd.z);
+                origin = v3s(0.0f);
+                // the origin is only consumed by a segment that continues (:86): with S == 1 no path of the last iteration does
+                if (kMulti || iter + 1u < B) { const float4 ro = pb.ray_o[slot]; origin = v3(ro.x, ro.y, ro.z); }
+            }
             HitRec h;
             {
                 const float4 ha = pb.hit_a[slot]; const uint2 hb = pb.hit_b[slot];
@@ -382,7 +401,7 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                 store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, origin, direction, 0.001f, 10000.0f);
                 pb.atten_sx[slot] = make_float4(atten.x, atten.y, atten.z, __uint_as_float(seed.x));
                 pb.color_sy[slot] = make_float4(color.x, color.y, color.z, __uint_as_float(seed.y));
-                pb.final_sb[slot] = make_float4(final_color.x, final_color.y, final_color.z, __uint_as_float(s | (j << 16)));
+                if (kMulti) pb.final_sb[slot] = make_float4(final_color.x, final_color.y, final_color.z, __uint_as_float(s | (j << 16)));
             }
         }
         queue_push(qout, qout_count, emit, slot);
