@@ -133,7 +133,7 @@ PT_D void store_ray(float4* __restrict__ ray_o, float4* __restrict__ ray_d, floa
     ray_d[slot] = make_float4(d.x, d.y, d.z, tmax);
     ray_e[slot] = make_float4(f.idir.x, f.idir.y, f.idir.z, __uint_as_float(bits));
     ray_s[slot] = make_float4(rp.m0x, rp.m0y, rp.m0z, rp.Sz);
-    ray_m[slot] = make_float4(rp.m1x, rp.m1y, rp.m1z, 0.0f);
+    ray_m[slot] = make_float4(rp.m1x, rp.m1y, rp.m1z, tmax);    // tmax again: K-trace's fetch then needs no ray_d (64 B per ray)
 }
 
 // world -> object: o' = Ainv*(o - T), d' = Ainv*d (not renormalised: t is shared between spaces).

@@ -106,7 +106,7 @@ struct TraceIO {
     const float4* ray_d;        // direction.xyz, tmax
     const float4* ray_e;        // 1/direction (box tests), bits: octant | kz<<3
     const float4* ray_s;        // shear row m0.xyz, Sz
-    const float4* ray_m;        // shear row m1.xyz, unused
+    const float4* ray_m;        // shear row m1.xyz, tmax
     float4* hit_a;              // per slot: t, b1, b2, instance
     uint2* hit_b;               // per slot: primitive_index, triangle_index
     uint32_t hit_a_stride;      // in float4: 1 = SoA, 2 = HitRec array
@@ -163,15 +163,20 @@ constexpr int kRefillMin = 4;
 #endif
 
 // world-space ray frame + shear constants of one slot (what store_ray() wrote)
+// The flat kernel fetches four of the five records (64 B): the direction itself is only needed on entry into a transformed
+// instance, and tmax rides in ray_m.w too (K-trace C2 1.068 -> 1.065 ms, C3 554.7 -> 548.4, C5 39.9 -> 39.6).  The two-level
+// kernel keeps the five-record fetch: without it C4 measured 13.31 -> 13.45 ms (profiles/r2z_variants.txt).
+template <bool kFlat>
 PT_D void load_ray(const TraceIO& io, uint32_t slot, RayFrame& f, RayPre& rp, float& tmin, float& tmax) {
-    const float4 ro = io.ray_o[slot], rd = io.ray_d[slot], re = io.ray_e[slot], rs = io.ray_s[slot], rm = io.ray_m[slot];
+    const float4 ro = io.ray_o[slot], re = io.ray_e[slot], rs = io.ray_s[slot], rm = io.ray_m[slot];
+    tmax = kFlat ? rm.w : io.ray_d[slot].w;
     f.o = v3(ro.x, ro.y, ro.z); f.idir = v3(re.x, re.y, re.z);
     const uint32_t bits = __float_as_uint(re.w);
     f.rs = bits & 7u;
     rp.kz = (int)((bits >> 3) & 3u);
     rp.m0x = rs.x; rp.m0y = rs.y; rp.m0z = rs.z; rp.Sz = rs.w;
     rp.m1x = rm.x; rp.m1y = rm.y; rp.m1z = rm.z;
-    tmin = ro.w; tmax = rd.w;
+    tmin = ro.w;
 }
 
 #define PT_TRACE_BOUNDS __launch_bounds__(kTraceBlock, kTraceMinBlocks)
@@ -248,7 +253,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                     if (rank < avail) {
                         const uint32_t qi = w_next + rank;
                         slot = io.queue ? io.queue[qi] : qi;
-                        load_ray(io, slot, f, rp, tmin, tmax);
+                        load_ray<kFlat>(io, slot, f, rp, tmin, tmax);
                         cur_inst = sc.start_inst;
                         best_t = kMissT;
                         sp = 0;
@@ -314,7 +319,7 @@ __global__ void PT_TRACE_BOUNDS k_trace_persistent(DeviceScene sc, TraceIO io) {
                 PT_STACK_POP(e);
                 if (kFlat) { G = e; break; }
                 if (e.x == 0xFFFFFFFFu) {
-                    if (e.y) { float t0, t1; load_ray(io, PT_SLOT, f, rp, t0, t1); }
+                    if (e.y) { float t0, t1; load_ray<kFlat>(io, PT_SLOT, f, rp, t0, t1); }
                     cur_inst = kInvalidId;
                     continue;
                 }
