@@ -117,7 +117,7 @@ extern "C" int pt_trace_rays_noalloc(PtRenderer* r, const PtRay* device_rays, si
     io.ray_o = s.ray_o; io.ray_d = s.ray_d; io.ray_e = s.ray_e; io.ray_s = s.ray_s; io.ray_m = s.ray_m;
     io.hit_a = reinterpret_cast<float4*>(s.hits); io.hit_a_stride = 2;
     io.hit_b = reinterpret_cast<uint2*>(s.hits) + 2; io.hit_b_stride = 4;
-    io.bias_word = 0x4B000000u; io.chunk = r->dims.chunk;
+    io.bias_word = 0x4B000000u; io.chunk = r->dims.chunk; io.uniform_origin = 0u; io.origin = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     const int blocks = r->num_sms * 4;   // as launch_trace_rays (render.cu)
     if (sc.start_inst != kInvalidId) k_trace_persistent<true><<<blocks, kTraceBlock, 0, st>>>(sc, io);
     else k_trace_persistent<false><<<blocks, kTraceBlock, 0, st>>>(sc, io);

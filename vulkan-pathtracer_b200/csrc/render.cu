@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(256) k_raygen(PixelMap pm, PathBuffers pb, Fra
             // iteration 0, which saves 48 B written here and 48 B read there per pixel
             const V3 d = primary_direction(fp.cam, x, y, pm.width, pm.height);
             store_ray(pb.ray_o, pb.ray_d, pb.ray_e, pb.ray_s, pb.ray_m, slot, v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]), d,
-                      0.001f, 10000.0f);                                                                         // :38-39,47-48
+                      0.001f, 10000.0f, fp.primary_lean);                                                        // :38-39,47-48
         }
     }
     queue_push(pb.queue[0], pb.qcount + 0, live, slot);
@@ -286,8 +286,10 @@ __global__ void PT_SHADE_BOUNDS k_shade(DeviceScene sc, PixelMap pm, PathBuffers
                 const float4 rd = pb.ray_d[slot];
                 direction = v3(rd.x, rd.y, rd.z);
                 origin = v3s(0.0f);
-                // the origin is only consumed by a segment that continues (:86): with S == 1 no path of the last iteration does
-                if (kMulti || iter + 1u < B) { const float4 ro = pb.ray_o[slot]; origin = v3(ro.x, ro.y, ro.z); }
+                // the origin is only consumed by a segment that continues (:86): with S == 1 no path of the last iteration does;
+                // primary rays (iteration 0) start at the camera, and K-raygen may not have written their origins (primary_lean)
+                if (iter == 0u) origin = v3(fp.cam.position[0], fp.cam.position[1], fp.cam.position[2]);
+                else if (kMulti || iter + 1u < B) { const float4 ro = pb.ray_o[slot]; origin = v3(ro.x, ro.y, ro.z); }
             }
             HitRec h;
             {
@@ -529,13 +531,15 @@ void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams&
     k_raygen<<<(pm.num_slots + 255) / 256, 256, 0, st>>>(pm, pb, fp);
 }
 
-void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
+void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, const float* uniform_origin, uint32_t tlas2_count,
                   const uint32_t* tlas2_leaf_instance, const LaunchDims& dims, cudaStream_t st) {
     if (mode == TRACE_BVH8) {
         TraceIO io;
         io.queue = pb.queue[iter & 1u]; io.count_ptr = pb.qcount + iter; io.count = 0; io.cursor = pb.trace_next + iter;
         io.ray_o = pb.ray_o; io.ray_d = pb.ray_d; io.ray_e = pb.ray_e; io.ray_s = pb.ray_s; io.ray_m = pb.ray_m; io.hit_a = pb.hit_a; io.hit_b = pb.hit_b;
         io.hit_a_stride = 1; io.hit_b_stride = 1; io.bias_word = 0x4B000000u; io.chunk = dims.chunk;
+        io.uniform_origin = uniform_origin ? 1u : 0u;
+        io.origin = uniform_origin ? make_float4(uniform_origin[0], uniform_origin[1], uniform_origin[2], 0.001f) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         if (sc.start_inst != kInvalidId) k_trace_persistent<true><<<dims.trace_flat, kTraceBlock, 0, st>>>(sc, io);
         else k_trace_persistent<false><<<dims.trace_persistent, kTraceBlock, 0, st>>>(sc, io);
         return;
@@ -581,7 +585,7 @@ void launch_trace_rays(const DeviceScene& sc, const RayRec* rays, uint32_t n, Hi
         io.ray_o = so; io.ray_d = sd; io.ray_e = se; io.ray_s = ss; io.ray_m = sm;
         io.hit_a = reinterpret_cast<float4*>(hits); io.hit_a_stride = 2;
         io.hit_b = reinterpret_cast<uint2*>(hits) + 2; io.hit_b_stride = 4;
-        io.bias_word = 0x4B000000u; io.chunk = dims.chunk;
+        io.bias_word = 0x4B000000u; io.chunk = dims.chunk; io.uniform_origin = 0u; io.origin = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         if (sc.start_inst != kInvalidId) k_trace_persistent<true><<<blocks, kTraceBlock, 0, st>>>(sc, io);
         else k_trace_persistent<false><<<blocks, kTraceBlock, 0, st>>>(sc, io);
         return;

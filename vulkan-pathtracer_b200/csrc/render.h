@@ -43,6 +43,10 @@ struct FrameParams {
     PtCamera cam;
     uint32_t num_samples, num_bounces;
     uint32_t flags;
+    // which records of a primary ray nobody reads (bit 0: origin + tmin, bit 1: direction): the flat instantiation of the
+    // persistent K-trace takes the camera position as a launch constant at iteration 0 and never reads directions, and K-shade
+    // restates the primary ray from the pixel when S == 1.  Set by pt_render; 0 for two-level scenes and the walker / counting modes.
+    uint32_t primary_lean;
     float* image;        // W*H*4 fp32 (full image; non-owned pixels untouched)
     uint32_t* id_inst;   // W*H each
     uint32_t* id_prim;
@@ -64,7 +68,8 @@ struct LaunchDims {
 LaunchDims compute_launch_dims(int num_sms);
 
 void launch_raygen(const PixelMap& pm, const PathBuffers& pb, const FrameParams& fp, cudaStream_t st);
-void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, uint32_t tlas2_count,
+// uniform_origin: non-null at iteration 0 when FrameParams::primary_lean bit 0 is set (camera position; tmin is K-raygen's 0.001)
+void launch_trace(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, TraceMode mode, const float* uniform_origin, uint32_t tlas2_count,
                   const uint32_t* tlas2_leaf_instance, const LaunchDims& dims, cudaStream_t st);
 // PT_FLAG_SORT_BY_MATERIAL: counting sort of queue `iter` by the material of each path's hit (misses last)
 void launch_material_sort(const DeviceScene& sc, const PathBuffers& pb, uint32_t iter, int num_sms, cudaStream_t st);

@@ -123,14 +123,15 @@ PT_D void frame_set(RayFrame& f, V3 o, V3 d) {
 // from it (box-test reciprocals + octant, watertight shear rows), 80 bytes per slot.  Computed
 // where rays are born (K-raygen / K-shade / k_ray_setup, all lanes busy) instead of in K-trace,
 // where refilled lanes would do it two at a time (profiles/r1a: 22 % of K-trace's issue slots).
+// skip: bit 0 = do not write ray_o, bit 1 = do not write ray_d (FrameParams::primary_lean; 0 everywhere but K-raygen)
 PT_D void store_ray(float4* __restrict__ ray_o, float4* __restrict__ ray_d, float4* __restrict__ ray_e, float4* __restrict__ ray_s,
-                    float4* __restrict__ ray_m, uint32_t slot, V3 o, V3 d, float tmin, float tmax) {
+                    float4* __restrict__ ray_m, uint32_t slot, V3 o, V3 d, float tmin, float tmax, uint32_t skip = 0u) {
     RayFrame f;
     frame_set(f, o, d);
     const RayPre rp = ray_precompute(d);
     const uint32_t bits = f.rs | ((uint32_t)rp.kz << 3);
-    ray_o[slot] = make_float4(o.x, o.y, o.z, tmin);
-    ray_d[slot] = make_float4(d.x, d.y, d.z, tmax);
+    if (!(skip & 1u)) ray_o[slot] = make_float4(o.x, o.y, o.z, tmin);
+    if (!(skip & 2u)) ray_d[slot] = make_float4(d.x, d.y, d.z, tmax);
     ray_e[slot] = make_float4(f.idir.x, f.idir.y, f.idir.z, __uint_as_float(bits));
     ray_s[slot] = make_float4(rp.m0x, rp.m0y, rp.m0z, rp.Sz);
     ray_m[slot] = make_float4(rp.m1x, rp.m1y, rp.m1z, tmax);    // tmax again: K-trace's fetch then needs no ray_d (64 B per ray)

@@ -113,6 +113,10 @@ struct TraceIO {
     uint32_t hit_b_stride;      // in uint2:  1 = SoA, 4 = HitRec array (hit_b = base + 2)
     uint32_t bias_word;
     uint32_t chunk;          // rays a warp takes per global atomic         // 0x4B000000 (see q2f)
+    // primary wavefront of a frame: every ray starts at the camera, so K-raygen does not write origins and the fetch takes
+    // (origin.xyz, tmin) from here (C2: 33 MB less written by K-raygen and 33 MB less read here per frame)
+    uint32_t uniform_origin; // 1: use `origin` instead of ray_o[slot] (flat instantiation only)
+    float4 origin;
 };
 
 constexpr int kTraceBlock = 128;
@@ -168,7 +172,9 @@ constexpr int kRefillMin = 4;
 // kernel keeps the five-record fetch: without it C4 measured 13.31 -> 13.45 ms (profiles/r2z_variants.txt).
 template <bool kFlat>
 PT_D void load_ray(const TraceIO& io, uint32_t slot, RayFrame& f, RayPre& rp, float& tmin, float& tmax) {
-    const float4 ro = io.ray_o[slot], re = io.ray_e[slot], rs = io.ray_s[slot], rm = io.ray_m[slot];
+    const float4 re = io.ray_e[slot], rs = io.ray_s[slot], rm = io.ray_m[slot];
+    // (flat kernel only: in the two-level kernel the extra select measured C4 13.28 -> 13.68 ms, profiles/r3a_variants.txt)
+    const float4 ro = (kFlat && io.uniform_origin) ? io.origin : io.ray_o[slot];
     tmax = kFlat ? rm.w : io.ray_d[slot].w;
     f.o = v3(ro.x, ro.y, ro.z); f.idir = v3(re.x, re.y, re.z);
     const uint32_t bits = __float_as_uint(re.w);
