@@ -76,7 +76,20 @@ __global__ void __launch_bounds__(256) k_raygen(PixelMap pm, PathBuffers pb, Fra
                       0.001f, 10000.0f, fp.primary_lean);                                                        // :38-39,47-48
         }
     }
-    queue_push(pb.queue[0], pb.qcount + 0, live, slot);
+    // block-aggregated append: one atomic per 256 slots.  A full-HD frame is 64 800 warps; one same-address atomic per warp
+    // (queue_push) serialises in L2 for about as long as the kernel needs to write its rays.
+    __shared__ uint32_t s_off[9];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t mask = __ballot_sync(0xffffffffu, live);
+    if (lane == 0u) s_off[warp] = (uint32_t)__popc(mask);
+    __syncthreads();
+    if (threadIdx.x == 0u) {
+        uint32_t total = 0;
+        for (int w = 0; w < 8; ++w) { const uint32_t c = s_off[w]; s_off[w] = total; total += c; }
+        s_off[8] = total ? atomicAdd(pb.qcount + 0, total) : 0u;
+    }
+    __syncthreads();
+    if (live) pb.queue[0][s_off[8] + s_off[warp] + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = slot;
 }
 
 // ------------------------------------------------------------------ K-trace
