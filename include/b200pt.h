@@ -337,7 +337,8 @@ int pt_set_profiling(PtRenderer* r, int enabled);
 int pt_get_stats(PtRenderer* r, PtStats* out);
 
 /* Kernel-level access for parity tests: trace `n` arbitrary world-space rays through the same
- * BVH and traversal kernel pt_render uses (host pointers). */
+ * BVH and traversal kernel pt_render uses (host pointers).  n < 2^31 (PT_ERR_INVALID_ARGUMENT beyond: the
+ * kernel keeps a flag in bit 31 of a ray's slot index; the same bound holds for the pixel slots of a frame). */
 int pt_trace_rays(PtRenderer* r, const PtRay* rays, size_t n, PtHit* hits);
 /* The same query for callers that cannot allocate (code under CUDA graph capture, tight serving
  * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference: added
