@@ -1,13 +1,14 @@
 // trace_kernel.cuh — K-trace: the persistent-thread BVH8 traversal kernel of the wavefront loop.
 //
 // Structure (evidence for each choice is in profiles/ and DESIGN.md §K-trace):
-//  * persistent warps; each warp owns a chunk of the ray queue taken with ONE global atomic per 128
+//  * persistent warps; each warp owns a chunk of the ray queue taken with ONE global atomic per 32
 //    rays; lanes whose ray has terminated are refilled from the warp's chunk with a ballot (dynamic
 //    fetch, Aila & Laine 2009), so a warp never waits for its slowest ray;
 //  * every loop iteration a lane does at most one leaf item (triangle test / instance entry) and
 //    one node test, in two warp-wide phases, so lanes in the same phase execute together;
-//  * node test: 80-byte node as 5 x LDG.128, 8-bit planes converted with PRMT + FADD (no I2F on
-//    the quarter-rate pipe), branch-free hit-mask assembly, conservative slabs (explicit FMAs);
+//  * node test: 80-byte node as 5 x LDG.128 (nothing else is fetched), 8-bit planes converted with one PRMT each (no I2F
+//    on the quarter-rate pipe), branch-free hit-mask assembly from compile-time words + the node's `valid` word,
+//    conservative slabs (explicit FMAs);
 //  * the traversal stack (node / leaf groups, 8 bytes each) lives in thread-local memory;
 //  * the closest hit lives in the slot's hit record, only its distance in a register: 64 registers, 8 CTAs per SM.
 // The closest-hit semantics are exactly those of trace_bvh8() in trace.cuh (the simple walker that
