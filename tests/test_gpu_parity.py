@@ -523,6 +523,39 @@ def test_traversal_byte_counter(sponza):
     r.deinit()
 
 
+def test_lean_primary_records_survive_trace_mode_switches(sponza):
+    """K-raygen leaves out the ray records nobody reads (origin: launch constant of the flat K-trace; direction with S == 1).
+    The counting walker reads them, so a frame rendered through it must write them again, and the next frame of the
+    persistent kernel must not depend on what the walker left behind; the walker-only renderer gives the same image."""
+    cam = S.camera_default(320, 200, 0)
+    for spp in (1, 3):
+        r = b200pt.Renderer(sponza, 320, 200, spp, 3)
+        r.record(cam); r.sync(); first = r.image()
+        r.count_traversal()
+        assert bits_equal(first, r.image()).all()
+        r.record(S.camera_default(320, 200, 1)); r.sync()       # another frame in between
+        r.record(cam); r.sync()
+        assert bits_equal(first, r.image()).all()
+        r.deinit()
+        w = b200pt.Renderer(sponza, 320, 200, spp, 3, flags=b200pt.PT_FLAG_TRACE_WALKER)
+        w.record(cam); w.sync()
+        assert bits_equal(first, w.image()).all()
+        w.deinit()
+
+
+def test_trace_rays_rejects_counts_beyond_the_slot_index_range():
+    """K-trace keeps a flag in bit 31 of a ray's slot index, so pt_trace_rays takes fewer than 2^31 rays (include/b200pt.h);
+    the count is checked before either buffer is touched."""
+    import ctypes as C
+    r = b200pt.Renderer(S.cornell().pack(), 16, 16, 1, 1)
+    dummy = np.zeros(1, b200pt.PtRay_dtype)
+    out = np.zeros(1, b200pt.PtHit_dtype)
+    status = b200pt.lib().pt_trace_rays(r.handle, dummy.ctypes.data, C.c_size_t(1 << 31), out.ctypes.data)
+    assert status == -1 and b"too many rays" in b200pt.lib().pt_last_error()      # PT_ERR_INVALID_ARGUMENT
+    assert len(r.trace(random_rays(7, 64, dtype=b200pt.PtRay_dtype))) == 64     # the renderer is still usable
+    r.deinit()
+
+
 # ------------------------------------------------------------------ animated instances / camera replay (SURVEY 8(f) rank 4)
 def _moved_instances(ps, seed):
     """A copy of `ps` whose instances got new rigid transforms (rows of M), plus the (n, 16) matrix array."""
